@@ -1,0 +1,151 @@
+"""The Python drop-in: same inputs and outputs as the reference's
+``DenseGGNNChemModel.compute_final_node_representations``
+(/root/reference/chem_tensorflow_dense.py:312-340), with the method's implicit inputs
+(placeholders ``adjacency_matrix`` :192, ``node_mask`` :177, weights :202-241,
+``params['num_timesteps']``) made explicit arguments.
+"""
+from __future__ import annotations
+
+import threading
+from typing import Optional, Union
+
+import numpy as np
+import torch
+
+from .engine import Propagator
+from .weights import GGNNWeights, as_weights
+
+_cache_lock = threading.Lock()
+_cache = {}          # (thread id, device index, id(weights object)) -> (weights ref, Propagator)
+
+
+def get_propagator(weights, device=None) -> Propagator:
+    """Propagator for these weights on this device, cached per host thread (a ctx is not
+    thread-safe).  ``weights``: path to a reference .pickle, its dict, or GGNNWeights."""
+    if isinstance(weights, Propagator):
+        return weights
+    if not torch.cuda.is_available():
+        raise RuntimeError("ggnn_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    key = (threading.get_ident(), dev.index, weights if isinstance(weights, str) else id(weights))
+    with _cache_lock:
+        hit = _cache.get(key)
+        if hit is not None:
+            return hit[1]
+    prop = Propagator(as_weights(weights), dev)
+    with _cache_lock:
+        if len(_cache) > 16:
+            _cache.clear()
+        _cache[key] = (weights, prop)     # keep `weights` alive so id() stays unique
+    return prop
+
+
+def _to_device(x, device, dtype=None, name="tensor"):
+    """numpy / torch (any device) -> contiguous torch tensor on `device`.  Host arrays go
+    through pinned memory so the copy is a real async DMA."""
+    if isinstance(x, np.ndarray):
+        if dtype is not None and x.dtype != dtype:
+            x = x.astype(dtype)
+        t = torch.from_numpy(np.ascontiguousarray(x))
+        return t.pin_memory().to(device, non_blocking=True), "numpy"
+    if isinstance(x, torch.Tensor):
+        if x.device.type == "cpu":
+            return x.contiguous().pin_memory().to(device, non_blocking=True), "cpu"
+        return x, "cuda"
+    raise ValueError(f"{name} must be a numpy array or torch tensor, got {type(x).__name__}")
+
+
+def _device_of(*xs):
+    for x in xs:
+        if isinstance(x, torch.Tensor) and x.device.type == "cuda":
+            return x.device
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _back(out: torch.Tensor, kind: str):
+    if kind == "numpy":
+        return out.cpu().numpy()
+    if kind == "cpu":
+        return out.cpu()
+    return out
+
+
+def compute_final_node_representations(initial_node_representations, adjacency_matrix,
+                                       node_mask=None, weights=None, num_timesteps: Optional[int] = None,
+                                       fixed_ts: Optional[int] = None, precision: str = "fp32",
+                                       skip_padded: bool = False):
+    """T steps of GGNN propagation (message transform per edge type + bias, aggregation over
+    the adjacency, GRU update) -- reference chem_tensorflow_dense.py:312-340, 391-437.
+
+    initial_node_representations : float32 [b, v, h]
+    adjacency_matrix             : float32 or uint8 [b, 2E, v, v], A[b, e, target, source] != 0 <=> edge
+    node_mask                    : [b, v] or None.  The reference never reads it inside the path
+                                   (padded rows are GRU-updated like any other); it is used only
+                                   when skip_padded=True, to zero the padded rows of the result.
+    weights                      : path to a reference .pickle, its dict, GGNNWeights, or Propagator
+    num_timesteps                : defaults to the checkpoint's params['num_timesteps']
+    fixed_ts                     : k -> use edge_weights_fixed / edge_biases_fixed for k steps
+    precision                    : "fp32" (strict) or "tf32" (tensor cores, FP32 accumulate)
+    Returns float32 [b, v, h] of the same kind (numpy / torch cpu / torch cuda) as the input states.
+    """
+    if weights is None:
+        raise ValueError("weights is required (path to a reference .pickle, dict or GGNNWeights)")
+    if not torch.cuda.is_available():
+        raise RuntimeError("ggnn_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    dev = weights.device if isinstance(weights, Propagator) else _device_of(initial_node_representations, adjacency_matrix)
+    prop = get_propagator(weights, dev)
+    h0, kind = _to_device(initial_node_representations, dev, np.float32, "initial_node_representations")
+    if isinstance(adjacency_matrix, np.ndarray) and adjacency_matrix.dtype not in (np.float32, np.uint8):
+        adjacency_matrix = adjacency_matrix.astype(np.float32)     # the placeholder is tf.float32
+    adj, _ = _to_device(adjacency_matrix, dev, None, "adjacency_matrix")
+    if adj.dtype == torch.float64:
+        adj = adj.float()
+    out = prop.propagate_dense(h0, adj, num_timesteps=num_timesteps, fixed_ts=fixed_ts, precision=precision)
+    if skip_padded:
+        if node_mask is None:
+            raise ValueError("skip_padded=True needs node_mask")
+        m, _ = _to_device(node_mask, dev, np.float32, "node_mask")
+        if tuple(m.shape) != tuple(out.shape[:2]):
+            raise ValueError(f"node_mask must be [b, v] = {tuple(out.shape[:2])}, got {tuple(m.shape)}")
+        out = out * (m != 0).to(out.dtype).unsqueeze(-1)
+    return _back(out, kind)
+
+
+def compute_final_node_representations_sparse(node_states, edges, graph_offsets=None, weights=None,
+                                              num_timesteps: Optional[int] = None,
+                                              fixed_ts: Optional[int] = None, precision: str = "fp32"):
+    """Edge-list form (the reference declares it at chem_tensorflow.py:522-523 and never
+    implements it).  node_states float32 [N, h]; edges int32 [nnz, 3] = (src, channel, dst),
+    channel 0-based in [0, 2E), node ids global.  ``graph_offsets`` is accepted for interface
+    symmetry (graphs are independent, so it is not needed for the arithmetic)."""
+    del graph_offsets
+    if weights is None:
+        raise ValueError("weights is required")
+    if not torch.cuda.is_available():
+        raise RuntimeError("ggnn_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    dev = weights.device if isinstance(weights, Propagator) else _device_of(node_states, edges)
+    prop = get_propagator(weights, dev)
+    h0, kind = _to_device(node_states, dev, np.float32, "node_states")
+    e, _ = _to_device(edges, dev, np.int32, "edges")
+    if e.dtype != torch.int32:
+        e = e.to(torch.int32)
+    out = prop.propagate_edges(h0, e, num_timesteps=num_timesteps, fixed_ts=fixed_ts, precision=precision)
+    return _back(out, kind)
+
+
+def compact_adjacency(adjacency_matrix, weights_or_propagator=None):
+    """Dense adjacency -> (rowptr, col) canonical CSR on the device (np.argwhere order)."""
+    dev = _device_of(adjacency_matrix)
+    adj, kind = _to_device(adjacency_matrix, dev, None, "adjacency_matrix")
+    if isinstance(weights_or_propagator, Propagator):
+        prop = weights_or_propagator
+    elif weights_or_propagator is not None:
+        prop = get_propagator(weights_or_propagator, dev)
+    else:
+        raise ValueError("compact_adjacency needs a Propagator (or weights) to own the scratch")
+    rowptr, col, _ = prop.compact_adjacency(adj)
+    if kind == "numpy":
+        return rowptr.cpu().numpy(), col.cpu().numpy()
+    return rowptr, col

@@ -1,0 +1,379 @@
+// api.cu -- the C ABI of libggnn_b200.so (see include/ggnn_b200.h for the contract).
+#include "plan.cuh"
+#include "tf32.cuh"
+
+#include <new>
+
+namespace {
+
+struct arena {
+  char* p = nullptr;
+  size_t bytes = 0;
+};
+
+// Two grow-only arenas per ctx: [0] compaction (bitmask, rowptr, scan), [1] col + plan + step
+// buffers.  They are separate because [1] is sized only after the edge count is known and
+// must not move [0].
+struct ctx_ext {
+  arena ar[2];
+};
+
+ctx_ext* ext_of(ggnn_ctx* c) { return reinterpret_cast<ctx_ext*>(c->ws); }
+
+int arena_reserve(ggnn_ctx* ctx, int which, size_t bytes, cudaStream_t st) {
+  arena& a = ext_of(ctx)->ar[which];
+  if (a.bytes >= bytes) return GGNN_OK;
+  if (a.p) {
+    GGNN_CUDA(ctx, cudaStreamSynchronize(st));
+    GGNN_CUDA(ctx, cudaFree(a.p));
+    a.p = nullptr;
+    a.bytes = 0;
+  }
+  size_t want = align_up(bytes + bytes / 8, (size_t)1 << 20);
+  cudaError_t e = cudaMalloc(&a.p, want);
+  if (e != cudaSuccess) {
+    want = align_up(bytes, (size_t)1 << 20);
+    GGNN_CUDA(ctx, cudaMalloc(&a.p, want));
+  }
+  a.bytes = want;
+  return GGNN_OK;
+}
+
+int free_dev(ggnn_ctx* ctx, float*& p) {
+  if (p) { cudaFree(p); p = nullptr; }
+  return GGNN_OK;
+}
+
+int dup_dev(ggnn_ctx* ctx, float*& dst, const float* src, size_t n, cudaStream_t st) {
+  free_dev(ctx, dst);
+  GGNN_CUDA(ctx, cudaMalloc(&dst, n * sizeof(float)));
+  GGNN_CUDA(ctx, cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return GGNN_OK;
+}
+
+struct device_guard {
+  int prev = -1;
+  explicit device_guard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~device_guard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+extern "C" int ggnn_version(void) { return 100; }
+
+extern "C" int ggnn_create(ggnn_ctx** out, int device) {
+  if (!out) return GGNN_E_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return GGNN_E_CUDA;
+  ggnn_ctx* c = new (std::nothrow) ggnn_ctx();
+  if (!c) return GGNN_E_CUDA;
+  c->device = device;
+  device_guard g(device);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete c; return GGNN_E_CUDA; }
+  if (prop.major != 10) {   // sm_100a only: no fallback path exists
+    delete c;
+    return GGNN_E_UNSUPPORTED;
+  }
+  c->sm_count = prop.multiProcessorCount;
+  c->ws = reinterpret_cast<char*>(new (std::nothrow) ctx_ext());
+  if (cudaMallocHost(&c->h_mail, 8 * sizeof(int64_t)) != cudaSuccess ||
+      cudaMalloc(&c->d_mail, 8 * sizeof(int64_t)) != cudaSuccess) {
+    ggnn_destroy(c);
+    return GGNN_E_CUDA;
+  }
+  *out = c;
+  return GGNN_OK;
+}
+
+extern "C" void ggnn_destroy(ggnn_ctx* c) {
+  if (!c) return;
+  device_guard g(c->device);
+  cudaDeviceSynchronize();
+  for (int s = 0; s < GGNN_MAX_SLOTS; ++s) {
+    free_dev(c, c->edge[s].W);
+    free_dev(c, c->edge[s].B);
+    free_dev(c, c->edge[s].Wt_tf32);
+  }
+  free_dev(c, c->Wg); free_dev(c, c->bg); free_dev(c, c->Wc); free_dev(c, c->bc);
+  free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
+  if (c->ws) {
+    ctx_ext* e = ext_of(c);
+    for (auto& a : e->ar) if (a.p) cudaFree(a.p);
+    delete e;
+  }
+  for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (auto& e : c->prof_pool) cudaEventDestroy(e);
+  if (c->h_mail) cudaFreeHost(c->h_mail);
+  if (c->d_mail) cudaFree(c->d_mail);
+  delete c;
+}
+
+extern "C" const char* ggnn_last_error(const ggnn_ctx* c) { return c ? c->err : "null ctx"; }
+extern "C" int64_t ggnn_launch_count(const ggnn_ctx* c) { return c ? c->launches : 0; }
+
+extern "C" int ggnn_profile_enable(ggnn_ctx* c, int on) {
+  if (!c) return GGNN_E_ARG;
+  c->prof_on = on != 0;
+  return GGNN_OK;
+}
+
+extern "C" int ggnn_profile_read(ggnn_ctx* c, double* ms, int64_t* launches) {
+  if (!c) return GGNN_E_ARG;
+  device_guard g(c->device);
+  GGNN_CUDA(c, cudaDeviceSynchronize());
+  for (auto& r : c->prof_recs) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) c->prof_ms[r.stage] += t;
+    c->prof_pool.push_back(r.a);
+    c->prof_pool.push_back(r.b);
+  }
+  c->prof_recs.clear();
+  for (int i = 0; i < GGNN_N_STAGES; ++i) {
+    if (ms) ms[i] = c->prof_ms[i];
+    if (launches) launches[i] = c->prof_launches[i];
+    c->prof_ms[i] = 0;
+    c->prof_launches[i] = 0;
+  }
+  return GGNN_OK;
+}
+
+extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const float* W,
+                                const float* B, const float* Wg, const float* bg,
+                                const float* Wc, const float* bc, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (slot < 0 || slot >= GGNN_MAX_SLOTS || !W) GGNN_FAIL(ctx, GGNN_E_ARG, "set_weights: bad slot or null W");
+  if (two_e <= 0 || h <= 0) GGNN_FAIL(ctx, GGNN_E_ARG, "set_weights: two_e and h must be positive");
+  if (h % 4 != 0) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "hidden size %d is not a multiple of 4", h);
+  const bool has_gru = Wg && bg && Wc && bc;
+  if (slot == GGNN_SLOT_MAIN && !has_gru) GGNN_FAIL(ctx, GGNN_E_ARG, "set_weights: slot 0 needs the GRU cell");
+  if (slot != GGNN_SLOT_MAIN && (!ctx->gru_set || two_e != ctx->two_e || h != ctx->h))
+    GGNN_FAIL(ctx, GGNN_E_SHAPE, "set_weights: slot %d must match slot 0 (two_e=%d, h=%d)", slot, ctx->two_e, ctx->h);
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (slot == GGNN_SLOT_MAIN) {
+    if (ctx->two_e != two_e || ctx->h != h) ctx->edge[GGNN_SLOT_FIXED].set = false;
+    ctx->two_e = two_e;
+    ctx->h = h;
+    ctx->hp = (int)align_up((size_t)h, 32);
+  }
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  GGNN_TRY(dup_dev(ctx, ew.W, W, (size_t)two_e * h * h, st));
+  if (B) GGNN_TRY(dup_dev(ctx, ew.B, B, (size_t)two_e * h, st)); else free_dev(ctx, ew.B);
+  if (has_gru) {
+    GGNN_TRY(dup_dev(ctx, ctx->Wg, Wg, (size_t)4 * h * h, st));
+    GGNN_TRY(dup_dev(ctx, ctx->bg, bg, (size_t)2 * h, st));
+    GGNN_TRY(dup_dev(ctx, ctx->Wc, Wc, (size_t)2 * h * h, st));
+    GGNN_TRY(dup_dev(ctx, ctx->bc, bc, (size_t)h, st));
+    ctx->gru_set = true;
+  }
+  GGNN_TRY(ggnn_tf32_pack_weights(ctx, slot, has_gru, st));
+  ew.set = true;
+  return GGNN_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// A1
+extern "C" int ggnn_compact_adjacency(ggnn_ctx* ctx, const void* adj, int adj_dtype, int b,
+                                      int two_e, int v, int32_t* rowptr, int32_t* col,
+                                      int64_t col_capacity, int64_t* nnz_out_dev, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (b < 0 || two_e <= 0 || v <= 0) GGNN_FAIL(ctx, GGNN_E_ARG, "compact: bad sizes b=%d two_e=%d v=%d", b, two_e, v);
+  if ((b > 0 && !adj) || !rowptr || !nnz_out_dev || (col_capacity > 0 && !col) || col_capacity < 0)
+    GGNN_FAIL(ctx, GGNN_E_ARG, "compact: null pointer");
+  if (adj_dtype != GGNN_ADJ_F32 && adj_dtype != GGNN_ADJ_U8) GGNN_FAIL(ctx, GGNN_E_ARG, "compact: bad adj_dtype %d", adj_dtype);
+  const int64_t rows = (int64_t)b * two_e * v;
+  if (rows >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "compact: b*two_e*v = %lld rows needs int64 rowptr; split the batch", (long long)rows);
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  GGNN_TRY(arena_reserve(ctx, 0, ggnn_compact_tmp_bytes(rows * v, rows), st));
+  char* tmp = ext_of(ctx)->ar[0].p;
+  GGNN_TRY(ggnn_compact_count(ctx, adj, adj_dtype, rows, v, rowptr, nnz_out_dev, tmp, st));
+  GGNN_TRY(ggnn_compact_fill(ctx, rows, v, rowptr, col, col_capacity, tmp, st));
+  return GGNN_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+namespace {
+
+int check_ready(ggnn_ctx* ctx, int slot, int precision) {
+  if (slot < 0 || slot >= GGNN_MAX_SLOTS) GGNN_FAIL(ctx, GGNN_E_ARG, "bad weight slot %d", slot);
+  if (!ctx->gru_set || !ctx->edge[slot].set) GGNN_FAIL(ctx, GGNN_E_STATE, "weights for slot %d not set", slot);
+  if (precision != GGNN_PREC_FP32 && precision != GGNN_PREC_TF32) GGNN_FAIL(ctx, GGNN_E_ARG, "bad precision %d", precision);
+  if (precision == GGNN_PREC_TF32 && !ggnn_tf32_supported(ctx))
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "TF32 path does not support h=%d", ctx->h);
+  return GGNN_OK;
+}
+
+int read_i64(ggnn_ctx* ctx, const int64_t* dev, int64_t* out, cudaStream_t st) {
+  GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->h_mail, dev, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  GGNN_CUDA(ctx, cudaStreamSynchronize(st));
+  *out = ctx->h_mail[0];
+  return GGNN_OK;
+}
+
+// step buffers after the plan, from arena 1
+void take_step_bufs(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_step_bufs* sb) {
+  sb->msg = a.take<float>((size_t)plan.max_tiles * GGNN_TILE_M * h);
+  sb->acts = a.take<float>((size_t)plan.N * h);
+  sb->rh = a.take<float>((size_t)plan.N * h);
+  sb->u = a.take<float>((size_t)plan.N * h);
+}
+
+int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& sb,
+              float* h_state, int T, int precision, cudaStream_t st) {
+  for (int t = 0; t < T; ++t) {
+    if (precision == GGNN_PREC_TF32) GGNN_TRY(ggnn_step_tf32(ctx, slot, plan, sb, h_state, st));
+    else GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, sb, h_state, st));
+  }
+  return GGNN_OK;
+}
+
+// propagate `bc` graphs whose canonical CSR is (rowptr, col) with nnz edges; state in place.
+// `extra` = bytes at the front of arena 1 already in use (col of the dense path).
+int propagate_csr_chunk(ggnn_ctx* ctx, int slot, float* h_state, const int32_t* rowptr,
+                        const int32_t* col, int64_t bc, int v, int64_t nnz, int T, int precision,
+                        size_t extra, cudaStream_t st) {
+  ggnn_plan plan;
+  ggnn_step_bufs sb;
+  {
+    ws_alloc dry(nullptr);
+    dry.off = extra;
+    GGNN_TRY(ggnn_plan_from_csr(ctx, rowptr, col, bc, ctx->two_e, v, nnz, &plan, dry, true, st));
+    take_step_bufs(dry, plan, ctx->h, &sb);
+    if (ext_of(ctx)->ar[1].bytes < dry.off + 256) {
+      if (extra) GGNN_FAIL(ctx, GGNN_E_CAPACITY, "internal: arena 1 under-reserved");
+      GGNN_TRY(arena_reserve(ctx, 1, dry.off + 256, st));
+    }
+  }
+  ws_alloc a(ext_of(ctx)->ar[1].p);
+  a.off = extra;
+  GGNN_TRY(ggnn_plan_from_csr(ctx, rowptr, col, bc, ctx->two_e, v, nnz, &plan, a, false, st));
+  take_step_bufs(a, plan, ctx->h, &sb);
+  return run_steps(ctx, slot, plan, sb, h_state, T, precision, st);
+}
+
+size_t csr_chunk_bytes(ggnn_ctx* ctx, int64_t bc, int v, int64_t nnz, size_t extra) {
+  ggnn_plan plan;
+  ggnn_step_bufs sb;
+  ws_alloc dry(nullptr);
+  dry.off = extra;
+  ggnn_plan_from_csr(ctx, nullptr, nullptr, bc, ctx->two_e, v, nnz, &plan, dry, true, 0);
+  take_step_bufs(dry, plan, ctx->h, &sb);
+  return dry.off + 256;
+}
+
+}  // namespace
+
+extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, const void* adj,
+                                    int adj_dtype, const float* mask_or_null, int b, int v, int T,
+                                    int precision, unsigned flags, float* h_out, void* stream) {
+  (void)mask_or_null; (void)flags;
+  if (!ctx) return GGNN_E_ARG;
+  if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: bad sizes b=%d v=%d T=%d", b, v, T);
+  if (b > 0 && (!h0 || !adj || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: null pointer");
+  if (adj_dtype != GGNN_ADJ_F32 && adj_dtype != GGNN_ADJ_U8) GGNN_FAIL(ctx, GGNN_E_ARG, "bad adj_dtype %d", adj_dtype);
+  GGNN_TRY(check_ready(ctx, slot, precision));
+  if (b == 0) return GGNN_OK;
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int two_e = ctx->two_e, h = ctx->h;
+  const size_t esz = adj_dtype == GGNN_ADJ_F32 ? 4 : 1;
+  if (h_out != h0)
+    GGNN_CUDA(ctx, cudaMemcpyAsync(h_out, h0, (size_t)b * v * h * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  // chunk so that canonical rows stay well inside int32 and scratch stays bounded
+  const int64_t rows_per_graph = (int64_t)two_e * v;
+  int64_t chunk = ((int64_t)1 << 26) / rows_per_graph;
+  if (chunk < 1) chunk = 1;
+  if (chunk > b) chunk = b;
+  for (int64_t g0 = 0; g0 < b; g0 += chunk) {
+    const int64_t bc = (b - g0 < chunk) ? b - g0 : chunk;
+    const int64_t rows = bc * rows_per_graph;
+    const char* adj_c = reinterpret_cast<const char*>(adj) + (size_t)g0 * rows_per_graph * v * esz;
+    // arena 0: [rowptr][compaction tmp]
+    const size_t rp_bytes = align_up((size_t)(rows + 1) * 4, 256);
+    GGNN_TRY(arena_reserve(ctx, 0, rp_bytes + ggnn_compact_tmp_bytes(rows * v, rows), st));
+    int32_t* rowptr = reinterpret_cast<int32_t*>(ext_of(ctx)->ar[0].p);
+    char* tmp = ext_of(ctx)->ar[0].p + rp_bytes;
+    GGNN_TRY(ggnn_compact_count(ctx, adj_c, adj_dtype, rows, v, rowptr, ctx->d_mail, tmp, st));
+    int64_t nnz = 0;
+    GGNN_TRY(read_i64(ctx, ctx->d_mail, &nnz, st));     // the one planning sync
+    if (nnz >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "chunk has %lld edges", (long long)nnz);
+    // arena 1: [col][plan][step buffers]
+    const size_t col_bytes = align_up((size_t)(nnz + 1) * 4, 256);
+    GGNN_TRY(arena_reserve(ctx, 1, csr_chunk_bytes(ctx, bc, v, nnz, col_bytes), st));
+    int32_t* col = reinterpret_cast<int32_t*>(ext_of(ctx)->ar[1].p);
+    GGNN_TRY(ggnn_compact_fill(ctx, rows, v, rowptr, col, nnz, tmp, st));
+    GGNN_TRY(propagate_csr_chunk(ctx, slot, h_out + (size_t)g0 * v * h, rowptr, col, bc, v, nnz,
+                                 T, precision, col_bytes, st));
+  }
+  return GGNN_OK;
+}
+
+extern "C" int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0, const int32_t* rowptr,
+                                  const int32_t* col, int b, int v, int T, int precision,
+                                  unsigned flags, float* h_out, void* stream) {
+  (void)flags;
+  if (!ctx) return GGNN_E_ARG;
+  if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: bad sizes");
+  if (b > 0 && (!h0 || !rowptr || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: null pointer");
+  GGNN_TRY(check_ready(ctx, slot, precision));
+  if (b == 0) return GGNN_OK;
+  const int64_t rows = (int64_t)b * ctx->two_e * v;
+  if (rows >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "propagate_csr: too many rows; split the batch");
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h_out != h0)
+    GGNN_CUDA(ctx, cudaMemcpyAsync(h_out, h0, (size_t)b * v * ctx->h * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  // nnz = rowptr[rows]
+  GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->h_mail + 1, rowptr + rows, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  GGNN_CUDA(ctx, cudaStreamSynchronize(st));
+  const int64_t nnz = *reinterpret_cast<int32_t*>(ctx->h_mail + 1);
+  if (nnz < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: rowptr[last] is negative");
+  if (nnz > 0 && !col) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: null col");
+  return propagate_csr_chunk(ctx, slot, h_out, rowptr, col, b, v, nnz, T, precision, 0, st);
+}
+
+extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, const int32_t* edges,
+                                    int64_t nnz, int64_t N, int T, int precision, unsigned flags,
+                                    float* h_out, void* stream) {
+  (void)flags;
+  if (!ctx) return GGNN_E_ARG;
+  if (nnz < 0 || N < 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: bad sizes");
+  if ((N > 0 && (!h0 || !h_out)) || (nnz > 0 && !edges)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: null pointer");
+  GGNN_TRY(check_ready(ctx, slot, precision));
+  if (N == 0) return GGNN_OK;
+  if (N >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "propagate_edges: N too large for int32 node ids");
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h_out != h0)
+    GGNN_CUDA(ctx, cudaMemcpyAsync(h_out, h0, (size_t)N * ctx->h * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  ggnn_plan plan;
+  ggnn_step_bufs sb;
+  {
+    ws_alloc dry(nullptr);
+    GGNN_TRY(ggnn_plan_from_edges(ctx, edges, nnz, N, ctx->two_e, &plan, dry, true, st));
+    take_step_bufs(dry, plan, ctx->h, &sb);
+    GGNN_TRY(arena_reserve(ctx, 1, dry.off + 256, st));
+  }
+  ws_alloc a(ext_of(ctx)->ar[1].p);
+  GGNN_TRY(ggnn_plan_from_edges(ctx, edges, nnz, N, ctx->two_e, &plan, a, false, st));
+  take_step_bufs(a, plan, ctx->h, &sb);
+  int64_t bad = 0;
+  GGNN_TRY(read_i64(ctx, ctx->d_mail + 2, &bad, st));   // planning sync: edge validation result
+  if (bad) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: %lld edges have node or channel ids out of range", (long long)bad);
+  return run_steps(ctx, slot, plan, sb, h_out, T, precision, st);
+}
+
+extern "C" size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h) {
+  (void)ctx;
+  if (N < 0 || nnz < 0 || two_e <= 0 || h <= 0) return 0;
+  const int64_t tiles_edge = nnz / GGNN_TILE_M + two_e + 1;
+  const int64_t tiles_dense = (int64_t)align_up((size_t)N, GGNN_TILE_M) / GGNN_TILE_M * two_e;
+  const int64_t tiles = nnz >= N * (int64_t)two_e ? tiles_dense : tiles_edge;
+  size_t bytes = (size_t)tiles * GGNN_TILE_M * (h + 1) * 4;       // messages + msg_src
+  bytes += (size_t)N * h * 4 * 3;                                  // acts, rh, u
+  bytes += (size_t)nnz * (4 + 4 + 8) + (size_t)N * 12;             // col/tmsg/keys, tptr...
+  return bytes + ((size_t)4 << 20);
+}

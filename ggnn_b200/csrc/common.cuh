@@ -1,0 +1,132 @@
+// common.cuh -- ctx, error plumbing and small device helpers shared by the kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/ggnn_b200.h"
+
+#define GGNN_MAX_SLOTS 2
+
+// One set of edge parameters (slot) as the kernels want them.
+struct ggnn_edge_weights {
+  float* W = nullptr;      // [two_e, h, h]  FP32, reference layout (K rows, N cols)
+  float* B = nullptr;      // [two_e, h] or nullptr
+  float* Wt_tf32 = nullptr;// [two_e, hp, hp] TF32-rounded, transposed ([n][k]), zero padded to hp
+  bool   set = false;
+};
+
+struct ggnn_ctx {
+  int device = 0;
+  int sm_count = 148;
+  int two_e = 0;
+  int h = 0;
+  int hp = 0;              // h padded to the tensor-core tile granularity
+  ggnn_edge_weights edge[GGNN_MAX_SLOTS];
+  // GRU cell (shared by both slots)
+  float* Wg = nullptr;     // [2h, 2h]
+  float* bg = nullptr;     // [2h]
+  float* Wc = nullptr;     // [2h, h]
+  float* bc = nullptr;     // [h]
+  float* Wgt_tf32 = nullptr; // [2hp, 2hp] transposed + padded + TF32-rounded
+  float* Wct_tf32 = nullptr; // [hp, 2hp]
+  float* bg_pad = nullptr;   // [2hp]
+  float* bc_pad = nullptr;   // [hp]
+  bool   gru_set = false;
+  // grow-only scratch arena
+  char*  ws = nullptr;
+  size_t ws_bytes = 0;
+  // small pinned host mailbox for device->host counts
+  int64_t* h_mail = nullptr;
+  int64_t* d_mail = nullptr;
+  int64_t launches = 0;
+  char err[512] = {0};
+  // optional per-stage CUDA-event instrumentation (ggnn_profile_*)
+  bool prof_on = false;
+  struct prof_rec { int stage; cudaEvent_t a, b; };
+  std::vector<prof_rec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
+  double prof_ms[GGNN_N_STAGES] = {0};
+  int64_t prof_launches[GGNN_N_STAGES] = {0};
+};
+
+// RAII stage timer: records an event pair around the launches of one stage when profiling is on
+struct prof_scope {
+  ggnn_ctx* c; cudaStream_t st; cudaEvent_t b = nullptr; int stage; int64_t l0;
+  prof_scope(ggnn_ctx* ctx, int stage_, cudaStream_t s) : c(ctx), st(s), stage(stage_), l0(ctx->launches) {
+    if (!c->prof_on) return;
+    cudaEvent_t a;
+    auto get = [&]() { cudaEvent_t e; if (c->prof_pool.empty()) cudaEventCreate(&e); else { e = c->prof_pool.back(); c->prof_pool.pop_back(); } return e; };
+    a = get(); b = get();
+    cudaEventRecord(a, st);
+    c->prof_recs.push_back({stage, a, b});
+  }
+  ~prof_scope() {
+    if (!c->prof_on || !b) return;
+    cudaEventRecord(b, st);
+    c->prof_launches[stage] += c->launches - l0;
+  }
+};
+
+#define GGNN_FAIL(ctx, code, ...)                                   \
+  do {                                                              \
+    if (ctx) snprintf((ctx)->err, sizeof((ctx)->err), __VA_ARGS__); \
+    return (code);                                                  \
+  } while (0)
+
+#define GGNN_CUDA(ctx, expr)                                                         \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess) {                                                         \
+      GGNN_FAIL(ctx, GGNN_E_CUDA, "%s failed: %s (%s:%d)", #expr,                    \
+                cudaGetErrorString(_e), __FILE__, __LINE__);                         \
+    }                                                                                \
+  } while (0)
+
+#define GGNN_TRY(expr)            \
+  do {                            \
+    int _r = (expr);              \
+    if (_r != GGNN_OK) return _r; \
+  } while (0)
+
+// post-launch check + launch counter
+#define GGNN_LAUNCHED(ctx)                 \
+  do {                                     \
+    (ctx)->launches++;                     \
+    GGNN_CUDA(ctx, cudaGetLastError());    \
+  } while (0)
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// Bump allocator over the ctx scratch arena.  Sizes are computed first (dry run),
+// the arena is grown once, then the same sequence hands out pointers.
+struct ws_alloc {
+  char* base;
+  size_t off = 0;
+  explicit ws_alloc(char* b) : base(b) {}
+  template <typename T>
+  T* take(size_t n) {
+    off = align_up(off, 256);
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+};
+
+
+// ---- scan.cu
+int ggnn_exclusive_scan_i32(ggnn_ctx* ctx, const int32_t* in, int32_t* out, int64_t n,
+                            int64_t* total_out_dev, int32_t* tmp, size_t tmp_elems,
+                            cudaStream_t st);
+size_t ggnn_scan_tmp_elems(int64_t n);
+
+// ---- compact.cu
+size_t ggnn_compact_tmp_bytes(int64_t total_elems, int64_t rows);
+int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t rows, int v,
+                       int32_t* rowptr, int64_t* nnz_out_dev, char* tmp, cudaStream_t st);
+int ggnn_compact_fill(ggnn_ctx* ctx, int64_t rows, int v, const int32_t* rowptr, int32_t* col,
+                      int64_t col_capacity, const char* tmp, cudaStream_t st);

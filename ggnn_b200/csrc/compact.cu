@@ -1,0 +1,239 @@
+// compact.cu -- A1: dense 0/1 adjacency [b, 2E, v, v] -> canonical CSR, bit-exact with
+// np.argwhere(adj != 0) (reference edge set: chem_tensorflow_dense.py:65-83).
+//
+// Row-major order of [b][e][t][s] already IS the canonical (graph, channel, target,
+// source) order, so this is a stable stream compaction, no sort:
+//   P1  stream the dense tensor once (128-bit loads, several in flight per thread) and
+//       emit one bit per element -> bitmask (1/32 .. 1/8 of the input bytes).  HBM-bound;
+//       this is the only pass that touches the dense data.
+//   P2  per-row popcounts of the bitmask -> rowptr (as counts)
+//   P3  exclusive scan of rowptr in place (scan.cu) -> nnz
+//   P4  per-row bit iteration -> col
+#include "common.cuh"
+
+namespace {
+
+constexpr int P1_THREADS = 256;
+constexpr int P1_UNROLL = 4;
+
+__device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ldg_stream_u4(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+// 4 floats per thread -> nibble; 8 adjacent lanes -> one 32-bit word of the bitmask.
+// n4 = number of float4 groups (total elements / 4); words = n4 / 8 rounded up.
+__global__ void __launch_bounds__(P1_THREADS)
+bitmask_f32_kernel(const float4* __restrict__ adj, int64_t n4, uint32_t* __restrict__ bits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * P1_THREADS;
+  // every warp iterates the same number of times so the shuffles stay converged
+  const int64_t iters = (n4 + stride * P1_UNROLL - 1) / (stride * P1_UNROLL);
+  int64_t i0 = (int64_t)blockIdx.x * P1_THREADS + threadIdx.x;
+  for (int64_t it = 0; it < iters; ++it, i0 += stride * P1_UNROLL) {
+    float4 x[P1_UNROLL];
+#pragma unroll
+    for (int u = 0; u < P1_UNROLL; ++u) {
+      int64_t i = i0 + u * stride;
+      x[u] = i < n4 ? ldg_stream_f4(adj + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < P1_UNROLL; ++u) {
+      int64_t i = i0 + u * stride;
+      uint32_t nib = (x[u].x != 0.f ? 1u : 0u) | (x[u].y != 0.f ? 2u : 0u) |
+                     (x[u].z != 0.f ? 4u : 0u) | (x[u].w != 0.f ? 8u : 0u);
+      uint32_t w = nib << ((lane & 7) * 4);
+      w |= __shfl_xor_sync(0xffffffffu, w, 1);
+      w |= __shfl_xor_sync(0xffffffffu, w, 2);
+      w |= __shfl_xor_sync(0xffffffffu, w, 4);
+      if ((lane & 7) == 0 && i < n4) bits[i >> 3] = w;
+    }
+  }
+}
+
+// 16 bytes per thread -> 16 bits; 2 adjacent lanes -> one word.  n16 = total / 16.
+__global__ void __launch_bounds__(P1_THREADS)
+bitmask_u8_kernel(const uint4* __restrict__ adj, int64_t n16, uint32_t* __restrict__ bits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * P1_THREADS;
+  const int64_t iters = (n16 + stride * P1_UNROLL - 1) / (stride * P1_UNROLL);
+  int64_t i0 = (int64_t)blockIdx.x * P1_THREADS + threadIdx.x;
+  for (int64_t it = 0; it < iters; ++it, i0 += stride * P1_UNROLL) {
+    uint4 x[P1_UNROLL];
+#pragma unroll
+    for (int u = 0; u < P1_UNROLL; ++u) {
+      int64_t i = i0 + u * stride;
+      x[u] = i < n16 ? ldg_stream_u4(adj + i) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < P1_UNROLL; ++u) {
+      int64_t i = i0 + u * stride;
+      uint32_t wd[4] = {x[u].x, x[u].y, x[u].z, x[u].w};
+      uint32_t m = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+#pragma unroll
+        for (int by = 0; by < 4; ++by)
+          m |= ((wd[q] >> (8 * by)) & 0xffu) ? (1u << (q * 4 + by)) : 0u;
+      }
+      uint32_t w = m << ((lane & 1) * 16);
+      w |= __shfl_xor_sync(0xffffffffu, w, 1);
+      if ((lane & 1) == 0 && i < n16) bits[i >> 1] = w;
+    }
+  }
+}
+
+// scalar tail / unaligned fallback: one thread per bitmask word over [first_word, words)
+template <typename T>
+__global__ void bitmask_scalar_kernel(const T* __restrict__ adj, int64_t total,
+                                      int64_t first_word, int64_t words,
+                                      uint32_t* __restrict__ bits) {
+  int64_t w = first_word + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= words) return;
+  uint32_t m = 0;
+  for (int j = 0; j < 32; ++j) {
+    int64_t i = w * 32 + j;
+    if (i < total && adj[i] != (T)0) m |= 1u << j;
+  }
+  bits[w] = m;
+}
+
+// popcount of bits [lo, hi) of the flat bitmask
+__device__ __forceinline__ int popc_range(const uint32_t* __restrict__ bits, int64_t lo, int64_t hi) {
+  int c = 0;
+  for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
+    uint32_t m = __ldg(bits + w);
+    int64_t wb = w << 5;
+    if (lo > wb) m &= 0xffffffffu << (int)(lo - wb);
+    if (hi < wb + 32) m &= 0xffffffffu >> (int)(wb + 32 - hi);
+    c += __popc(m);
+  }
+  return c;
+}
+
+__global__ void rowcount_kernel(const uint32_t* __restrict__ bits, int64_t rows, int v,
+                                int32_t* __restrict__ rowptr) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r > rows) return;
+  if (r == rows) { rowptr[r] = 0; return; }
+  int c;
+  if (v == 128) {           // aligned fast path: 4 words per row, one 128-bit load
+    uint4 m = __ldg(reinterpret_cast<const uint4*>(bits) + r);
+    c = __popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w);
+  } else {
+    c = popc_range(bits, r * v, (r + 1) * v);
+  }
+  rowptr[r] = c;
+}
+
+__global__ void fill_kernel(const uint32_t* __restrict__ bits, int64_t rows, int v,
+                            const int32_t* __restrict__ rowptr, int32_t* __restrict__ col,
+                            int64_t cap) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  int start = rowptr[r];
+  int cnt = rowptr[r + 1] - start;
+  if (cnt == 0) return;
+  const int64_t lo = r * v, hi = lo + v;
+  int64_t pos = start;
+  for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
+    uint32_t m = __ldg(bits + w);
+    int64_t wb = w << 5;
+    if (lo > wb) m &= 0xffffffffu << (int)(lo - wb);
+    if (hi < wb + 32) m &= 0xffffffffu >> (int)(wb + 32 - hi);
+    while (m) {
+      int bpos = __ffs(m) - 1;
+      m &= m - 1;
+      if (pos < cap) col[pos] = (int32_t)(wb + bpos - lo);
+      ++pos;
+    }
+  }
+}
+
+}  // namespace
+
+// tmp layout: [bitmask words][scan tmp]
+size_t ggnn_compact_tmp_bytes(int64_t total_elems, int64_t rows) {
+  size_t words = (size_t)ceil_div64(total_elems, 32);
+  return align_up(words * 4 + 16, 256) + ggnn_scan_tmp_elems(rows + 1) * 4 + 256;
+}
+
+// P1..P3: bitmask, row counts, scan.  rowptr is final afterwards, *nnz_out_dev holds nnz.
+int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t rows, int v,
+                       int32_t* rowptr, int64_t* nnz_out_dev, char* tmp, cudaStream_t st) {
+  const int64_t total = rows * (int64_t)v;
+  const int64_t words = ceil_div64(total, 32);
+  uint32_t* bits = reinterpret_cast<uint32_t*>(tmp);
+  int32_t* scan_tmp = reinterpret_cast<int32_t*>(tmp + align_up((size_t)words * 4 + 16, 256));
+  const size_t scan_elems = ggnn_scan_tmp_elems(rows + 1);
+
+  if (total > 0) {
+    prof_scope ps(ctx, GGNN_STAGE_COMPACT_MASK, st);
+    const bool aligned = (reinterpret_cast<uintptr_t>(adj) & 15u) == 0;
+    int64_t vec_words = 0;   // words produced by the vector kernel
+    if (adj_dtype == GGNN_ADJ_F32) {
+      if (aligned) {
+        vec_words = total / 32;                       // whole words only
+        int64_t n4 = vec_words * 8;
+        if (n4 > 0) {
+          int64_t want = ceil_div64(n4, (int64_t)P1_THREADS * P1_UNROLL);
+          int grid = (int)(want < (int64_t)ctx->sm_count * 16 ? want : (int64_t)ctx->sm_count * 16);
+          bitmask_f32_kernel<<<grid, P1_THREADS, 0, st>>>(
+              reinterpret_cast<const float4*>(adj), n4, bits);
+          GGNN_LAUNCHED(ctx);
+        }
+      }
+      if (vec_words < words) {
+        int64_t n = words - vec_words;
+        bitmask_scalar_kernel<float><<<(unsigned)ceil_div64(n, 256), 256, 0, st>>>(
+            reinterpret_cast<const float*>(adj), total, vec_words, words, bits);
+        GGNN_LAUNCHED(ctx);
+      }
+    } else {
+      if (aligned) {
+        vec_words = total / 32;
+        int64_t n16 = vec_words * 2;
+        if (n16 > 0) {
+          int64_t want = ceil_div64(n16, (int64_t)P1_THREADS * P1_UNROLL);
+          int grid = (int)(want < (int64_t)ctx->sm_count * 16 ? want : (int64_t)ctx->sm_count * 16);
+          bitmask_u8_kernel<<<grid, P1_THREADS, 0, st>>>(
+              reinterpret_cast<const uint4*>(adj), n16, bits);
+          GGNN_LAUNCHED(ctx);
+        }
+      }
+      if (vec_words < words) {
+        int64_t n = words - vec_words;
+        bitmask_scalar_kernel<uint8_t><<<(unsigned)ceil_div64(n, 256), 256, 0, st>>>(
+            reinterpret_cast<const uint8_t*>(adj), total, vec_words, words, bits);
+        GGNN_LAUNCHED(ctx);
+      }
+    }
+  }
+  prof_scope ps(ctx, GGNN_STAGE_COMPACT_REST, st);
+  rowcount_kernel<<<(unsigned)ceil_div64(rows + 1, 256), 256, 0, st>>>(bits, rows, v, rowptr);
+  GGNN_LAUNCHED(ctx);
+  GGNN_TRY(ggnn_exclusive_scan_i32(ctx, rowptr, rowptr, rows + 1, nnz_out_dev, scan_tmp,
+                                   scan_elems, st));
+  return GGNN_OK;
+}
+
+// P4: needs the bitmask left in tmp by ggnn_compact_count.
+int ggnn_compact_fill(ggnn_ctx* ctx, int64_t rows, int v, const int32_t* rowptr, int32_t* col,
+                      int64_t col_capacity, const char* tmp, cudaStream_t st) {
+  const uint32_t* bits = reinterpret_cast<const uint32_t*>(tmp);
+  prof_scope ps(ctx, GGNN_STAGE_COMPACT_REST, st);
+  if (rows > 0) {
+    fill_kernel<<<(unsigned)ceil_div64(rows, 256), 256, 0, st>>>(bits, rows, v, rowptr, col,
+                                                                col_capacity);
+    GGNN_LAUNCHED(ctx);
+  }
+  return GGNN_OK;
+}

@@ -1,0 +1,13 @@
+// tf32.cuh -- tcgen05 (kind::tf32) timestep: declarations.
+#pragma once
+#include "plan.cuh"
+
+// (re)pack the weights of `slot` (and the GRU cell when with_gru) into the K-major,
+// TF32-rounded, padded layouts the tcgen05 kernels read.
+int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st);
+
+// one timestep in TF32 mode; same buffers as the FP32 step
+int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
+                   float* h_state, cudaStream_t st);
+
+bool ggnn_tf32_supported(const ggnn_ctx* ctx);

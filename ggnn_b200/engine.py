@@ -1,0 +1,230 @@
+"""Host-side mirror of the reference's propagation interface, on top of the C ABI.
+
+``Propagator`` owns one ``ggnn_ctx`` (one per device and host thread).  torch is used only
+for device memory and streams; all arithmetic happens in libggnn_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+from .weights import GGNNWeights, as_weights
+
+_PREC = {"fp32": _lib.PREC_FP32, "tf32": _lib.PREC_TF32}
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream_ptr(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class Propagator:
+    """One ctx: packed weights + scratch on one CUDA device."""
+
+    def __init__(self, weights: Union[GGNNWeights, dict, str], device: Union[int, str, torch.device, None] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ggnn_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if dev.type != "cuda":
+            raise ValueError(f"device must be a CUDA device, got {dev}")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        self._l = _lib.lib()
+        self._ctx = C.c_void_p()
+        rc = self._l.ggnn_create(C.byref(self._ctx), dev.index)
+        if rc != _lib.OK:
+            self._ctx = C.c_void_p()
+            raise RuntimeError(f"ggnn_create failed: {_lib.ERR_NAMES.get(rc, rc)} "
+                               "(needs an sm_100 device)")
+        self.weights: Optional[GGNNWeights] = None
+        self.set_weights(weights)
+
+    # -- lifetime ---------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self._l.ggnn_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int, what: str):
+        if rc == _lib.OK:
+            return
+        msg = self._l.ggnn_last_error(self._ctx)
+        msg = msg.decode() if msg else ""
+        name = _lib.ERR_NAMES.get(rc, str(rc))
+        if rc in (_lib.E_ARG, _lib.E_SHAPE):
+            raise ValueError(f"{what}: {name}: {msg}")
+        raise RuntimeError(f"{what}: {name}: {msg}")
+
+    @property
+    def launches(self) -> int:
+        return int(self._l.ggnn_launch_count(self._ctx))
+
+    def profile(self, on: bool = True):
+        """Turn the per-stage CUDA-event instrumentation on or off."""
+        self._check(self._l.ggnn_profile_enable(self._ctx, int(on)), "ggnn_profile_enable")
+
+    def profile_read(self):
+        """{stage: (milliseconds, launches)} since the last read; synchronises the device."""
+        n = len(_lib.STAGES)
+        ms = (C.c_double * n)()
+        ln = (C.c_int64 * n)()
+        self._check(self._l.ggnn_profile_read(self._ctx, ms, ln), "ggnn_profile_read")
+        return {name: (float(ms[i]), int(ln[i])) for i, name in enumerate(_lib.STAGES)}
+
+    # -- parameters -------------------------------------------------------------------
+    def set_weights(self, weights):
+        w = as_weights(weights)
+        dev = self.device
+
+        def up(a):
+            return None if a is None else torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(dev)
+
+        with torch.cuda.device(dev):
+            st = _stream_ptr(dev)
+            keep = [up(w.edge_weights), up(w.edge_biases), up(w.gru_gate_kernel), up(w.gru_gate_bias),
+                    up(w.gru_cand_kernel), up(w.gru_cand_bias)]
+            rc = self._l.ggnn_set_weights(self._ctx, _lib.SLOT_MAIN, w.two_e, w.hidden_size,
+                                          *[_ptr(t) for t in keep], st)
+            self._check(rc, "ggnn_set_weights")
+            if w.edge_weights_fixed is not None:
+                kf = [up(w.edge_weights_fixed), up(w.edge_biases_fixed)]
+                rc = self._l.ggnn_set_weights(self._ctx, _lib.SLOT_FIXED, w.two_e, w.hidden_size,
+                                              _ptr(kf[0]), _ptr(kf[1]), None, None, None, None, st)
+                self._check(rc, "ggnn_set_weights(fixed)")
+                keep += kf
+            torch.cuda.current_stream(dev).synchronize()   # staging tensors may now be freed
+        self.weights = w
+
+    # -- A1 ---------------------------------------------------------------------------
+    def compact_adjacency(self, adj: torch.Tensor, col_capacity: Optional[int] = None
+                          ) -> Tuple[torch.Tensor, torch.Tensor, int]:
+        """Dense [b, 2E, v, v] (float32 or uint8, CUDA) -> (rowptr int32 [b*2E*v+1],
+        col int32 [nnz], nnz).  Synchronises to return nnz and trim ``col``."""
+        adj, dt = self._adj(adj)
+        b, c, v, _ = adj.shape
+        rows = b * c * v
+        with torch.cuda.device(self.device):
+            rowptr = torch.empty(rows + 1, dtype=torch.int32, device=self.device)
+            nnz_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
+            if col_capacity is None:
+                # two calls: count first (capacity 0), then fill
+                rc = self._l.ggnn_compact_adjacency(self._ctx, _ptr(adj), dt, b, c, v, _ptr(rowptr),
+                                                    None, 0, _ptr(nnz_dev), _stream_ptr(self.device))
+                self._check(rc, "ggnn_compact_adjacency")
+                col_capacity = int(nnz_dev.item())
+            col = torch.empty(max(col_capacity, 1), dtype=torch.int32, device=self.device)
+            rc = self._l.ggnn_compact_adjacency(self._ctx, _ptr(adj), dt, b, c, v, _ptr(rowptr),
+                                                _ptr(col), col_capacity, _ptr(nnz_dev),
+                                                _stream_ptr(self.device))
+            self._check(rc, "ggnn_compact_adjacency")
+            nnz = int(nnz_dev.item())
+        if nnz > col_capacity:
+            raise RuntimeError(f"compact_adjacency: GGNN_E_CAPACITY: {nnz} edges > capacity {col_capacity}")
+        return rowptr, col[:nnz], nnz
+
+    # -- A2 ---------------------------------------------------------------------------
+    def _adj(self, adj: torch.Tensor):
+        if adj.dim() != 4 or adj.shape[2] != adj.shape[3]:
+            raise ValueError(f"adjacency_matrix must be [b, 2E, v, v], got {tuple(adj.shape)}")
+        if adj.dtype == torch.float32:
+            dt = _lib.ADJ_F32
+        elif adj.dtype == torch.uint8:
+            dt = _lib.ADJ_U8
+        else:
+            raise ValueError(f"adjacency_matrix must be float32 or uint8, got {adj.dtype}")
+        if adj.device != self.device:
+            raise ValueError(f"adjacency_matrix is on {adj.device}, ctx is on {self.device}")
+        return adj.contiguous(), dt
+
+    def _slot_T(self, num_timesteps, fixed_ts):
+        if fixed_ts is not None:
+            if self.weights.edge_weights_fixed is None:
+                raise ValueError("fixed_ts given but the weights hold no edge_weights_fixed")
+            return _lib.SLOT_FIXED, int(fixed_ts)
+        if num_timesteps is None:
+            num_timesteps = self.weights.params.get("num_timesteps")
+            if num_timesteps is None:
+                raise ValueError("num_timesteps not given and not in the checkpoint params")
+        return _lib.SLOT_MAIN, int(num_timesteps)
+
+    def _state(self, h0: torch.Tensor, nd: int):
+        if h0.dim() != nd or h0.shape[-1] != self.weights.hidden_size:
+            raise ValueError(f"node states must be {nd}-D with last dim {self.weights.hidden_size}, "
+                             f"got {tuple(h0.shape)}")
+        if h0.dtype != torch.float32:
+            raise ValueError(f"node states must be float32, got {h0.dtype}")
+        if h0.device != self.device:
+            raise ValueError(f"node states are on {h0.device}, ctx is on {self.device}")
+        return h0.contiguous()
+
+    def propagate_dense(self, h0: torch.Tensor, adj: torch.Tensor, num_timesteps=None, fixed_ts=None,
+                        precision: str = "fp32", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if precision not in _PREC:
+            raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
+        h0 = self._state(h0, 3)
+        adj, dt = self._adj(adj)
+        b, v, h = h0.shape
+        if adj.shape[0] != b or adj.shape[2] != v or adj.shape[1] != self.weights.two_e:
+            raise ValueError(f"adjacency {tuple(adj.shape)} does not match states {tuple(h0.shape)} "
+                             f"and 2E={self.weights.two_e}")
+        slot, T = self._slot_T(num_timesteps, fixed_ts)
+        if out is None:
+            out = torch.empty_like(h0)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_propagate_dense(self._ctx, slot, _ptr(h0), _ptr(adj), dt, None, b, v, T,
+                                              _PREC[precision], 0, _ptr(out), _stream_ptr(self.device))
+        self._check(rc, "ggnn_propagate_dense")
+        return out
+
+    def propagate_csr(self, h0, rowptr, col, num_timesteps=None, fixed_ts=None, precision="fp32", out=None):
+        if precision not in _PREC:
+            raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
+        h0 = self._state(h0, 3)
+        b, v, h = h0.shape
+        if rowptr.dtype != torch.int32 or col.dtype != torch.int32:
+            raise ValueError("rowptr and col must be int32")
+        if rowptr.numel() != b * self.weights.two_e * v + 1:
+            raise ValueError(f"rowptr has {rowptr.numel()} entries, expected b*2E*v+1 = "
+                             f"{b * self.weights.two_e * v + 1}")
+        slot, T = self._slot_T(num_timesteps, fixed_ts)
+        if out is None:
+            out = torch.empty_like(h0)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_propagate_csr(self._ctx, slot, _ptr(h0), _ptr(rowptr.contiguous()),
+                                            _ptr(col.contiguous()), b, v, T, _PREC[precision], 0,
+                                            _ptr(out), _stream_ptr(self.device))
+        self._check(rc, "ggnn_propagate_csr")
+        return out
+
+    def propagate_edges(self, h0, edges, num_timesteps=None, fixed_ts=None, precision="fp32", out=None):
+        if precision not in _PREC:
+            raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
+        h0 = self._state(h0, 2)
+        if edges.dim() != 2 or edges.shape[1] != 3 or edges.dtype != torch.int32:
+            raise ValueError(f"edges must be int32 [nnz, 3] (src, channel, dst), got "
+                             f"{edges.dtype} {tuple(edges.shape)}")
+        if edges.device != self.device:
+            raise ValueError(f"edges are on {edges.device}, ctx is on {self.device}")
+        slot, T = self._slot_T(num_timesteps, fixed_ts)
+        if out is None:
+            out = torch.empty_like(h0)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_propagate_edges(self._ctx, slot, _ptr(h0), _ptr(edges.contiguous()),
+                                              edges.shape[0], h0.shape[0], T, _PREC[precision], 0,
+                                              _ptr(out), _stream_ptr(self.device))
+        self._check(rc, "ggnn_propagate_edges")
+        return out

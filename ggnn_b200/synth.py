@@ -1,0 +1,129 @@
+"""Synthetic inputs in the reference's formats: dependency trees as
+``(head, label, word)`` triples (the ``graph`` field of the reference's JSON,
+parser/to_graph.py:36-41), their dense ``[b, 2E, v, v]`` adjacency built by the four rules of
+``graph_to_adj_mat_bd`` (chem_tensorflow_dense.py:65-83), and random multi-relational graphs
+for the edge-list path.  Pure torch so the same code runs on the host (tests) and on the
+device (bench: the 6 MB/graph dense tensors are generated in HBM, never shipped over PCIe).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+
+def zipf_probs(n: int, s: float = 1.1) -> torch.Tensor:
+    p = torch.arange(1, n + 1, dtype=torch.float64).pow(-s)
+    return (p / p.sum()).float()
+
+
+def random_trees(b: int, n_words: int, num_edge_types: int, seed: int = 0,
+                 device="cpu", lengths: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Random recursive trees.  Returns int32 [b, n_words, 3] rows (head, label, word) with
+    word = 1..n (node 0 is the artificial ROOT), label in 1..E-1 drawn Zipf(1.1); rows past a
+    graph's own length (``lengths`` [b], optional) are (-1, -1, -1)."""
+    E = num_edge_types
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    n = n_words
+    # tree over ranks 1..n: rank 1 is the root (head 0), rank r>1 attaches to a uniform earlier rank
+    u = torch.rand(b, n, generator=g)
+    ranks = torch.arange(1, n + 1).unsqueeze(0).expand(b, n)
+    head_rank = (u * (ranks - 1).clamp(min=1)).floor().long() + 1          # in [1, r-1]
+    head_rank[:, 0] = 0
+    if lengths is None:
+        lengths = torch.full((b,), n, dtype=torch.long)
+    lengths = lengths.long().clamp(1, n)
+    # random word position for every rank: a permutation of 1..len per graph (ranks > len unused)
+    keys = torch.rand(b, n, generator=g)
+    keys = torch.where(ranks <= lengths.unsqueeze(1), keys, torch.full_like(keys, 2.0))
+    perm = keys.argsort(dim=1) + 1               # perm[:, j] = rank placed at word position j+1
+    pos_of_rank = torch.empty(b, n + 1, dtype=torch.long)
+    pos_of_rank[:, 0] = 0
+    pos_of_rank.scatter_(1, perm, torch.arange(1, n + 1).unsqueeze(0).expand(b, n).contiguous())
+    word = pos_of_rank.gather(1, ranks)                      # word position of rank r
+    head = pos_of_rank.gather(1, head_rank)                  # word position of its head (0 = ROOT)
+    label = torch.multinomial(zipf_probs(E - 1), b * n, replacement=True, generator=g).view(b, n) + 1
+    tri = torch.stack([head, label, word], dim=2)
+    valid = (ranks <= lengths.unsqueeze(1)).unsqueeze(2)
+    tri = torch.where(valid, tri, torch.full_like(tri, -1))
+    # order rows by word position like the CoNLL reader does (padding rows last)
+    order = torch.where(valid.squeeze(2), word, torch.full_like(word, n + 1)).argsort(dim=1)
+    tri = tri.gather(1, order.unsqueeze(2).expand(b, n, 3))
+    return tri.to(torch.int32).to(device)
+
+
+def edges_from_triples(triples: torch.Tensor, v: int, num_edge_types: int) -> torch.Tensor:
+    """The four rules of graph_to_adj_mat_bd as an edge list: int32 [4*m, 4] rows
+    (graph, channel, target, source) for the m valid triples (not de-duplicated, unsorted)."""
+    E = num_edge_types
+    b, n, _ = triples.shape
+    t = triples.long()
+    gidx = torch.arange(b, device=t.device).view(b, 1).expand(b, n)
+    valid = t[..., 2] >= 0
+    src, lab, dst = t[..., 0][valid], t[..., 1][valid], t[..., 2][valid]
+    g = gidx[valid]
+    ch = torch.cat([lab - 1, lab - 1 + E, torch.full_like(lab, E - 1), torch.full_like(lab, 2 * E - 1)])
+    tg = torch.cat([dst, src, dst, dst - 1])
+    sc = torch.cat([src, dst, dst - 1, dst])
+    return torch.stack([g.repeat(4), ch, tg, sc], dim=1).to(torch.int32)
+
+
+def dense_adjacency(triples: torch.Tensor, v: int, num_edge_types: int,
+                    dtype=torch.float32, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[b, 2E, v, v] adjacency, A[b, e, target, source] = 1 (assignment, so duplicates are 1)."""
+    b = triples.shape[0]
+    c = 2 * num_edge_types
+    if out is None:
+        out = torch.zeros(b, c, v, v, dtype=dtype, device=triples.device)
+    else:
+        out.zero_()
+    e = edges_from_triples(triples, v, num_edge_types).long()
+    flat = ((e[:, 0] * c + e[:, 1]) * v + e[:, 2]) * v + e[:, 3]
+    out.view(-1)[flat] = 1
+    return out
+
+
+def global_edge_list(triples: torch.Tensor, v: int, num_edge_types: int) -> torch.Tensor:
+    """int32 [nnz, 3] rows (src, channel, dst) with global node ids g*v + node, de-duplicated
+    -- the input format of the edge-list path for the same graphs."""
+    e = edges_from_triples(triples, v, num_edge_types).long()
+    c = 2 * num_edge_types
+    key = ((e[:, 0] * c + e[:, 1]) * v + e[:, 2]) * v + e[:, 3]
+    key = torch.unique(key)
+    s = key % v
+    t = (key // v) % v
+    ch = (key // (v * v)) % c
+    g = key // (v * v * c)
+    return torch.stack([g * v + s, ch, g * v + t], dim=1).to(torch.int32)
+
+
+def random_multigraph(n_graphs: int, nodes: int, base_edges: int, num_types: int, seed: int = 0,
+                      device="cpu") -> torch.Tensor:
+    """C4-style graphs: per graph `base_edges` uniform random (src, dst, type) edges plus their
+    reverses on channel type + num_types.  Returns int32 [n_graphs*2*base_edges, 3]
+    (src, channel, dst) with global node ids."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    src = torch.randint(0, nodes, (n_graphs, base_edges), generator=g)
+    dst = torch.randint(0, nodes, (n_graphs, base_edges), generator=g)
+    typ = torch.randint(0, num_types, (n_graphs, base_edges), generator=g)
+    off = (torch.arange(n_graphs) * nodes).view(-1, 1)
+    fwd = torch.stack([src + off, typ, dst + off], dim=2)
+    bwd = torch.stack([dst + off, typ + num_types, src + off], dim=2)
+    return torch.cat([fwd, bwd], dim=1).view(-1, 3).to(torch.int32).to(device)
+
+
+def wsj_like_lengths(n: int, seed: int = 0, max_len: int = 140) -> torch.Tensor:
+    """Sentence lengths ~ round(lognormal(3.1, 0.45)) clipped to [2, max_len]."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    z = torch.randn(n, generator=g)
+    return torch.exp(3.1 + 0.45 * z).round().clamp(2, max_len).long()
+
+
+def bucket_size(max_node_id: int) -> int:
+    """First even bucket size in 4, 6, ..., 198 strictly greater than the largest node id
+    (chem_tensorflow_dense.py:529-532, 584-585)."""
+    for s in range(4, 200, 2):
+        if s > max_node_id:
+            return s
+    raise ValueError(f"node id {max_node_id} exceeds the reference's largest bucket (198)")

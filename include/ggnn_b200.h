@@ -1,0 +1,148 @@
+/* ggnn_b200.h -- C ABI of libggnn_b200.so (sm_100a).
+ *
+ * Drop-in boundary for ONE path of crismolav/ggnn: the GGNN propagation step
+ *   DenseGGNNChemModel.compute_final_node_representations
+ *       /root/reference/chem_tensorflow_dense.py:312-340   (driver)
+ *       /root/reference/chem_tensorflow_dense.py:391-437   (compute_timestep_fast)
+ *       /root/reference/chem_tensorflow_dense.py:350-389   (compute_timestep_normal)
+ *       /root/reference/chem_tensorflow_dense.py:237-241,333 (TF GRUCell)
+ *   and its edge-list ("sparse") form, which the reference only declares
+ *       /root/reference/chem_tensorflow.py:522-523.
+ *
+ * The reference exposes no FFI for this path (it is a Python method building TF
+ * ops); these entry points are what a ctypes binding for it would bind -- see
+ * INTEGRATION.md.  Plain pointers and sizes only; no torch / CUDA types.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer on the ctx's device unless it says "host";
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - all work is enqueued on `stream`; the calls that must learn a device-side
+ *     count to size their plan (propagate_dense / propagate_csr / propagate_edges)
+ *     synchronise `stream` once while planning and say so below; compact_adjacency
+ *     and set_weights do not synchronise;
+ *   - return 0 on success, a negative GGNN_E_* otherwise; never throws, never exits;
+ *     ggnn_last_error() gives the text for the last failure on that ctx;
+ *   - one ctx per (device, host thread); a ctx is not thread-safe; ctxs are independent;
+ *   - the caller owns every input/output buffer until the stream work has finished;
+ *     the ctx owns packed weights and scratch.
+ */
+#ifndef GGNN_B200_H
+#define GGNN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GGNN_OK              0
+#define GGNN_E_ARG          -1   /* null pointer, bad enum, negative size            */
+#define GGNN_E_SHAPE        -2   /* sizes inconsistent with the weights / each other */
+#define GGNN_E_CAPACITY     -3   /* an output buffer is too small                    */
+#define GGNN_E_CUDA         -4   /* a CUDA call failed; see ggnn_last_error          */
+#define GGNN_E_UNSUPPORTED  -5   /* valid request this build cannot serve            */
+#define GGNN_E_STATE        -6   /* weights not set, etc.                            */
+
+/* adjacency element type: the reference's placeholder is tf.float32
+ * (chem_tensorflow_dense.py:192-193); uint8 is accepted as a 4x smaller twin. */
+#define GGNN_ADJ_F32  0
+#define GGNN_ADJ_U8   1
+
+/* arithmetic mode of the message / GRU contractions */
+#define GGNN_PREC_FP32  0   /* strict: FP32 FFMA, <= 1e-5 norm-wise vs the FP64 oracle  */
+#define GGNN_PREC_TF32  1   /* tcgen05 kind::tf32, FP32 accumulate, <= 2e-3 norm-wise   */
+
+/* weight slot: 0 = edge_weights / edge_biases (chem_tensorflow_dense.py:202-206),
+ *              1 = edge_weights_fixed / edge_biases_fixed (:208-212), used when the
+ *                  reference is called with fixed_ts (:400-403, 411-412).
+ * The GRU cell is shared by both slots (:237-241). */
+#define GGNN_SLOT_MAIN   0
+#define GGNN_SLOT_FIXED  1
+
+/* flags */
+#define GGNN_FLAG_LOOP_ORDER  1u  /* reserved: summation order of compute_timestep_normal */
+
+typedef struct ggnn_ctx ggnn_ctx;
+
+/* lifetime -------------------------------------------------------------------- */
+int         ggnn_create(ggnn_ctx** out, int device);
+void        ggnn_destroy(ggnn_ctx* ctx);
+const char* ggnn_last_error(const ggnn_ctx* ctx);      /* host string, owned by ctx */
+int         ggnn_version(void);
+
+/* parameters ------------------------------------------------------------------
+ * Replaces self.weights['edge_weights'|'edge_biases'|'node_gru'] (chem_tensorflow_dense.py
+ * :202-212, 237-241).  Layouts are the reference's / TF's:
+ *   W  [two_e, h, h]  (m = h_state @ W[e]),  B [two_e, h] or NULL (use_edge_bias False)
+ *   Wg [2h, 2h] rows 0:h multiply the message, h:2h the state; cols 0:h = r, h:2h = u
+ *   bg [2h], Wc [2h, h], bc [h].
+ * The ctx copies and re-packs them; the caller's buffers are free after the stream
+ * work completes.  For slot 1 the GRU pointers may be NULL (slot 0's cell is used). */
+int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h,
+                     const float* W, const float* B_or_null,
+                     const float* Wg, const float* bg,
+                     const float* Wc, const float* bc, void* stream);
+
+/* A1: adjacency compaction -----------------------------------------------------
+ * Dense adj [b, two_e, v, v] (A[b,e,target,source] != 0 <=> edge;
+ * graph_to_adj_mat_bd, chem_tensorflow_dense.py:65-83) -> canonical CSR:
+ *   rows = (b, e, target) row-major, rowptr int32 [b*two_e*v + 1], col int32 = source,
+ * i.e. exactly np.argwhere(adj != 0) order.  *nnz_out_dev (device int64) receives nnz.
+ * If nnz > col_capacity only the first col_capacity columns are written and
+ * *nnz_out_dev still holds the true count (caller checks).  No synchronisation. */
+int ggnn_compact_adjacency(ggnn_ctx* ctx, const void* adj, int adj_dtype,
+                           int b, int two_e, int v,
+                           int32_t* rowptr, int32_t* col, int64_t col_capacity,
+                           int64_t* nnz_out_dev, void* stream);
+
+/* A2..A6: propagation ----------------------------------------------------------
+ * h0, h_out: float32 [b, v, h] (h_out may alias h0).  T = number of timesteps.
+ * Every row is updated, padded or not (the reference never reads node_mask inside
+ * the path); `mask_or_null` is accepted for signature parity.
+ * Synchronises `stream` once while planning (reads the edge count). */
+int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0,
+                         const void* adj, int adj_dtype, const float* mask_or_null,
+                         int b, int v, int T, int precision, unsigned flags,
+                         float* h_out, void* stream);
+
+int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0,
+                       const int32_t* rowptr, const int32_t* col,
+                       int b, int v, int T, int precision, unsigned flags,
+                       float* h_out, void* stream);
+
+/* Edge-list form (A9): h0/h_out float32 [N, h]; edges int32 [nnz, 3] rows
+ * (src, channel, dst), channel 0-based in [0, two_e), node ids global in [0, N).
+ * acts[dst] = sum over edges (h[src] @ W[channel] + B[channel]); messages into one
+ * node are summed in ascending (channel, src) order, edge-list order for ties. */
+int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0,
+                         const int32_t* edges, int64_t nnz, int64_t N,
+                         int T, int precision, unsigned flags,
+                         float* h_out, void* stream);
+
+/* bytes of ctx-owned scratch a propagate call of this size will hold */
+size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h);
+
+/* instrumentation: number of kernel launches this ctx has issued so far */
+int64_t ggnn_launch_count(const ggnn_ctx* ctx);
+
+/* instrumentation: per-stage device time.  With profiling on, the ctx records a CUDA event
+ * pair on the caller's stream around each stage's launches.  ggnn_profile_read synchronises
+ * the device, adds the elapsed times into ms[GGNN_N_STAGES] / launches[GGNN_N_STAGES]
+ * (either may be NULL) and resets the accumulators. */
+#define GGNN_STAGE_COMPACT_MASK  0   /* dense adjacency -> bitmask (the HBM-bound pass)   */
+#define GGNN_STAGE_COMPACT_REST  1   /* row counts, scan, column fill                      */
+#define GGNN_STAGE_PLAN          2   /* channel-major message rows + target CSR            */
+#define GGNN_STAGE_MSG           3   /* message transform  h[src] @ W_e + b_e              */
+#define GGNN_STAGE_AGG           4   /* segmented gather-sum                               */
+#define GGNN_STAGE_GRU_GATES     5   /* [x,h] @ Wg, sigmoid, r*h                           */
+#define GGNN_STAGE_GRU_CAND      6   /* [x,rh] @ Wc, tanh, state update                    */
+#define GGNN_STAGE_OTHER         7
+#define GGNN_N_STAGES            8
+int ggnn_profile_enable(ggnn_ctx* ctx, int on);
+int ggnn_profile_read(ggnn_ctx* ctx, double* ms, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGNN_B200_H */

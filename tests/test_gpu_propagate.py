@@ -1,0 +1,202 @@
+"""GPU parity: propagation (A2-A9) against the CPU oracle, through the C ABI.
+
+Tolerances (norm-wise, max|out-ref| / max|ref|, SURVEY.md F11 / BASELINE north_star):
+  strict FP32  <= 1e-5   vs the FP64 oracle
+  TF32 mode    <= 2e-3   vs the FP64 oracle
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import ggnn_b200
+from ggnn_b200 import Propagator, synth, weights as W
+from oracle import ggnn_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 1e-5, "tf32": 2e-3}
+
+
+def _weights(two_e, h, seed=0, fixed=False, bias=True):
+    w = O.make_weights(two_e, h, seed)
+    if fixed:
+        w2 = O.make_weights(two_e, h, seed + 100)
+        w["edge_weights_fixed"], w["edge_biases_fixed"] = w2["edge_weights"], w2["edge_biases"]
+    if not bias:
+        w.pop("edge_biases")
+        w.pop("edge_biases_fixed", None)
+    return w
+
+
+def _trees(b, v, E, seed, lengths=None):
+    tri = synth.random_trees(b, v - 1, E, seed=seed, lengths=lengths)
+    return tri, synth.dense_adjacency(tri, v, E).numpy()
+
+
+def _h0(b, v, h, seed=1):
+    return np.random.default_rng(seed).uniform(-0.1, 0.1, (b, v, h)).astype(np.float32)
+
+
+def _precisions(h):
+    return ["fp32", "tf32"]
+
+
+def _run_both(w, h0, adj, T, precision, **kw):
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=T,
+                                                       precision=precision, **kw)
+    ref = O.propagate_dense(h0, adj, w, T, fixed_ts=kw.get("fixed_ts"), use_bias="edge_biases" in w)
+    return out, ref
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_c1_small_dev(golden_dir, precision):
+    """BASELINE config 1: the three small_dev.conll graphs, v=6, 2E=10, h=100, T=4."""
+    d = np.load(os.path.join(golden_dir, "c1_small_dev.npz"))
+    adj = d["adj"]
+    w = _weights(10, 100, 0)
+    h0 = _h0(3, 6, 100)
+    out, ref = _run_both(w, h0, adj, 4, precision)
+    assert out.shape == (3, 6, 100) and out.dtype == np.float32
+    assert O.normwise_err(out, ref) <= TOL[precision]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+@pytest.mark.parametrize("b,v,E,h,T", [(8, 32, 10, 128, 8), (5, 16, 6, 64, 4), (3, 128, 46, 128, 8),
+                                       (20, 30, 46, 400, 4), (2, 8, 3, 32, 1), (4, 64, 12, 256, 2)])
+def test_random_trees(precision, b, v, E, h, T):
+    _, adj = _trees(b, v, E, seed=b + v)
+    w = _weights(2 * E, h, 0)
+    out, ref = _run_both(w, _h0(b, v, h), adj, T, precision)
+    assert O.normwise_err(out, ref) <= TOL[precision]
+
+
+def test_fp32_is_well_inside_tolerance_and_reproducible():
+    _, adj = _trees(8, 32, 10, seed=0)
+    w = _weights(20, 128, 0)
+    h0 = _h0(8, 32, 128)
+    out, ref = _run_both(w, h0, adj, 8, "fp32")
+    assert O.normwise_err(out, ref) <= 2e-6            # oracle's own FP32 is at ~5e-7
+    out2, _ = _run_both(w, h0, adj, 8, "fp32")
+    assert np.array_equal(out, out2)                   # no float atomics: bit-reproducible
+
+
+def test_ragged_lengths_and_padded_rows():
+    """Padded rows are GRU-updated (F8); skip_padded zeroes them; real rows are unaffected."""
+    lengths = torch.tensor([31, 2, 1, 17, 9, 30])
+    _, adj = _trees(6, 32, 8, seed=4, lengths=lengths)
+    w = _weights(16, 64, 2)
+    h0 = _h0(6, 32, 64)
+    out, ref = _run_both(w, h0, adj, 4, "fp32")
+    assert O.normwise_err(out, ref) <= 1e-5
+    assert not np.allclose(out[2, 20], h0[2, 20])      # a padded row moved
+    mask = (np.arange(32)[None, :] <= lengths.numpy()[:, None]).astype(np.float32)
+    out_m = ggnn_b200.compute_final_node_representations(h0, adj, node_mask=mask, weights=w,
+                                                         num_timesteps=4, skip_padded=True)
+    assert np.array_equal(out_m, out * mask[..., None])
+
+
+def test_fixed_ts_and_no_bias():
+    _, adj = _trees(4, 16, 5, seed=7)
+    w = _weights(10, 32, 0, fixed=True)
+    h0 = _h0(4, 16, 32)
+    out, ref = _run_both(w, h0, adj, 4, "fp32", fixed_ts=1)
+    assert O.normwise_err(out, ref) <= 1e-5
+    assert not np.allclose(out, O.propagate_dense(h0, adj, w, 1))
+    wn = _weights(10, 32, 0, bias=False)
+    out, ref = _run_both(wn, h0, adj, 3, "fp32")
+    assert O.normwise_err(out, ref) <= 1e-5
+
+
+def test_general_graphs_not_just_trees():
+    """Any 0/1 adjacency: multi-edges per (target, channel), self loops, dense channels."""
+    rng = np.random.default_rng(5)
+    b, c, v, h = 3, 6, 20, 32
+    adj = (rng.random((b, c, v, v)) < 0.15).astype(np.float32)
+    w = _weights(c, h, 1)
+    out, ref = _run_both(w, _h0(b, v, h), adj, 3, "fp32")
+    assert O.normwise_err(out, ref) <= 1e-5
+    out8 = ggnn_b200.compute_final_node_representations(_h0(b, v, h), adj.astype(np.uint8), weights=w,
+                                                        num_timesteps=3)
+    assert np.array_equal(out8, out)
+
+
+def test_edge_cases():
+    w = _weights(6, 16, 0)
+    # no edges at all: pure GRU(0, h)
+    h0 = _h0(2, 4, 16)
+    adj = np.zeros((2, 6, 4, 4), np.float32)
+    out, ref = _run_both(w, h0, adj, 2, "fp32")
+    assert O.normwise_err(out, ref) <= 1e-5
+    # T = 0 is the identity; empty batch
+    out0 = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=0)
+    assert np.array_equal(out0, h0)
+    e = ggnn_b200.compute_final_node_representations(np.zeros((0, 4, 16), np.float32),
+                                                     np.zeros((0, 6, 4, 4), np.float32), weights=w,
+                                                     num_timesteps=2)
+    assert e.shape == (0, 4, 16)
+
+
+def test_csr_edges_and_dense_paths_agree():
+    b, v, E, h, T = 6, 32, 10, 64, 4
+    tri, adj = _trees(b, v, E, seed=2)
+    w = W.from_dict(_weights(2 * E, h, 0))
+    prop = Propagator(w, "cuda:0")
+    h0 = torch.from_numpy(_h0(b, v, h)).cuda()
+    adj_d = torch.from_numpy(adj).cuda()
+    dense = prop.propagate_dense(h0, adj_d, num_timesteps=T)
+    rowptr, col, _ = prop.compact_adjacency(adj_d)
+    csr = prop.propagate_csr(h0, rowptr, col, num_timesteps=T)
+    assert torch.equal(dense, csr)
+    edges = synth.global_edge_list(tri, v, E)
+    perm = torch.randperm(edges.shape[0], generator=torch.Generator().manual_seed(0))
+    sp = prop.propagate_edges(h0.view(-1, h), edges[perm].cuda(), num_timesteps=T).view(b, v, h)
+    assert torch.equal(dense, sp)                      # same summation order -> bit-identical
+    sp2 = ggnn_b200.compute_final_node_representations_sparse(
+        h0.view(-1, h).cpu().numpy(), edges.numpy(), weights=prop, num_timesteps=T)
+    assert np.array_equal(sp2.reshape(b, v, h), dense.cpu().numpy())
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_sparse_large_graph_dense_mode(precision):
+    """C4 shape scaled down: nnz >= N*2E so every (node, channel) is transformed once."""
+    n_graphs, nodes, base, types, h, T = 2, 512, 4096, 4, 256, 8
+    edges = synth.random_multigraph(n_graphs, nodes, base, types, seed=3)
+    w = _weights(2 * types, h, 0)
+    h0 = np.random.default_rng(0).uniform(-0.1, 0.1, (n_graphs * nodes, h)).astype(np.float32)
+    out = ggnn_b200.compute_final_node_representations_sparse(h0, edges.numpy(), weights=w,
+                                                              num_timesteps=T, precision=precision)
+    ref = O.propagate_edges(h0, edges.numpy(), w, T)
+    assert O.normwise_err(out, ref) <= TOL[precision]
+
+
+def test_errors():
+    w = _weights(6, 16, 0)
+    h0 = _h0(2, 4, 16)
+    adj = np.zeros((2, 6, 4, 4), np.float32)
+    with pytest.raises(ValueError):
+        ggnn_b200.compute_final_node_representations(h0[..., :8], adj, weights=w, num_timesteps=1)
+    with pytest.raises(ValueError):
+        ggnn_b200.compute_final_node_representations(h0, adj[:, :4], weights=w, num_timesteps=1)
+    with pytest.raises(ValueError):
+        ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=1, precision="fp8")
+    with pytest.raises(ValueError):
+        ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=1, fixed_ts=1)
+    with pytest.raises(ValueError):
+        ggnn_b200.compute_final_node_representations(h0, adj, weights=w)           # no T anywhere
+    bad = np.array([[0, 0, 1], [0, 99, 1]], np.int32)
+    with pytest.raises(ValueError, match="out of range"):
+        ggnn_b200.compute_final_node_representations_sparse(h0.reshape(-1, 16), bad, weights=w, num_timesteps=1)
+
+
+def test_reference_checkpoint_file(tmp_path):
+    """Weights come in through the reference's .pickle; T defaults to its params."""
+    w = W.from_dict(_weights(10, 32, 0, fixed=True))
+    path = str(tmp_path / "m.pickle")
+    W.save_checkpoint(path, w, {"num_timesteps": 3})
+    _, adj = _trees(3, 8, 5, seed=1)
+    h0 = _h0(3, 8, 32)
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=path)
+    ref = O.propagate_dense(h0, adj, _weights(10, 32, 0, fixed=True), 3)
+    assert O.normwise_err(out, ref) <= 1e-5

@@ -1,0 +1,134 @@
+"""CPU tests: the oracle against the golden vectors made by the reference's own NumPy helpers
+(scripts/make_golden.py), and its internal consistency (dense == loop == edge-list)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ggnn_oracle as O
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_c1_adjacency_matches_reference(golden_dir):
+    d = _load(golden_dir, "c1_small_dev.npz")
+    E, v = int(d["E"]), int(d["v"])
+    assert (E, v) == (5, 6)
+    for i in range(3):
+        tri = d[f"triples_{i}"].tolist()
+        ours = O.graph_to_adj_mat_bd(tri, v, E)
+        assert np.array_equal(ours, d["adj"][i].astype(np.float64))
+        # edge list straight from the triples == argwhere of the reference's dense matrix
+        ref_edges = d["edges_bets"][d["edges_bets"][:, 0] == i][:, 1:]
+        assert np.array_equal(O.edges_from_triples(tri, E), ref_edges)
+    nnz = [(d["adj"][i] != 0).sum() for i in range(3)]
+    assert nnz == [16, 20, 20]                      # 4n non-zeros
+    # graph 0, spelled out in SURVEY.md 8(a) A1
+    g0 = d["edges_bets"][d["edges_bets"][:, 0] == 0][:, 1:].tolist()
+    assert g0[:4] == [[0, 3, 0], [2, 1, 2], [2, 4, 3], [3, 2, 3]]
+
+
+def test_random_trees_match_reference_adjacency(golden_dir):
+    d = _load(golden_dir, "random_trees_ref_adj.npz")
+    ci = 0
+    while f"case{ci}_shape" in d:
+        b, c, v = d[f"case{ci}_shape"].tolist()
+        E = c // 2
+        adj = np.zeros((b, c, v, v), np.float32)
+        for g in range(b):
+            tri = [t for t in d[f"case{ci}_triples"][g].tolist() if t[2] >= 0]
+            adj[g] = O.graph_to_adj_mat_bd(tri, v, E)
+        assert np.array_equal(np.argwhere(adj != 0).astype(np.int32), d[f"case{ci}_edges_bets"])
+        rowptr, col = O.compact_adjacency(adj)
+        e4 = O.csr_to_edges(rowptr, col, b, c, v)
+        assert np.array_equal(e4, d[f"case{ci}_edges_bets"])
+        ci += 1
+    assert ci == 5
+
+
+def test_conventions_pinned_by_reference_tests(golden_dir):
+    d = _load(golden_dir, "conventions.npz")
+    # tests_chem.py:29-48: amat[e-1, dest, src] = 1
+    a = np.zeros((2, 4, 4))
+    for (src, e, dest) in d["graph"].tolist():
+        a[e - 1, dest, src] = 1
+    assert np.array_equal(a, d["adj_dir"])
+    assert d["decoded"].tolist() == [[3, 1], [3, 1], [0, 2]]      # tests_chem.py:9-27
+
+
+def _random_batch(rng, b, v, E):
+    adjs = []
+    for _ in range(b):
+        n = v - 1
+        tri = []
+        for w in range(1, n + 1):
+            head = 0 if w == 1 else int(rng.integers(1, w))
+            tri.append([head, int(rng.integers(1, E)), w])
+        adjs.append(O.graph_to_adj_mat_bd(tri, v, E))
+    return np.stack(adjs).astype(np.float32)
+
+
+def test_forms_agree_and_probe_numbers():
+    """FP64 dense == FP64 edge-list to ~1e-15; FP32 within ~5e-7 of FP64."""
+    rng = np.random.default_rng(0)
+    b, v, E, h, T = 8, 32, 10, 128, 8
+    adj = _random_batch(rng, b, v, E)
+    w = O.make_weights(2 * E, h, 0)
+    h0 = rng.uniform(-0.1, 0.1, (b, v, h)).astype(np.float32)
+    r64 = O.propagate_dense(h0, adj, w, T, dtype=np.float64)
+    edges = O.dense_to_edges(adj)
+    e64 = O.propagate_edges(h0.reshape(-1, h), edges, w, T, dtype=np.float64).reshape(b, v, h)
+    l64 = O.propagate_dense(h0, adj, w, T, dtype=np.float64, form="loop")
+    assert O.normwise_err(e64, r64) < 1e-13
+    assert O.normwise_err(l64, r64) < 1e-13
+    r32 = O.propagate_dense(h0, adj, w, T, dtype=np.float32)
+    e32 = O.propagate_edges(h0.reshape(-1, h), edges, w, T, dtype=np.float32).reshape(b, v, h)
+    assert O.normwise_err(r32, r64) < 2e-6
+    assert O.normwise_err(e32, r64) < 2e-6
+    assert 0.3 < np.abs(r64).max() < 1.0
+
+
+def test_bias_counted_per_edge_and_isolated_nodes_get_zero():
+    """F9: acts[t] = sum over edges (h[s] W_e + b_e); a node without in-edges gets exactly 0."""
+    E, v, h = 3, 6, 8
+    tri = [[0, 1, 1], [1, 2, 2], [1, 2, 3]]        # nodes 4, 5 are padding
+    adj = O.graph_to_adj_mat_bd(tri, v, E)[None].astype(np.float32)
+    w = O.make_weights(2 * E, h, 1)
+    hh = np.random.default_rng(2).standard_normal((v, h))
+    acts = O.timestep_fast(hh, adj, w, True, np.float64)
+    assert np.all(acts[4] == 0) and np.all(acts[5] == 0)
+    # node 1: in-edges: head 0 (ch 0), children 2, 3 (ch 1+E each), prev 0 (ch E-1), next 2 (ch 2E-1)
+    W, B = w["edge_weights"].astype(np.float64), w["edge_biases"].astype(np.float64)
+    want = (hh[0] @ W[0] + B[0, 0]) + (hh[2] @ W[1 + E] + B[1 + E, 0]) + (hh[3] @ W[1 + E] + B[1 + E, 0]) \
+        + (hh[0] @ W[E - 1] + B[E - 1, 0]) + (hh[2] @ W[2 * E - 1] + B[2 * E - 1, 0])
+    assert np.allclose(acts[1], want, rtol=1e-12, atol=1e-12)
+
+
+def test_fixed_ts_uses_fixed_weights():
+    rng = np.random.default_rng(5)
+    E, v, h = 4, 8, 16
+    adj = _random_batch(rng, 2, v, E)
+    w = O.make_weights(2 * E, h, 0)
+    w2 = O.make_weights(2 * E, h, 9)
+    w["edge_weights_fixed"], w["edge_biases_fixed"] = w2["edge_weights"], w2["edge_biases"]
+    h0 = rng.uniform(-0.1, 0.1, (2, v, h)).astype(np.float32)
+    a = O.propagate_dense(h0, adj, w, 4, fixed_ts=1)
+    wf = dict(w, edge_weights=w2["edge_weights"], edge_biases=w2["edge_biases"])
+    bb = O.propagate_dense(h0, adj, wf, 1)
+    assert np.array_equal(a, bb)
+    assert not np.allclose(a, O.propagate_dense(h0, adj, w, 1))
+
+
+def test_padded_rows_are_updated():
+    """F8: node_mask is never read inside the path; padded rows go through GRU(0, h)."""
+    E, v, h = 3, 6, 8
+    tri = [[0, 1, 1], [1, 2, 2]]
+    adj = O.graph_to_adj_mat_bd(tri, v, E)[None].astype(np.float32)
+    w = O.make_weights(2 * E, h, 3)
+    h0 = np.random.default_rng(0).uniform(-0.5, 0.5, (1, v, h)).astype(np.float32)
+    out = O.propagate_dense(h0, adj, w, 2)
+    assert not np.allclose(out[0, 5], h0[0, 5])
+    want = O.gru_cell(np.zeros((1, h)), O.gru_cell(np.zeros((1, h)), h0[0, 5:6].astype(np.float64), w, np.float64), w, np.float64)
+    assert np.allclose(out[0, 5], want[0], atol=1e-12)
