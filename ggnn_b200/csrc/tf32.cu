@@ -1,8 +1,356 @@
-// tf32.cu -- tcgen05 (kind::tf32) timestep.  (placeholder until the kernels land)
+// tf32.cu -- GGNN_PREC_TF32 timestep: the three contractions of a timestep on the 5th-gen
+// tensor cores (tcgen05.mma kind::tf32, FP32 accumulators in TMEM).
+//
+//   MSG    M[r,:]  = tf32(h[msg_src[r],:]) @ tf32(W[type]) + B[type]
+//   GATES  g = sigmoid([tf32(acts), tf32(h)] @ tf32(Wg) + bg);  rh = g[:, :h]*h;  u = g[:, h:]
+//   CAND   c = tanh([tf32(acts), tf32(rh)] @ tf32(Wc) + bc);    h' = u*h + (1-u)*c
+//
+// One CTA = one 128-row x (<=128)-column output tile.  Warp roles:
+//   warps 0-3  operand producers (global -> registers -> cvt.rna.tf32 -> 128B-swizzled smem),
+//              then the epilogue (tcgen05.ld, fused bias / sigmoid / tanh / state update)
+//   warp  4    one elected lane issues tcgen05.mma and commits to the mbarriers
+// Operands are K-major; weights are pre-transposed, TF32-rounded and zero-padded to hp
+// (a multiple of 32) once in ggnn_set_weights, so the mainloop needs no K/N edge cases.
 #include "tf32.cuh"
+#include "tc.cuh"
 
-int ggnn_tf32_pack_weights(ggnn_ctx*, int, bool, cudaStream_t) { return GGNN_OK; }
-bool ggnn_tf32_supported(const ggnn_ctx*) { return false; }
-int ggnn_step_tf32(ggnn_ctx* ctx, int, const ggnn_plan&, const ggnn_step_bufs&, float*, cudaStream_t) {
-  GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "TF32 path not built yet");
+namespace {
+
+constexpr int BM = 128;           // rows per tile  (UMMA M, one TMEM lane per row)
+constexpr int BN = 128;           // max columns per tile (UMMA N, TMEM columns)
+constexpr int BKF = 32;           // floats per K chunk = one 128-byte swizzle row
+constexpr int STAGES = 3;
+constexpr int A_BYTES = BM * BKF * 4;     // 16 KB
+constexpr int B_BYTES = BN * BKF * 4;     // 16 KB
+constexpr int NPROD = 128;                // producer / epilogue threads (warps 0-3)
+constexpr int NTHREADS = NPROD + 32;      // + MMA warp
+constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
+
+enum { MODE_MSG = 0, MODE_GATES = 1, MODE_CAND = 2 };
+
+struct tparams {
+  const float* A1;          // [*, h]  K segment 1 source rows
+  const float* A2;          // [*, h]  K segment 2 source rows (GATES: h, CAND: rh) or null
+  const int32_t* gather;    // MSG: source row per message row (-1 = padding)
+  const float* Bt;          // [Np, Kp] transposed, TF32-rounded, padded weights (per type for MSG)
+  const float* bias;        // [Np] padded bias (per type: [h] unpadded for MSG) or null
+  int h, hp;                // real / padded hidden size
+  int Kp;                   // padded K = hp * (segments)
+  int Np;                   // padded N
+  int64_t M;
+  const int32_t* tile_type;
+  const int32_t* n_tiles;
+  float* out0;              // MSG: msg;  GATES: rh;  CAND: h state (in/out)
+  float* out1;              // GATES: u
+  const float* hstate;      // GATES: h
+  const float* ubuf;        // CAND: u
+};
+
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_f(float x) {
+  // tanh(x) = 1 - 2/(exp(2x)+1); __expf relative error ~2^-21, far below the TF32 noise floor
+  float e = __expf(2.0f * x);
+  return 1.0f - 2.0f / (e + 1.0f);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(NTHREADS)
+gemm_tf32_kernel(const tparams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t row0 = (int64_t)blockIdx.y * BM;
+  const int n0 = blockIdx.x * BN;
+  const int n_tile = min(BN, p.Np - n0);              // multiple of 32
+
+  const float* Bt = p.Bt;
+  const float* bias = p.bias;
+  if (MODE == MODE_MSG) {
+    if ((int)blockIdx.y >= *p.n_tiles) return;        // uniform across the CTA
+    const int type = p.tile_type[blockIdx.y];
+    Bt += (size_t)type * p.Np * p.Kp;
+    if (bias) bias += (size_t)type * p.h;
+  }
+
+  // ---- shared memory carve-up (1024-byte aligned operand tiles)
+  const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA = base, sB = base + STAGES * A_BYTES;
+  const uint32_t bars = sB + STAGES * B_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+  const uint32_t accum_bar = bars + 8u * (2 * STAGES);
+  const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 1);
+  uint8_t* smem_al = smem_raw + (base - tc::smem_u32(smem_raw));
+
+  if (warp == 4 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      tc::mbar_init(full_bar(s), NPROD);
+      tc::mbar_init(empty_bar(s), 1);
+    }
+    tc::mbar_init(accum_bar, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 0) tc::tmem_alloc(tmem_slot, BN);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
+
+  const int KC = p.Kp / BKF;                          // K chunks
+  const int KC1 = p.hp / BKF;                         // chunks of segment 1
+
+  if (warp < 4) {
+    // ================= producers =================
+    const int c16 = tid & 7;                          // 16-byte chunk within the 128-byte row
+    const int rbase = tid >> 3;                       // rows rbase + 16*j, j = 0..7
+    int64_t src1[8], src2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int64_t grow = row0 + rbase + 16 * j;
+      src1[j] = -1; src2[j] = -1;
+      if (grow < p.M) {
+        if (MODE == MODE_MSG) src1[j] = p.gather[grow];
+        else { src1[j] = grow; src2[j] = grow; }
+      }
+    }
+    for (int kc = 0; kc < KC; ++kc) {
+      const int s = kc % STAGES;
+      if (kc >= STAGES) tc::mbar_wait(empty_bar(s), ((kc / STAGES) - 1) & 1);
+      const bool seg2 = kc >= KC1;
+      const float* Asrc = seg2 ? p.A2 : p.A1;
+      const int kloc = (seg2 ? kc - KC1 : kc) * BKF + c16 * 4;     // column within the segment
+      const bool kin = kloc < p.h;                                 // h % 4 == 0
+      float4 va[8], vb[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int64_t r = seg2 ? src2[j] : src1[j];
+        va[j] = (kin && r >= 0) ? *reinterpret_cast<const float4*>(Asrc + r * p.h + kloc)
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int n = rbase + 16 * j;
+        vb[j] = n < n_tile ? __ldg(reinterpret_cast<const float4*>(Bt + (size_t)(n0 + n) * p.Kp + kc * BKF + c16 * 4))
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      uint8_t* a_st = smem_al + (sA - base) + s * A_BYTES;
+      uint8_t* b_st = smem_al + (sB - base) + s * B_BYTES;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int r = rbase + 16 * j;
+        const int off = (r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4);
+        float4 t = va[j];
+        t.x = tc::to_tf32(t.x); t.y = tc::to_tf32(t.y); t.z = tc::to_tf32(t.z); t.w = tc::to_tf32(t.w);
+        *reinterpret_cast<float4*>(a_st + off) = t;
+        *reinterpret_cast<float4*>(b_st + off) = vb[j];
+      }
+      tc::fence_proxy_async();
+      tc::mbar_arrive(full_bar(s));
+    }
+
+    // ================= epilogue =================
+    tc::mbar_wait(accum_bar, 0);
+    tc::fence_after_sync();
+    const int64_t row = row0 + warp * 32 + lane;
+    bool row_ok = row < p.M;
+    if (MODE == MODE_MSG && row_ok) row_ok = p.gather[row] >= 0;
+    for (int cc = 0; cc < n_tile / 32; ++cc) {
+      uint32_t acc[32];
+      tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cc * 32), acc);
+      tc::tmem_ld_wait();
+      const int n = n0 + cc * 32;                      // padded column index of acc[0]
+      if (!row_ok) {
+        // nothing to store for this row (keep the warp converged for the next tcgen05.ld)
+      } else if (MODE == MODE_MSG || MODE == MODE_CAND) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int col = n + q * 4;
+          if (col >= p.h) break;
+          float v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(acc[q * 4 + i]);
+          if (bias) {
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + col));
+            v[0] += bb.x; v[1] += bb.y; v[2] += bb.z; v[3] += bb.w;
+          }
+          if (MODE == MODE_MSG) {
+            *reinterpret_cast<float4*>(p.out0 + row * p.h + col) = make_float4(v[0], v[1], v[2], v[3]);
+          } else {
+            const float4 hv = *reinterpret_cast<const float4*>(p.out0 + row * p.h + col);
+            const float4 uv = *reinterpret_cast<const float4*>(p.ubuf + row * p.h + col);
+            float4 o;
+            o.x = uv.x * hv.x + (1.0f - uv.x) * tanh_f(v[0]);
+            o.y = uv.y * hv.y + (1.0f - uv.y) * tanh_f(v[1]);
+            o.z = uv.z * hv.z + (1.0f - uv.z) * tanh_f(v[2]);
+            o.w = uv.w * hv.w + (1.0f - uv.w) * tanh_f(v[3]);
+            *reinterpret_cast<float4*>(p.out0 + row * p.h + col) = o;
+          }
+        }
+      } else {  // GATES: padded columns [0,hp) = r, [hp,2hp) = u
+        const bool is_r = n < p.hp;
+        const int cbase = is_r ? n : n - p.hp;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int col = cbase + q * 4;
+          if (col >= p.h) break;
+          const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + n + q * 4));
+          float g[4];
+          g[0] = sigmoid_f(__uint_as_float(acc[q * 4 + 0]) + bb.x);
+          g[1] = sigmoid_f(__uint_as_float(acc[q * 4 + 1]) + bb.y);
+          g[2] = sigmoid_f(__uint_as_float(acc[q * 4 + 2]) + bb.z);
+          g[3] = sigmoid_f(__uint_as_float(acc[q * 4 + 3]) + bb.w);
+          if (is_r) {
+            const float4 hv = *reinterpret_cast<const float4*>(p.hstate + row * p.h + col);
+            *reinterpret_cast<float4*>(p.out0 + row * p.h + col) =
+                make_float4(g[0] * hv.x, g[1] * hv.y, g[2] * hv.z, g[3] * hv.w);
+          } else {
+            *reinterpret_cast<float4*>(p.out1 + row * p.h + col) = make_float4(g[0], g[1], g[2], g[3]);
+          }
+        }
+      }
+    }
+  } else {
+    // ================= MMA issuer (warp 4, one lane) =================
+    if (lane == 0) {
+      const uint32_t idesc = tc::umma_idesc(/*TF32*/ 2, BM, n_tile);
+      for (int kc = 0; kc < KC; ++kc) {
+        const int s = kc % STAGES;
+        tc::mbar_wait(full_bar(s), (kc / STAGES) & 1);
+        tc::fence_after_sync();
+        const uint32_t a0 = sA + s * A_BYTES, b0 = sB + s * B_BYTES;
+#pragma unroll
+        for (int k = 0; k < BKF / 8; ++k) {           // UMMA K = 8 for TF32 (32 bytes)
+          tc::umma_tf32(tmem_base, tc::umma_desc_sw128(a0 + k * 32), tc::umma_desc_sw128(b0 + k * 32),
+                        idesc, (kc | k) != 0);
+        }
+        tc::umma_commit(empty_bar(s));                // frees the smem stage when the MMAs retire
+      }
+      tc::umma_commit(accum_bar);                     // accumulator complete -> epilogue
+    }
+    __syncwarp();
+  }
+
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem_base, BN);
+}
+
+// ---- weight packing -------------------------------------------------------------------
+// dst[e][n][k] (n, k < hp) = tf32(src[e][k][n]) for k, n < h, else 0
+__global__ void pack_edge_kernel(const float* __restrict__ W, float* __restrict__ Wt, int two_e,
+                                 int h, int hp) {
+  const int64_t total = (int64_t)two_e * hp * hp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % hp), n = (int)((i / hp) % hp);
+    const int64_t e = i / ((int64_t)hp * hp);
+    Wt[i] = (k < h && n < h) ? tc::to_tf32(W[(e * h + k) * h + n]) : 0.f;
+  }
+}
+
+// GRU kernels: src [2h, ncols*h] (rows: x part then h part; column blocks of width h)
+// dst [ncols*hp, 2hp]: dst[nb*hp + n][kb*hp + k] = tf32(src[kb*h + k][nb*h + n])
+__global__ void pack_gru_kernel(const float* __restrict__ src, float* __restrict__ dst, int ncols,
+                                int h, int hp) {
+  const int Kp = 2 * hp, Np = ncols * hp;
+  const int64_t total = (int64_t)Np * Kp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % Kp), nn = (int)(i / Kp);
+    const int kb = kk / hp, k = kk % hp, nb = nn / hp, n = nn % hp;
+    dst[i] = (k < h && n < h) ? tc::to_tf32(src[(size_t)(kb * h + k) * (ncols * h) + nb * h + n]) : 0.f;
+  }
+}
+
+__global__ void pack_bias_kernel(const float* __restrict__ src, float* __restrict__ dst, int nblocks,
+                                 int h, int hp) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nblocks * hp) return;
+  const int nb = i / hp, n = i % hp;
+  dst[i] = n < h ? src[nb * h + n] : 0.f;
+}
+
+int realloc_f(ggnn_ctx* ctx, float*& p, size_t n) {
+  if (p) { cudaFree(p); p = nullptr; }
+  GGNN_CUDA(ctx, cudaMalloc(&p, n * sizeof(float)));
+  return GGNN_OK;
+}
+
+template <int MODE>
+int launch(ggnn_ctx* ctx, const tparams& p, unsigned mtiles, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    GGNN_CUDA(ctx, cudaFuncSetAttribute(gemm_tf32_kernel<MODE>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr_set = true;
+  }
+  dim3 grid((p.Np + BN - 1) / BN, mtiles);
+  gemm_tf32_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(p);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+}  // namespace
+
+bool ggnn_tf32_supported(const ggnn_ctx* ctx) { return ctx->h % 4 == 0 && ctx->hp >= 32; }
+
+int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st) {
+  const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  GGNN_TRY(realloc_f(ctx, ew.Wt_tf32, (size_t)two_e * hp * hp));
+  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32, two_e, h, hp);
+  GGNN_LAUNCHED(ctx);
+  if (with_gru) {
+    GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32, (size_t)4 * hp * hp));
+    GGNN_TRY(realloc_f(ctx, ctx->Wct_tf32, (size_t)2 * hp * hp));
+    GGNN_TRY(realloc_f(ctx, ctx->bg_pad, (size_t)2 * hp));
+    GGNN_TRY(realloc_f(ctx, ctx->bc_pad, (size_t)hp));
+    pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, ctx->Wgt_tf32, 2, h, hp);
+    GGNN_LAUNCHED(ctx);
+    pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, ctx->Wct_tf32, 1, h, hp);
+    GGNN_LAUNCHED(ctx);
+    pack_bias_kernel<<<(2 * hp + 255) / 256, 256, 0, st>>>(ctx->bg, ctx->bg_pad, 2, h, hp);
+    GGNN_LAUNCHED(ctx);
+    pack_bias_kernel<<<(hp + 255) / 256, 256, 0, st>>>(ctx->bc, ctx->bc_pad, 1, h, hp);
+    GGNN_LAUNCHED(ctx);
+  }
+  return GGNN_OK;
+}
+
+int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
+                   float* h_state, cudaStream_t st) {
+  const int h = ctx->h, hp = ctx->hp;
+  const ggnn_edge_weights& ew = ctx->edge[slot];
+  if (plan.N == 0) return GGNN_OK;
+  if (plan.max_tiles > 0 && plan.nnz > 0) {
+    prof_scope ps(ctx, GGNN_STAGE_MSG, st);
+    tparams p{};
+    p.A1 = h_state; p.gather = plan.msg_src;
+    p.Bt = ew.Wt_tf32; p.bias = ew.B;
+    p.h = h; p.hp = hp; p.Kp = hp; p.Np = hp;
+    p.M = plan.max_tiles * GGNN_TILE_M;
+    p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
+    p.out0 = bufs.msg;
+    GGNN_TRY(launch<MODE_MSG>(ctx, p, (unsigned)plan.max_tiles, st));
+  }
+  GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, st));
+  const unsigned mt = (unsigned)ceil_div64(plan.N, BM);
+  {
+    prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+    tparams p{};
+    p.A1 = bufs.acts; p.A2 = h_state;
+    p.Bt = ctx->Wgt_tf32; p.bias = ctx->bg_pad;
+    p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = 2 * hp; p.M = plan.N;
+    p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state;
+    GGNN_TRY(launch<MODE_GATES>(ctx, p, mt, st));
+  }
+  {
+    prof_scope ps(ctx, GGNN_STAGE_GRU_CAND, st);
+    tparams p{};
+    p.A1 = bufs.acts; p.A2 = bufs.rh;
+    p.Bt = ctx->Wct_tf32; p.bias = ctx->bc;
+    p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = hp; p.M = plan.N;
+    p.out0 = h_state; p.ubuf = bufs.u;
+    GGNN_TRY(launch<MODE_CAND>(ctx, p, mt, st));
+  }
+  return GGNN_OK;
 }
