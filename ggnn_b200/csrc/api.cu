@@ -223,8 +223,10 @@ void take_step_bufs(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_step_bufs* s
 
 int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& sb,
               float* h_state, int T, int precision, cudaStream_t st) {
+  if (precision == GGNN_PREC_TF32 && T > 0)   // state is kept TF32-rounded between steps
+    GGNN_TRY(ggnn_tf32_round_copy(ctx, h_state, h_state, plan.N * ctx->h, st));
   for (int t = 0; t < T; ++t) {
-    if (precision == GGNN_PREC_TF32) GGNN_TRY(ggnn_step_tf32(ctx, slot, plan, sb, h_state, st));
+    if (precision == GGNN_PREC_TF32) GGNN_TRY(ggnn_step_tf32(ctx, slot, plan, sb, h_state, t == T - 1, st));
     else GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, sb, h_state, st));
   }
   return GGNN_OK;

@@ -1,6 +1,7 @@
 // common.cuh -- ctx, error plumbing and small device helpers shared by the kernels.
 #pragma once
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -16,6 +17,8 @@ struct ggnn_edge_weights {
   float* W = nullptr;      // [two_e, h, h]  FP32, reference layout (K rows, N cols)
   float* B = nullptr;      // [two_e, h] or nullptr
   float* Wt_tf32 = nullptr;// [two_e, hp, hp] TF32-rounded, transposed ([n][k]), zero padded to hp
+  CUtensorMap tm_Wt;       // TMA view of Wt_tf32 as [two_e*hp rows, hp cols], box 32 x tm_rows
+  int    tm_rows = 0;
   bool   set = false;
 };
 
@@ -33,6 +36,8 @@ struct ggnn_ctx {
   float* bc = nullptr;     // [h]
   float* Wgt_tf32 = nullptr; // [2hp, 2hp] transposed + padded + TF32-rounded
   float* Wct_tf32 = nullptr; // [hp, 2hp]
+  CUtensorMap tm_Wg, tm_Wc;  // TMA views of the packed GRU kernels
+  int    tm_rows_g = 0, tm_rows_c = 0;
   float* bg_pad = nullptr;   // [2hp]
   float* bc_pad = nullptr;   // [hp]
   bool   gru_set = false;

@@ -36,4 +36,4 @@ struct ggnn_step_bufs {
 int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
                    float* h_state, cudaStream_t st);
 int ggnn_aggregate(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* acts, int h,
-                   cudaStream_t st);
+                   bool round_tf32, cudaStream_t st);

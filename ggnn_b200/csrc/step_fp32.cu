@@ -7,6 +7,7 @@
 //   GATES  g = sigmoid([acts, h] @ Wg + bg); rh = g[:, :h] * h; u = g[:, h:]     (TF GRUCell)
 //   CAND   c = tanh([acts, rh] @ Wc + bc);  h' = u*h + (1-u)*c
 #include "plan.cuh"
+#include "tc.cuh"
 
 namespace {
 
@@ -183,7 +184,8 @@ sgemm_kernel(const sgemm_params p) {
 // so the result is bit-reproducible.
 __global__ void __launch_bounds__(256)
 aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg,
-                 const float* __restrict__ msg, float* __restrict__ acts, int64_t N, int h) {
+                 const float* __restrict__ msg, float* __restrict__ acts, int64_t N, int h,
+                 int round_tf32) {
   const int lane = threadIdx.x & 31;
   const int64_t node = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (node >= N) return;
@@ -208,6 +210,10 @@ aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ t
       float4 m0 = __ldg(reinterpret_cast<const float4*>(msg + (size_t)r0 * h) + c);
       acc.x += m0.x; acc.y += m0.y; acc.z += m0.z; acc.w += m0.w;
     }
+    if (round_tf32) {   // acts only feeds tensor-core operands in TF32 mode: round once, here
+      acc.x = tc::to_tf32(acc.x); acc.y = tc::to_tf32(acc.y);
+      acc.z = tc::to_tf32(acc.z); acc.w = tc::to_tf32(acc.w);
+    }
     reinterpret_cast<float4*>(acts + (size_t)node * h)[c] = acc;
   }
 }
@@ -215,12 +221,12 @@ aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ t
 }  // namespace
 
 int ggnn_aggregate(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* acts, int h,
-                   cudaStream_t st) {
+                   bool round_tf32, cudaStream_t st) {
   if (plan.N == 0) return GGNN_OK;
   prof_scope ps(ctx, GGNN_STAGE_AGG, st);
   const int64_t threads = plan.N * 32;
   aggregate_kernel<<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(plan.tptr, plan.tmsg, msg,
-                                                                      acts, plan.N, h);
+                                                                      acts, plan.N, h, round_tf32 ? 1 : 0);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
@@ -244,7 +250,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     sgemm_kernel<MODE_MSG><<<grid, NT, 0, st>>>(p);
     GGNN_LAUNCHED(ctx);
   }
-  GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, st));
+  GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, false, st));
   const unsigned mt = (unsigned)ceil_div64(plan.N, BM);
   {  // GATES
     prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);

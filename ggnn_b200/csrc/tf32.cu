@@ -6,7 +6,8 @@
 //   CAND   c = tanh([tf32(acts), tf32(rh)] @ tf32(Wc) + bc);    h' = u*h + (1-u)*c
 //
 // One CTA = one 128-row x (<=128)-column output tile.  Warp roles:
-//   warps 0-3  operand producers (global -> registers -> cvt.rna.tf32 -> 128B-swizzled smem),
+//   warps 0-3  operand producers: activations by 16-byte cp.async straight into the
+//              128B-swizzled tile (no register staging), weights by one TMA box per K chunk;
 //              then the epilogue (tcgen05.ld, fused bias / sigmoid / tanh / state update)
 //   warp  4    one elected lane issues tcgen05.mma and commits to the mbarriers
 // Operands are K-major; weights are pre-transposed, TF32-rounded and zero-padded to hp
@@ -44,6 +45,8 @@ struct tparams {
   float* out1;              // GATES: u
   const float* hstate;      // GATES: h
   const float* ubuf;        // CAND: u
+  int b_bytes;              // bytes one TMA box of the weight map delivers per K chunk
+  int round_out;            // GATES: always rounds rh; CAND: round h' to TF32 (not on the last step)
 };
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
@@ -55,7 +58,7 @@ __device__ __forceinline__ float tanh_f(float x) {
 
 template <int MODE>
 __global__ void __launch_bounds__(NTHREADS)
-gemm_tf32_kernel(const tparams p) {
+gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
   extern __shared__ uint8_t smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t row0 = (int64_t)blockIdx.y * BM;
@@ -83,13 +86,14 @@ gemm_tf32_kernel(const tparams p) {
 
   if (warp == 4 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      tc::mbar_init(full_bar(s), NPROD);
+      tc::mbar_init(full_bar(s), NPROD + 1);
       tc::mbar_init(empty_bar(s), 1);
     }
     tc::mbar_init(accum_bar, 1);
     tc::fence_barrier_init();
   }
   if (warp == 0) tc::tmem_alloc(tmem_slot, BN);
+  if (warp == 1 && lane == 0) tc::tma_prefetch_desc(&tmapB);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -112,39 +116,36 @@ gemm_tf32_kernel(const tparams p) {
         else { src1[j] = grow; src2[j] = grow; }
       }
     }
+    int b_row = n0;
+    if (MODE == MODE_MSG) b_row += p.tile_type[blockIdx.y] * p.Np;
+    uint32_t a_off[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int r = rbase + 16 * j;
+      a_off[j] = (r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4);
+    }
     for (int kc = 0; kc < KC; ++kc) {
       const int s = kc % STAGES;
       if (kc >= STAGES) tc::mbar_wait(empty_bar(s), ((kc / STAGES) - 1) & 1);
+      if (tid == 0) {        // weights: one TMA box [b rows x 32 k] per chunk, 128B-swizzled by the TMA unit
+        tc::mbar_arrive_expect_tx(full_bar(s), (uint32_t)p.b_bytes);
+        tc::tma_load_2d(sB + s * B_BYTES, &tmapB, kc * BKF, b_row, full_bar(s));
+      }
+      // activations: 16-byte cp.async straight into the swizzled tile (operands are already
+      // TF32-rounded where they were produced, so no register staging is needed)
       const bool seg2 = kc >= KC1;
       const float* Asrc = seg2 ? p.A2 : p.A1;
       const int kloc = (seg2 ? kc - KC1 : kc) * BKF + c16 * 4;     // column within the segment
       const bool kin = kloc < p.h;                                 // h % 4 == 0
-      float4 va[8], vb[8];
+      const uint32_t a_st = sA + s * A_BYTES;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const int64_t r = seg2 ? src2[j] : src1[j];
-        va[j] = (kin && r >= 0) ? *reinterpret_cast<const float4*>(Asrc + r * p.h + kloc)
-                                : make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool ok = kin && r >= 0;
+        tc::cp_async16(a_st + a_off[j], ok ? (const void*)(Asrc + r * p.h + kloc) : (const void*)Asrc,
+                       ok ? 16u : 0u);
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int n = rbase + 16 * j;
-        vb[j] = n < n_tile ? __ldg(reinterpret_cast<const float4*>(Bt + (size_t)(n0 + n) * p.Kp + kc * BKF + c16 * 4))
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      uint8_t* a_st = smem_al + (sA - base) + s * A_BYTES;
-      uint8_t* b_st = smem_al + (sB - base) + s * B_BYTES;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int r = rbase + 16 * j;
-        const int off = (r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4);
-        float4 t = va[j];
-        t.x = tc::to_tf32(t.x); t.y = tc::to_tf32(t.y); t.z = tc::to_tf32(t.z); t.w = tc::to_tf32(t.w);
-        *reinterpret_cast<float4*>(a_st + off) = t;
-        *reinterpret_cast<float4*>(b_st + off) = vb[j];
-      }
-      tc::fence_proxy_async();
-      tc::mbar_arrive(full_bar(s));
+      tc::cp_async_arrive(full_bar(s));
     }
 
     // ================= epilogue =================
@@ -182,6 +183,9 @@ gemm_tf32_kernel(const tparams p) {
             o.y = uv.y * hv.y + (1.0f - uv.y) * tanh_f(v[1]);
             o.z = uv.z * hv.z + (1.0f - uv.z) * tanh_f(v[2]);
             o.w = uv.w * hv.w + (1.0f - uv.w) * tanh_f(v[3]);
+            if (p.round_out) {
+              o.x = tc::to_tf32(o.x); o.y = tc::to_tf32(o.y); o.z = tc::to_tf32(o.z); o.w = tc::to_tf32(o.w);
+            }
             *reinterpret_cast<float4*>(p.out0 + row * p.h + col) = o;
           }
         }
@@ -201,7 +205,8 @@ gemm_tf32_kernel(const tparams p) {
           if (is_r) {
             const float4 hv = *reinterpret_cast<const float4*>(p.hstate + row * p.h + col);
             *reinterpret_cast<float4*>(p.out0 + row * p.h + col) =
-                make_float4(g[0] * hv.x, g[1] * hv.y, g[2] * hv.z, g[3] * hv.w);
+                make_float4(tc::to_tf32(g[0] * hv.x), tc::to_tf32(g[1] * hv.y),
+                            tc::to_tf32(g[2] * hv.z), tc::to_tf32(g[3] * hv.w));
           } else {
             *reinterpret_cast<float4*>(p.out1 + row * p.h + col) = make_float4(g[0], g[1], g[2], g[3]);
           }
@@ -275,8 +280,50 @@ int realloc_f(ggnn_ctx* ctx, float*& p, size_t n) {
   return GGNN_OK;
 }
 
+// ---- TMA tensor maps over the packed weights ---------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+
+encode_tiled_fn get_encode() {
+  static encode_tiled_fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<encode_tiled_fn>(p);
+  }
+  return fn;
+}
+
+// 2-D FP32 tensor [rows, cols] row-major, box = 32 columns (128 bytes) x box_rows, 128B swizzle
+int make_weight_map(ggnn_ctx* ctx, CUtensorMap* tm, float* base, int64_t rows, int64_t cols, int* box_rows) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  *box_rows = (int)(rows < BN ? rows : BN);
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 4};
+  cuuint32_t box[2] = {(cuuint32_t)BKF, (cuuint32_t)*box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return GGNN_OK;
+}
+
+__global__ void round_copy_kernel(const float4* __restrict__ src, float4* __restrict__ dst, int64_t n4) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 v = src[i];
+    v.x = tc::to_tf32(v.x); v.y = tc::to_tf32(v.y); v.z = tc::to_tf32(v.z); v.w = tc::to_tf32(v.w);
+    dst[i] = v;
+  }
+}
+
 template <int MODE>
-int launch(ggnn_ctx* ctx, const tparams& p, unsigned mtiles, cudaStream_t st) {
+int launch(ggnn_ctx* ctx, const tparams& p, const CUtensorMap& tm, unsigned mtiles, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     GGNN_CUDA(ctx, cudaFuncSetAttribute(gemm_tf32_kernel<MODE>,
@@ -284,7 +331,7 @@ int launch(ggnn_ctx* ctx, const tparams& p, unsigned mtiles, cudaStream_t st) {
     attr_set = true;
   }
   dim3 grid((p.Np + BN - 1) / BN, mtiles);
-  gemm_tf32_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(p);
+  gemm_tf32_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(p, tm);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
@@ -293,12 +340,23 @@ int launch(ggnn_ctx* ctx, const tparams& p, unsigned mtiles, cudaStream_t st) {
 
 bool ggnn_tf32_supported(const ggnn_ctx* ctx) { return ctx->h % 4 == 0 && ctx->hp >= 32; }
 
+// h (any FP32) -> TF32-rounded copy; n = number of floats (multiple of 4). src may equal dst.
+int ggnn_tf32_round_copy(ggnn_ctx* ctx, const float* src, float* dst, int64_t n, cudaStream_t st) {
+  if (n <= 0) return GGNN_OK;
+  prof_scope ps(ctx, GGNN_STAGE_OTHER, st);
+  round_copy_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(reinterpret_cast<const float4*>(src),
+                                                      reinterpret_cast<float4*>(dst), n / 4);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
 int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st) {
   const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
   ggnn_edge_weights& ew = ctx->edge[slot];
   GGNN_TRY(realloc_f(ctx, ew.Wt_tf32, (size_t)two_e * hp * hp));
   pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32, two_e, h, hp);
   GGNN_LAUNCHED(ctx);
+  GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt, ew.Wt_tf32, (int64_t)two_e * hp, hp, &ew.tm_rows));
   if (with_gru) {
     GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32, (size_t)4 * hp * hp));
     GGNN_TRY(realloc_f(ctx, ctx->Wct_tf32, (size_t)2 * hp * hp));
@@ -312,12 +370,16 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
     GGNN_LAUNCHED(ctx);
     pack_bias_kernel<<<(hp + 255) / 256, 256, 0, st>>>(ctx->bc, ctx->bc_pad, 1, h, hp);
     GGNN_LAUNCHED(ctx);
+    GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wg, ctx->Wgt_tf32, 2 * hp, 2 * hp, &ctx->tm_rows_g));
+    GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wc, ctx->Wct_tf32, hp, 2 * hp, &ctx->tm_rows_c));
   }
   return GGNN_OK;
 }
 
+// One timestep.  The state buffer holds TF32-rounded values between steps (so every MMA operand
+// is exact in TF32 and can be copied asynchronously); the last step stores the unrounded FP32.
 int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
-                   float* h_state, cudaStream_t st) {
+                   float* h_state, bool last_step, cudaStream_t st) {
   const int h = ctx->h, hp = ctx->hp;
   const ggnn_edge_weights& ew = ctx->edge[slot];
   if (plan.N == 0) return GGNN_OK;
@@ -330,9 +392,10 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.M = plan.max_tiles * GGNN_TILE_M;
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg;
-    GGNN_TRY(launch<MODE_MSG>(ctx, p, (unsigned)plan.max_tiles, st));
+    p.b_bytes = ew.tm_rows * BKF * 4;
+    GGNN_TRY(launch<MODE_MSG>(ctx, p, ew.tm_Wt, (unsigned)plan.max_tiles, st));
   }
-  GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, st));
+  GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, /*round_tf32=*/true, st));
   const unsigned mt = (unsigned)ceil_div64(plan.N, BM);
   {
     prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
@@ -341,7 +404,8 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.Bt = ctx->Wgt_tf32; p.bias = ctx->bg_pad;
     p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = 2 * hp; p.M = plan.N;
     p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state;
-    GGNN_TRY(launch<MODE_GATES>(ctx, p, mt, st));
+    p.b_bytes = ctx->tm_rows_g * BKF * 4;
+    GGNN_TRY(launch<MODE_GATES>(ctx, p, ctx->tm_Wg, mt, st));
   }
   {
     prof_scope ps(ctx, GGNN_STAGE_GRU_CAND, st);
@@ -350,7 +414,9 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.Bt = ctx->Wct_tf32; p.bias = ctx->bc;
     p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = hp; p.M = plan.N;
     p.out0 = h_state; p.ubuf = bufs.u;
-    GGNN_TRY(launch<MODE_CAND>(ctx, p, mt, st));
+    p.b_bytes = ctx->tm_rows_c * BKF * 4;
+    p.round_out = last_step ? 0 : 1;
+    GGNN_TRY(launch<MODE_CAND>(ctx, p, ctx->tm_Wc, mt, st));
   }
   return GGNN_OK;
 }

@@ -8,6 +8,9 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
 
 // one timestep in TF32 mode; same buffers as the FP32 step
 int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
-                   float* h_state, cudaStream_t st);
+                   float* h_state, bool last_step, cudaStream_t st);
+
+// dst = TF32-rounded src (n floats, multiple of 4); src may equal dst
+int ggnn_tf32_round_copy(ggnn_ctx* ctx, const float* src, float* dst, int64_t n, cudaStream_t st);
 
 bool ggnn_tf32_supported(const ggnn_ctx* ctx);
