@@ -3,6 +3,7 @@
 #include "tf32.cuh"
 
 #include <new>
+#include <stdlib.h>
 
 namespace {
 
@@ -77,6 +78,7 @@ extern "C" int ggnn_create(ggnn_ctx** out, int device) {
     return GGNN_E_UNSUPPORTED;
   }
   c->sm_count = prop.multiProcessorCount;
+  c->no_fused = getenv("GGNN_NO_FUSED") != nullptr;
   c->ws = reinterpret_cast<char*>(new (std::nothrow) ctx_ext());
   if (cudaMallocHost(&c->h_mail, 8 * sizeof(int64_t)) != cudaSuccess ||
       cudaMalloc(&c->d_mail, 8 * sizeof(int64_t)) != cudaSuccess) {
@@ -112,6 +114,14 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
 
 extern "C" const char* ggnn_last_error(const ggnn_ctx* c) { return c ? c->err : "null ctx"; }
 extern "C" int64_t ggnn_launch_count(const ggnn_ctx* c) { return c ? c->launches : 0; }
+
+// development aid (not in the public header): device buffer the persistent kernels write
+// globaltimer phase traces of CTA 0 into; pass NULL to switch tracing off
+extern "C" int ggnn_debug_trace(ggnn_ctx* c, unsigned long long* dev_buf) {
+  if (!c) return GGNN_E_ARG;
+  c->dbg_trace = dev_buf;
+  return GGNN_OK;
+}
 
 extern "C" int ggnn_profile_enable(ggnn_ctx* c, int on) {
   if (!c) return GGNN_E_ARG;

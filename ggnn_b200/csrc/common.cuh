@@ -36,7 +36,9 @@ struct ggnn_ctx {
   float* bc = nullptr;     // [h]
   float* Wgt_tf32 = nullptr; // [2hp, 2hp] transposed + padded + TF32-rounded
   float* Wct_tf32 = nullptr; // [hp, 2hp]
-  CUtensorMap tm_Wg, tm_Wc;  // TMA views of the packed GRU kernels
+  CUtensorMap tm_Wg, tm_Wc, tm_Wg256;  // TMA views of the packed GRU kernels (256-row box: fused kernel)
+  unsigned long long* dbg_trace = nullptr;   // device buffer for kernel phase traces (ggnn_debug_trace)
+  bool   no_fused = false;   // debugging / A-B switch (GGNN_NO_FUSED=1)
   int    tm_rows_g = 0, tm_rows_c = 0;
   float* bg_pad = nullptr;   // [2hp]
   float* bc_pad = nullptr;   // [hp]

@@ -1,0 +1,430 @@
+// gru_fused.cu -- TF32 mode, hidden size <= 128: aggregation + the whole GRU cell in ONE
+// persistent kernel per timestep.  Per 128-node tile (one graph at v = 128):
+//
+//   AGG    x[t,:]  = sum of the incoming message rows (segmented gather-sum, target-CSR order),
+//                    rounded to TF32 and written straight into the MMA operand tile in smem
+//   MMA1   gates   = [x, h] @ Wg        (TMEM cols   0..255: r | u)
+//          cand_x  =  x     @ Wc[:h]    (TMEM cols 256..383)
+//   EPI1   r, u = sigmoid(gates + b); rh = tf32(r * h) written over the h tile in smem;
+//          u*h and 1-u parked in TMEM
+//   MMA2   cand   += rh @ Wc[h:]
+//   EPI2   c = tanh(cand + b); h' = u*h + (1-u)*c -> smem -> TMA store
+//
+// acts, r*h and u never touch HBM (the three-kernel path moves 5 x 64 KB more per tile).
+// Warp roles (576 threads, 1 CTA / SM, ~224 KB smem, 512 TMEM columns):
+//   warps 0-7   aggregation producers (generic-proxy smem stores + fence.proxy.async)
+//   warps 8-15  epilogue (TMEM lanes 32*(warp%4)..), thread = node row, 64 columns each
+//   warp  16    TMA: h tile (4 boxes) and the weight ring (2 x 48 KB stages, 12 fills per tile)
+//   warp  17    tcgen05.mma issuer
+// AGG of tile i+1 overlaps MMA/EPI of tile i (x tile is released by a tcgen05.commit as soon
+// as MMA1 has consumed it).
+#include "tf32.cuh"
+#include "tc.cuh"
+#include <cuda_fp16.h>
+
+namespace {
+
+constexpr int HP = 128;                      // padded hidden size this kernel is built for
+constexpr int BM = 128;
+constexpr int BKF = 32;
+constexpr int CHUNK_BYTES = BM * BKF * 4;    // 16 KB: one [128 x 32] K-major operand chunk
+constexpr int TILE_BYTES = 4 * CHUNK_BYTES;  // 64 KB: x tile / h tile
+constexpr int WSTAGES = 2;
+constexpr int WSTAGE_BYTES = 48 * 1024;      // [256 gate rows | 128 cand rows] x 32 k
+constexpr int N_AGG_WARPS = 8;
+constexpr int N_EPI_WARPS = 8;   // two per TMEM lane quarter, each takes half of the columns
+constexpr int WARP_TMA = N_AGG_WARPS + N_EPI_WARPS;      // 16
+constexpr int WARP_MMA = WARP_TMA + 1;                   // 17
+constexpr int NTHREADS = (WARP_MMA + 1) * 32;            // 576
+constexpr int SMEM_BYTES = 2 * TILE_BYTES + WSTAGES * WSTAGE_BYTES + 1024 /*align*/ + 128 /*barriers*/ +
+                           3 * HP * 4 /*biases*/;   // 232 064 <= 232 448 (227 KB opt-in limit)
+constexpr int AGG_BATCH = 32;                // message rows (FP16, 8 bytes per lane) in flight per warp
+
+struct gparams {
+  const __half* msg;        // [*, h] message rows (FP16: same 11-bit significand as a TF32 operand)
+  const int32_t* tptr;      // [N+1]
+  const int32_t* tmsg;      // [nnz]
+  float* h_state;           // [N, h] in/out (TF32-rounded between steps)
+  const float* bg_pad;      // [2*HP]
+  const float* bc;          // [h]
+  int64_t N;
+  int h;
+  int n_tiles;
+  int round_out;
+  unsigned long long* dbg;  // optional [64 events x 16 iterations] globaltimer trace of CTA 0
+};
+
+__device__ __forceinline__ void trace(const gparams& p, int it, int ev) {
+  if (p.dbg && blockIdx.x == 0 && it < 16) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.dbg[it * 64 + ev] = t;
+  }
+}
+
+// barrier slots (8 bytes each) after the operand buffers
+enum {
+  BAR_W_FULL = 0,                    // [WSTAGES]
+  BAR_W_EMPTY = BAR_W_FULL + WSTAGES,
+  BAR_X_FULL = BAR_W_EMPTY + WSTAGES,
+  BAR_X_EMPTY,
+  BAR_H_FULL,
+  BAR_H_EMPTY,
+  BAR_GATES_DONE,
+  BAR_RH_FULL,
+  BAR_CAND_DONE,
+  BAR_TMEM_EMPTY,
+  BAR_COUNT
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+gru_fused_kernel(const gparams p, const __grid_constant__ CUtensorMap tmH,
+                 const __grid_constant__ CUtensorMap tmWg, const __grid_constant__ CUtensorMap tmWc) {
+  extern __shared__ uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (base - tc::smem_u32(smem_raw));
+  const uint32_t sX = base;                         // x tile: 4 chunks
+  const uint32_t sH = base + TILE_BYTES;            // h tile, later r*h
+  const uint32_t sW = base + 2 * TILE_BYTES;        // weight ring
+  const uint32_t bars = sW + WSTAGES * WSTAGE_BYTES;
+  auto bar = [&](int i) { return bars + 8u * i; };
+  const uint32_t tmem_slot = bars + 8u * BAR_COUNT;
+
+  if (warp == WARP_MMA && lane == 0) {
+    for (int s = 0; s < WSTAGES; ++s) {
+      tc::mbar_init(bar(BAR_W_FULL + s), 1);
+      tc::mbar_init(bar(BAR_W_EMPTY + s), 1);
+    }
+    tc::mbar_init(bar(BAR_X_FULL), N_AGG_WARPS);
+    tc::mbar_init(bar(BAR_X_EMPTY), 1);
+    tc::mbar_init(bar(BAR_H_FULL), 1);
+    tc::mbar_init(bar(BAR_H_EMPTY), 1);
+    tc::mbar_init(bar(BAR_GATES_DONE), 1);
+    tc::mbar_init(bar(BAR_RH_FULL), N_EPI_WARPS);
+    tc::mbar_init(bar(BAR_CAND_DONE), 1);
+    tc::mbar_init(bar(BAR_TMEM_EMPTY), N_EPI_WARPS);
+    tc::fence_barrier_init();
+  }
+  if (warp == WARP_TMA) {
+    if (lane == 0) {
+      tc::tma_prefetch_desc(&tmH);
+      tc::tma_prefetch_desc(&tmWg);
+      tc::tma_prefetch_desc(&tmWc);
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, 512);
+  }
+  {   // biases -> smem (read by every epilogue thread for every tile)
+    float* s_bias = reinterpret_cast<float*>(smem_al + (tmem_slot + 16 - base));
+    if (tid < 2 * HP) s_bias[tid] = p.bg_pad[tid];
+    else if (tid < 3 * HP) s_bias[tid] = (tid - 2 * HP) < p.h ? p.bc[tid - 2 * HP] : 0.f;
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
+  const int h = p.h;
+
+  if (warp < N_AGG_WARPS) {
+    // =============================== aggregation ===============================
+    // warp w owns rows 16w .. 16w+15 of the tile; their message lists are one contiguous
+    // range of tmsg.  lane -> (K chunk = lane / 8, 16-byte slot = lane % 8) of the row.
+    const int kc = lane >> 3, c16 = lane & 7;
+    const bool col_ok = lane * 4 < h;
+    const int lane_c = col_ok ? lane : 0;
+    auto load_ptr = [&](int tile) -> int {           // tptr[r0 .. r0+16] -> lanes 0..16 (clamped at N)
+      int64_t rr = (int64_t)tile * BM + warp * 16 + lane;
+      if (rr > p.N) rr = p.N;
+      return lane <= 16 ? __ldg(p.tptr + rr) : 0;
+    };
+    int it = 0;
+    int my_ptr = blockIdx.x < p.n_tiles ? load_ptr(blockIdx.x) : 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+      const int P0 = __shfl_sync(0xffffffffu, my_ptr, 0);
+      const int P1 = __shfl_sync(0xffffffffu, my_ptr, 16);
+      // prefetch: this tile's first index batch and the next tile's row pointers
+      int my_idx = (P0 + lane < P1) ? __ldg(p.tmsg + P0 + lane) : 0;
+      const int next_tile = tile + gridDim.x;
+      const int nxt_ptr = next_tile < p.n_tiles ? load_ptr(next_tile) : 0;
+      if (it > 0) tc::mbar_wait_relaxed(bar(BAR_X_EMPTY), (it - 1) & 1);
+      if (lane == 0) trace(p, it, warp * 2);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      int row = 0;                                            // local row 0..15 being accumulated
+      int row_end = __shfl_sync(0xffffffffu, my_ptr, 1);
+      auto flush_rows_until = [&](int pos) {
+        // emit every row whose list ends at or before `pos`
+        while (row < 16 && row_end <= pos) {
+          const int r = warp * 16 + row;
+          const uint32_t off = kc * CHUNK_BYTES + (r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4);
+          float4 o = col_ok ? acc : make_float4(0.f, 0.f, 0.f, 0.f);
+          o.x = tc::to_tf32(o.x); o.y = tc::to_tf32(o.y); o.z = tc::to_tf32(o.z); o.w = tc::to_tf32(o.w);
+          *reinterpret_cast<float4*>(smem_al + (sX - base) + off) = o;
+          acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          ++row;
+          row_end = __shfl_sync(0xffffffffu, my_ptr, row + 1 <= 16 ? row + 1 : 16);
+        }
+      };
+      for (int pb = P0; pb < P1; pb += AGG_BATCH) {
+        const int nb = min(AGG_BATCH, P1 - pb);
+        const int cur_idx = my_idx;
+        if (pb + AGG_BATCH + lane < P1) my_idx = __ldg(p.tmsg + pb + AGG_BATCH + lane);   // next batch
+        uint2 v[AGG_BATCH];
+#pragma unroll
+        for (int j = 0; j < AGG_BATCH; ++j) {
+          // unconditional loads (lanes / slots past the end re-read a valid address and are
+          // ignored below): predicated loads made ptxas serialise the whole batch
+          const int idx = __shfl_sync(0xffffffffu, cur_idx, j < nb ? j : 0);
+          v[j] = __ldg(reinterpret_cast<const uint2*>(p.msg + (size_t)idx * h) + lane_c);
+        }
+#pragma unroll
+        for (int j = 0; j < AGG_BATCH; ++j) {
+          if (j < nb) {
+            flush_rows_until(pb + j);
+            const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&v[j].x));
+            const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&v[j].y));
+            acc.x += lo.x; acc.y += lo.y; acc.z += hi.x; acc.w += hi.y;
+          }
+        }
+      }
+      flush_rows_until(0x7fffffff);
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) { tc::mbar_arrive(bar(BAR_X_FULL)); trace(p, it, warp * 2 + 1); }
+      my_ptr = nxt_ptr;
+    }
+  }
+  else if (warp == WARP_TMA) {
+    // =============================== TMA producer ===============================
+    if (lane == 0) {
+      int fill = 0;                                           // running weight-stage fill count
+      auto w_fill = [&](int gate_col, int cand_col) {
+        const int s = fill % WSTAGES;
+        if (fill >= WSTAGES) tc::mbar_wait_relaxed(bar(BAR_W_EMPTY + s), ((fill / WSTAGES) - 1) & 1);
+        const uint32_t dst = sW + s * WSTAGE_BYTES;
+        const uint32_t bytes = (gate_col >= 0 ? 2 * CHUNK_BYTES : 0) + (cand_col >= 0 ? CHUNK_BYTES : 0);
+        tc::mbar_arrive_expect_tx(bar(BAR_W_FULL + s), bytes);
+        if (gate_col >= 0) tc::tma_load_2d(dst, &tmWg, gate_col, 0, bar(BAR_W_FULL + s));                 // 256 rows
+        if (cand_col >= 0) tc::tma_load_2d(dst + 2 * CHUNK_BYTES, &tmWc, cand_col, 0, bar(BAR_W_FULL + s)); // 128 rows
+        ++fill;
+      };
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        // h tile (free once MMA2 of the previous tile has read r*h out of it)
+        if (it > 0) tc::mbar_wait_relaxed(bar(BAR_H_EMPTY), (it - 1) & 1);
+        tc::mbar_arrive_expect_tx(bar(BAR_H_FULL), TILE_BYTES);
+#pragma unroll
+        for (int kc = 0; kc < 4; ++kc)
+          tc::tma_load_2d(sH + kc * CHUNK_BYTES, &tmH, kc * BKF, tile * BM, bar(BAR_H_FULL));
+        // weights, in the order the MMA warp consumes them
+        for (int kc = 0; kc < 4; ++kc) w_fill(kc * BKF, kc * BKF);            // x chunks: gates + cand_x
+        for (int kc = 0; kc < 4; ++kc) w_fill(HP + kc * BKF, -1);             // h chunks: gates
+        for (int kc = 0; kc < 4; ++kc) w_fill(-1, HP + kc * BKF);             // r*h chunks: cand
+      }
+    }
+    __syncwarp();
+  } else if (warp == WARP_MMA) {
+    // =============================== MMA issuer ===============================
+    if (lane == 0) {
+      const uint32_t idesc256 = tc::umma_idesc(2, BM, 256);
+      const uint32_t idesc128 = tc::umma_idesc(2, BM, 128);
+      const uint32_t d_gates = tmem_base, d_cand = tmem_base + 256;
+      int use = 0;                                            // running weight-stage use count
+      auto w_wait = [&]() {
+        const int s = use % WSTAGES;
+        tc::mbar_wait(bar(BAR_W_FULL + s), (use / WSTAGES) & 1);
+        tc::fence_after_sync();
+        return sW + s * WSTAGE_BYTES;
+      };
+      auto w_release = [&]() {
+        tc::umma_commit(bar(BAR_W_EMPTY + (use % WSTAGES)));
+        ++use;
+      };
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        if (it > 0) tc::mbar_wait(bar(BAR_TMEM_EMPTY), (it - 1) & 1);
+        trace(p, it, 16);
+        tc::mbar_wait(bar(BAR_X_FULL), it & 1);
+        tc::fence_after_sync();
+        trace(p, it, 17);
+        for (int kc = 0; kc < 4; ++kc) {                      // x chunks -> gates and cand
+          const uint32_t w = w_wait();
+          const uint32_t a = sX + kc * CHUNK_BYTES;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc::umma_tf32(d_gates, tc::umma_desc_sw128(a + k * 32), tc::umma_desc_sw128(w + k * 32),
+                          idesc256, (kc | k) != 0);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc::umma_tf32(d_cand, tc::umma_desc_sw128(a + k * 32),
+                          tc::umma_desc_sw128(w + 2 * CHUNK_BYTES + k * 32), idesc128, (kc | k) != 0);
+          w_release();
+        }
+        tc::umma_commit(bar(BAR_X_EMPTY));                    // x tile may be refilled (next tile's AGG)
+        trace(p, it, 18);
+        tc::mbar_wait(bar(BAR_H_FULL), it & 1);
+        tc::fence_after_sync();
+        trace(p, it, 19);
+        for (int kc = 0; kc < 4; ++kc) {                      // h chunks -> gates
+          const uint32_t w = w_wait();
+          const uint32_t a = sH + kc * CHUNK_BYTES;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc::umma_tf32(d_gates, tc::umma_desc_sw128(a + k * 32), tc::umma_desc_sw128(w + k * 32),
+                          idesc256, 1);
+          w_release();
+        }
+        tc::umma_commit(bar(BAR_GATES_DONE));
+        trace(p, it, 20);
+        tc::mbar_wait(bar(BAR_RH_FULL), it & 1);              // epilogue replaced h by tf32(r*h)
+        tc::fence_after_sync();
+        trace(p, it, 21);
+        for (int kc = 0; kc < 4; ++kc) {                      // r*h chunks -> cand
+          const uint32_t w = w_wait();
+          const uint32_t a = sH + kc * CHUNK_BYTES;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc::umma_tf32(d_cand, tc::umma_desc_sw128(a + k * 32),
+                          tc::umma_desc_sw128(w + 2 * CHUNK_BYTES + k * 32), idesc128, 1);
+          w_release();
+        }
+        tc::umma_commit(bar(BAR_CAND_DONE));
+        trace(p, it, 22);
+      }
+    }
+    __syncwarp();
+  }
+  else {
+    // =============================== epilogue (warps 8-15) ===============================
+    const int ew = warp & 3;                                  // TMEM lane quarter this warp may access
+    const int chalf = (warp - N_AGG_WARPS) >> 2;              // which 64 of the 128 columns
+    const int r = ew * 32 + lane;                             // row within the tile = TMEM lane
+    const uint32_t t_lane = tmem_base + ((uint32_t)(ew * 32) << 16);
+    const float* s_bg = reinterpret_cast<const float*>(smem_al + (tmem_slot + 16 - base));
+    const float* s_bc = s_bg + 2 * HP;
+    uint8_t* hrow = smem_al + (sH - base) + (r >> 3) * 1024 + (r & 7) * 128;
+    const bool leader = tid == N_AGG_WARPS * 32;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+      // ---- EPI1: both gates.  r*h (TF32) replaces h in smem as the next MMA operand;
+      //      u*h and (1-u) are parked in TMEM (cols 384.. and 128..) so EPI2 never re-reads h.
+      tc::mbar_wait(bar(BAR_GATES_DONE), it & 1);
+      tc::fence_after_sync();
+      if (leader) trace(p, it, 32);
+#pragma unroll 1
+      for (int c16 = 0; c16 < 4; ++c16) {
+        const int col0 = chalf * 64 + c16 * 16;               // first of 16 columns
+        const int cc = col0 >> 5, q0 = (col0 & 31) >> 2;      // K chunk, first 16-byte slot
+        uint32_t ar[16], au[16];
+        tc::tmem_ld16(t_lane + col0, ar);
+        tc::tmem_ld16(t_lane + 128 + col0, au);
+        float4 hv[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          hv[q] = *reinterpret_cast<const float4*>(hrow + cc * CHUNK_BYTES + (((q0 + q) ^ (r & 7)) << 4));
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float hh[4] = {hv[q].x, hv[q].y, hv[q].z, hv[q].w};
+          float o[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int c = col0 + q * 4 + i;
+            const float rg = tc::fast_sigmoid(__uint_as_float(ar[q * 4 + i]) + s_bg[c]);
+            const float ug = tc::fast_sigmoid(__uint_as_float(au[q * 4 + i]) + s_bg[HP + c]);
+            o[i] = tc::to_tf32(rg * hh[i]);
+            ar[q * 4 + i] = __float_as_uint(ug * hh[i]);
+            au[q * 4 + i] = __float_as_uint(1.0f - ug);
+          }
+          *reinterpret_cast<float4*>(hrow + cc * CHUNK_BYTES + (((q0 + q) ^ (r & 7)) << 4)) =
+              make_float4(o[0], o[1], o[2], o[3]);
+        }
+        tc::tmem_st16(t_lane + 384 + col0, ar);
+        tc::tmem_st16(t_lane + 128 + col0, au);
+      }
+      tc::tmem_st_wait();
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(bar(BAR_RH_FULL));
+      if (leader) trace(p, it, 33);
+
+      // ---- EPI2: candidate and new state, staged in the (now free) h tile and written with TMA
+      tc::mbar_wait(bar(BAR_CAND_DONE), it & 1);
+      tc::fence_after_sync();
+      if (leader) trace(p, it, 34);
+#pragma unroll 1
+      for (int c16 = 0; c16 < 4; ++c16) {
+        const int col0 = chalf * 64 + c16 * 16;
+        const int cc = col0 >> 5, q0 = (col0 & 31) >> 2;
+        uint32_t ac[16], om[16], uh[16];
+        tc::tmem_ld16(t_lane + 256 + col0, ac);
+        tc::tmem_ld16(t_lane + 128 + col0, om);
+        tc::tmem_ld16(t_lane + 384 + col0, uh);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float o[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int c = col0 + q * 4 + i;
+            o[i] = fmaf(__uint_as_float(om[q * 4 + i]),
+                        tc::fast_tanh(__uint_as_float(ac[q * 4 + i]) + s_bc[c]),
+                        __uint_as_float(uh[q * 4 + i]));
+            if (p.round_out) o[i] = tc::to_tf32(o[i]);
+          }
+          *reinterpret_cast<float4*>(hrow + cc * CHUNK_BYTES + (((q0 + q) ^ (r & 7)) << 4)) =
+              make_float4(o[0], o[1], o[2], o[3]);
+        }
+      }
+      tc::fence_before_sync();                                // TMEM reads done
+      tc::fence_proxy_async();                                // smem writes -> visible to the TMA unit
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(bar(BAR_TMEM_EMPTY));
+      tc::named_bar_sync(1, N_EPI_WARPS * 32);
+      if (leader) {
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc)
+          tc::tma_store_2d(&tmH, cc * BKF, tile * BM, sH + cc * CHUNK_BYTES);   // rows >= N, cols >= h clipped
+        tc::tma_store_commit();
+        tc::tma_store_wait_read();
+        tc::mbar_arrive(bar(BAR_H_EMPTY));                    // h tile may be refilled
+        trace(p, it, 35);
+      }
+    }
+    if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == WARP_TMA) tc::tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace
+
+bool ggnn_gru_fused_supported(const ggnn_ctx* ctx) { return ctx->hp == HP && ctx->h % 4 == 0; }
+
+int ggnn_gru_fused_step(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* h_state,
+                        bool last_step, cudaStream_t st) {
+  if (plan.N == 0) return GGNN_OK;
+  static bool attr_set = false;
+  if (!attr_set) {
+    GGNN_CUDA(ctx, cudaFuncSetAttribute(gru_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SMEM_BYTES));
+    attr_set = true;
+  }
+  CUtensorMap tmH;
+  GGNN_TRY(ggnn_make_tmap_2d(ctx, &tmH, h_state, plan.N, ctx->h, BM));
+  gparams p{};
+  p.msg = reinterpret_cast<const __half*>(msg); p.tptr = plan.tptr; p.tmsg = plan.tmsg; p.h_state = h_state;
+  p.bg_pad = ctx->bg_pad; p.bc = ctx->bc;
+  p.N = plan.N; p.h = ctx->h;
+  p.n_tiles = (int)ceil_div64(plan.N, BM);
+  p.round_out = last_step ? 0 : 1;
+  p.dbg = ctx->dbg_trace;
+  const int grid = p.n_tiles < ctx->sm_count ? p.n_tiles : ctx->sm_count;
+  prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+  gru_fused_kernel<<<grid, NTHREADS, SMEM_BYTES, st>>>(p, tmH, ctx->tm_Wg256, ctx->tm_Wc);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}

@@ -14,6 +14,7 @@
 // (a multiple of 32) once in ggnn_set_weights, so the mainloop needs no K/N edge cases.
 #include "tf32.cuh"
 #include "tc.cuh"
+#include <cuda_fp16.h>
 
 namespace {
 
@@ -46,6 +47,7 @@ struct tparams {
   const float* hstate;      // GATES: h
   const float* ubuf;        // CAND: u
   int b_bytes;              // bytes one TMA box of the weight map delivers per K chunk
+  __half* out_half;         // MSG: when set, messages are stored as FP16 [M, h] instead of out0
   int round_out;            // GATES: always rounds rh; CAND: round h' to TF32 (not on the last step)
 };
 
@@ -174,7 +176,15 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
             v[0] += bb.x; v[1] += bb.y; v[2] += bb.z; v[3] += bb.w;
           }
           if (MODE == MODE_MSG) {
-            *reinterpret_cast<float4*>(p.out0 + row * p.h + col) = make_float4(v[0], v[1], v[2], v[3]);
+            if (p.out_half) {
+              __half2 lo = __floats2half2_rn(v[0], v[1]), hi = __floats2half2_rn(v[2], v[3]);
+              uint2 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&lo);
+              pk.y = *reinterpret_cast<uint32_t*>(&hi);
+              *reinterpret_cast<uint2*>(p.out_half + row * p.h + col) = pk;
+            } else {
+              *reinterpret_cast<float4*>(p.out0 + row * p.h + col) = make_float4(v[0], v[1], v[2], v[3]);
+            }
           } else {
             const float4 hv = *reinterpret_cast<const float4*>(p.out0 + row * p.h + col);
             const float4 uv = *reinterpret_cast<const float4*>(p.ubuf + row * p.h + col);
@@ -298,22 +308,6 @@ encode_tiled_fn get_encode() {
   return fn;
 }
 
-// 2-D FP32 tensor [rows, cols] row-major, box = 32 columns (128 bytes) x box_rows, 128B swizzle
-int make_weight_map(ggnn_ctx* ctx, CUtensorMap* tm, float* base, int64_t rows, int64_t cols, int* box_rows) {
-  encode_tiled_fn enc = get_encode();
-  if (!enc) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled entry point not found");
-  *box_rows = (int)(rows < BN ? rows : BN);
-  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t gstride[1] = {(cuuint64_t)cols * 4};
-  cuuint32_t box[2] = {(cuuint32_t)BKF, (cuuint32_t)*box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, gdim, gstride, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
-  return GGNN_OK;
-}
-
 __global__ void round_copy_kernel(const float4* __restrict__ src, float4* __restrict__ dst, int64_t n4) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     float4 v = src[i];
@@ -337,6 +331,27 @@ int launch(ggnn_ctx* ctx, const tparams& p, const CUtensorMap& tm, unsigned mtil
 }
 
 }  // namespace
+
+int ggnn_make_tmap_2d(ggnn_ctx* ctx, CUtensorMap* tm, const float* base, int64_t rows, int64_t cols,
+                      int box_rows) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 4};
+  cuuint32_t box[2] = {(cuuint32_t)BKF, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return GGNN_OK;
+}
+
+static int make_weight_map(ggnn_ctx* ctx, CUtensorMap* tm, float* base, int64_t rows, int64_t cols,
+                           int* box_rows) {
+  *box_rows = (int)(rows < BN ? rows : BN);
+  return ggnn_make_tmap_2d(ctx, tm, base, rows, cols, *box_rows);
+}
 
 bool ggnn_tf32_supported(const ggnn_ctx* ctx) { return ctx->h % 4 == 0 && ctx->hp >= 32; }
 
@@ -372,6 +387,7 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
     GGNN_LAUNCHED(ctx);
     GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wg, ctx->Wgt_tf32, 2 * hp, 2 * hp, &ctx->tm_rows_g));
     GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wc, ctx->Wct_tf32, hp, 2 * hp, &ctx->tm_rows_c));
+    if (2 * hp <= 256) GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg256, ctx->Wgt_tf32, 2 * hp, 2 * hp, 2 * hp));
   }
   return GGNN_OK;
 }
@@ -383,6 +399,7 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
   const int h = ctx->h, hp = ctx->hp;
   const ggnn_edge_weights& ew = ctx->edge[slot];
   if (plan.N == 0) return GGNN_OK;
+  const bool fused = ggnn_gru_fused_supported(ctx) && !ctx->no_fused;
   if (plan.max_tiles > 0 && plan.nnz > 0) {
     prof_scope ps(ctx, GGNN_STAGE_MSG, st);
     tparams p{};
@@ -392,9 +409,11 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.M = plan.max_tiles * GGNN_TILE_M;
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg;
+    if (fused) p.out_half = reinterpret_cast<__half*>(bufs.msg);
     p.b_bytes = ew.tm_rows * BKF * 4;
     GGNN_TRY(launch<MODE_MSG>(ctx, p, ew.tm_Wt, (unsigned)plan.max_tiles, st));
   }
+  if (fused) return ggnn_gru_fused_step(ctx, plan, bufs.msg, h_state, last_step, st);
   GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, /*round_tf32=*/true, st));
   const unsigned mt = (unsigned)ceil_div64(plan.N, BM);
   {

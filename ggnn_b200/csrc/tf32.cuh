@@ -14,3 +14,13 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
 int ggnn_tf32_round_copy(ggnn_ctx* ctx, const float* src, float* dst, int64_t n, cudaStream_t st);
 
 bool ggnn_tf32_supported(const ggnn_ctx* ctx);
+
+// 2-D FP32 row-major tensor [rows, cols] -> TMA map with a 32-column (128-byte) x box_rows box,
+// 128B swizzle (the K-major SWIZZLE_128B operand layout of tc.cuh)
+int ggnn_make_tmap_2d(ggnn_ctx* ctx, CUtensorMap* tm, const float* base, int64_t rows, int64_t cols,
+                      int box_rows);
+
+// fused aggregation + GRU timestep (gru_fused.cu), hidden size padded to 128
+bool ggnn_gru_fused_supported(const ggnn_ctx* ctx);
+int ggnn_gru_fused_step(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* h_state,
+                        bool last_step, cudaStream_t st);
