@@ -21,7 +21,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "{\n\t"
       ".reg .pred p;\n\t"
       "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 2000;\n\t"   // HW-suspended up to ~2 us per try
       "@p bra DONE;\n\t"
       "bra WAIT_LOOP;\n\t"
       "DONE:\n\t"
@@ -199,6 +199,12 @@ __device__ __forceinline__ float fast_sigmoid(float x) {
 }
 __device__ __forceinline__ float fast_tanh(float x) {
   return fmaf(-2.0f, rcp_approx(1.0f + ex2_approx(2.8853900817779268f * x)), 1.0f);
+}
+
+// TF32 rounding for values known to be finite and far from FLT_MAX (gate products, sums of
+// messages): round-half-up on the 13 dropped bits, 2 integer ops instead of cvt.rna's 3-4
+__device__ __forceinline__ float to_tf32_fast(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
 }
 
 __device__ __forceinline__ float to_tf32(float x) {     // round to nearest, ties away (cvt.rna)

@@ -31,4 +31,5 @@ for it in range(6):
     if not agg_s:
         break
     print(f"iter {it}: agg start {min(agg_s) - t0:7d}..{max(agg_s) - t0:7d}  done {min(agg_e) - t0:7d}..{max(agg_e) - t0:7d} ns")
+    print("   w0: start=%d done=%d " % (row[0]-t0, row[1]-t0) + " ".join(f"e{k}={row[k]-t0}" for k in range(40,48) if row[k]))
     print("   " + "  ".join(f"{names[k]}={row[k] - t0}" for k in sorted(names) if row[k]))
