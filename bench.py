@@ -325,7 +325,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])
+    ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32"])
     ap.add_argument("--graphs", type=int, default=TOTAL_GRAPHS, help="global batch (all GPUs)")
     ap.add_argument("--pool", type=int, default=4096, help="distinct dense adjacency graphs resident per GPU")
     ap.add_argument("--e2e-graphs", type=int, default=256)
