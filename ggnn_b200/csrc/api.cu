@@ -225,7 +225,7 @@ int read_i64(ggnn_ctx* ctx, const int64_t* dev, int64_t* out, cudaStream_t st) {
 
 // step buffers after the plan, from arena 1
 void take_step_bufs(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_step_bufs* sb) {
-  sb->msg = a.take<float>((size_t)plan.max_tiles * GGNN_TILE_M * h);
+  sb->msg = a.take<float>((size_t)plan.max_tiles * GGNN_TILE_M * (h < 64 ? 64 : h));   // >= 256 B per row: FP16 rows of pitch 128
   sb->acts = a.take<float>((size_t)plan.N * h);
   sb->rh = a.take<float>((size_t)plan.N * h);
   sb->u = a.take<float>((size_t)plan.N * h);

@@ -45,7 +45,7 @@ constexpr int SMEM_BYTES = 2 * TILE_BYTES + WSTAGES * WSTAGE_BYTES + 1024 /*alig
                            3 * HP * 4 /*biases*/;   // 232 064 <= 232 448 (227 KB opt-in limit)
 
 struct gparams {
-  const __half* msg;        // [*, h] message rows (FP16: same 11-bit significand as a TF32 operand)
+  const __half* msg;        // [*, 128] message rows (pitch HP halves whatever h is; FP16: same 11-bit significand as a TF32 operand)
   const int32_t* tptr;      // [N+1]
   const int32_t* tmsg;      // [nnz]
   float* h_state;           // [N, h] in/out (TF32-rounded between steps)
@@ -174,7 +174,7 @@ gru_fused_kernel(const gparams p, const __grid_constant__ CUtensorMap tmH,
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int idx = __shfl_sync(0xffffffffu, my_idx, (pb + j < P1) ? j : 0);
-          v[j] = __ldg(reinterpret_cast<const uint2*>(p.msg + (size_t)idx * h) + lane_c);
+          v[j] = __ldg(reinterpret_cast<const uint2*>(p.msg + (size_t)idx * HP) + lane_c);
         }
       };
       uint2 cur[32];

@@ -347,6 +347,21 @@ int ggnn_make_tmap_2d(ggnn_ctx* ctx, CUtensorMap* tm, const float* base, int64_t
   return GGNN_OK;
 }
 
+int ggnn_make_tmap_2d_f16(ggnn_ctx* ctx, CUtensorMap* tm, const void* base, int64_t rows, int64_t cols,
+                          int box_cols, int box_rows) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) GGNN_FAIL(ctx, GGNN_E_CUDA, "cuTensorMapEncodeTiled (f16) failed (%d)", (int)r);
+  return GGNN_OK;
+}
+
 static int make_weight_map(ggnn_ctx* ctx, CUtensorMap* tm, float* base, int64_t rows, int64_t cols,
                            int* box_rows) {
   *box_rows = (int)(rows < BN ? rows : BN);
@@ -400,7 +415,9 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
   const ggnn_edge_weights& ew = ctx->edge[slot];
   if (plan.N == 0) return GGNN_OK;
   const bool fused = ggnn_gru_fused_supported(ctx) && !ctx->no_fused;
-  if (plan.max_tiles > 0 && plan.nnz > 0) {
+  if (fused) {
+    GGNN_TRY(ggnn_msg_tc_step(ctx, slot, plan, h_state, bufs.msg, st));
+  } else if (plan.max_tiles > 0 && plan.nnz > 0) {
     prof_scope ps(ctx, GGNN_STAGE_MSG, st);
     tparams p{};
     p.A1 = h_state; p.gather = plan.msg_src;
@@ -409,7 +426,6 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.M = plan.max_tiles * GGNN_TILE_M;
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg;
-    if (fused) p.out_half = reinterpret_cast<__half*>(bufs.msg);
     p.b_bytes = ew.tm_rows * BKF * 4;
     GGNN_TRY(launch<MODE_MSG>(ctx, p, ew.tm_Wt, (unsigned)plan.max_tiles, st));
   }

@@ -24,3 +24,12 @@ int ggnn_make_tmap_2d(ggnn_ctx* ctx, CUtensorMap* tm, const float* base, int64_t
 bool ggnn_gru_fused_supported(const ggnn_ctx* ctx);
 int ggnn_gru_fused_step(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* h_state,
                         bool last_step, cudaStream_t st);
+
+// FP16 row-major [rows, cols] -> TMA map, box_cols x box_rows box (box_cols * 2 = 128 bytes), 128B swizzle
+int ggnn_make_tmap_2d_f16(ggnn_ctx* ctx, CUtensorMap* tm, const void* base, int64_t rows, int64_t cols,
+                          int box_cols, int box_rows);
+
+// persistent TF32 message transform with FP16 output rows of pitch 128 (msg_tc.cu), hp == 128
+bool ggnn_msg_tc_supported(const ggnn_ctx* ctx);
+int ggnn_msg_tc_step(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const float* h_state,
+                     void* msg_half, cudaStream_t st);
