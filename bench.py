@@ -319,6 +319,101 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------
+# secondary workload: BASELINE config 5 (training step of the path, data parallel)
+# ---------------------------------------------------------------------------------------
+def c5_inputs(n_graphs, seed, device):
+    """C2-shaped synthetic trees: WSJ-like lengths, 2E = 92, rows = bucket size."""
+    from ggnn_b200 import synth
+    lengths = synth.wsj_like_lengths(n_graphs, seed=seed)
+    tri = synth.random_trees(n_graphs, int(lengths.max()), E, seed=seed, lengths=lengths)
+    rows = torch.tensor([synth.bucket_size(int(l)) for l in lengths])
+    edges, off = synth.packed_edge_list(tri, rows, E)
+    N = int(off[-1])
+    g = torch.Generator().manual_seed(seed)
+    h0 = (torch.rand(N, 400, generator=g) - 0.5) * 0.2
+    d = torch.randn(N, 400, generator=g)
+    return h0.to(device), edges.to(device), d.to(device), N
+
+
+def run_c5(args):
+    import torch.distributed as dist
+    import ggnn_b200
+    from ggnn_b200 import dist as gdist
+    from oracle import ggnn_oracle as O
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    Hc, Tc, per_gpu = 400, 4, args.c5_graphs
+    wd = O.make_weights(TWO_E, Hc, 0)
+    prop = ggnn_b200.Propagator(ggnn_b200.from_dict(wd), dev)
+    h0, edges, d, N = c5_inputs(per_gpu, 1000 + rank, dev)
+    grads = torch.zeros(prop.grad_floats, device=dev)
+
+    def step():
+        return gdist.train_step(prop, h0, edges, lambda hT: d, Tc, grads=grads)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = prop.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = prop.launches - l0
+    if world > 1:
+        tms = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    ms_per_step = ms / args.steps
+    nnz = int(edges.shape[0])
+    if rank == 0:
+        flop = 3 * Tc * (nnz * 2 * Hc * Hc + N * 12 * Hc * Hc)       # bwd counted as 2x fwd (SURVEY 8d)
+        line = {"metric": "GGNN propagation training step graphs/sec (fwd+bwd, T=4)",
+                "value": per_gpu * world / (ms_per_step * 1e-3), "unit": "graphs/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": "C5 synthetic WSJ-shaped trees, h=400 2E=92 T=4, fwd+bwd of the path + "
+                                       "one all-reduce of the 62.9 MB flat weight gradient",
+                           "graphs_per_gpu": per_gpu, "nodes_per_gpu": N, "edges_per_gpu": nnz,
+                           "parallelism": f"data parallel x{world}, NCCL all-reduce (sum) of {prop.grad_floats} floats"},
+                "achieved_tflops_algorithmic_per_gpu": flop / (ms_per_step * 1e-3) / 1e12,
+                "clocks": clocks, "gpu_launches": int(launches)}
+        if world == 1 and not args.no_cpu:
+            from oracle import grad_oracle as G
+            n = 64
+            h0c, ec, dc, _ = c5_inputs(n, 7, "cpu")
+            torch.set_num_threads(os.cpu_count() or 1)
+            t0 = time.perf_counter()
+            G.grads(h0c.numpy(), ec.numpy(), wd, Tc, dc.numpy(), dtype=torch.float32)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": n / dt, "unit": "graphs/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"{n} C5 graphs, torch-CPU FP32 autograd over the edge-list restatement"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -331,9 +426,14 @@ def main():
     ap.add_argument("--e2e-graphs", type=int, default=256)
     ap.add_argument("--ref-graphs", type=int, default=64, help="graphs per step of the CPU reference arm")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c5"],
+                    help="c3 = the headline forward benchmark; c5 = training step (secondary line)")
+    ap.add_argument("--c5-graphs", type=int, default=2048, help="graphs per GPU of the c5 workload")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c5":
+        run_c5(args)
     else:
         run_gpu(args)
 

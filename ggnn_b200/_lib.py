@@ -15,6 +15,7 @@ OK, E_ARG, E_SHAPE, E_CAPACITY, E_CUDA, E_UNSUPPORTED, E_STATE = 0, -1, -2, -3, 
 ADJ_F32, ADJ_U8 = 0, 1
 PREC_FP32, PREC_TF32 = 0, 1
 SLOT_MAIN, SLOT_FIXED = 0, 1
+FLAG_SAVE_TAPE = 2
 STAGES = ("compact_mask", "compact_rest", "plan", "msg", "agg", "gru_gates", "gru_cand", "other")
 
 ERR_NAMES = {E_ARG: "GGNN_E_ARG", E_SHAPE: "GGNN_E_SHAPE", E_CAPACITY: "GGNN_E_CAPACITY",
@@ -32,6 +33,8 @@ SIGNATURES = {
     "ggnn_propagate_dense": (_i, [_vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _u, _vp, _vp]),
     "ggnn_propagate_csr": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _u, _vp, _vp]),
     "ggnn_propagate_edges": (_i, [_vp, _i, _vp, _vp, _i64, _i64, _i, _i, _u, _vp, _vp]),
+    "ggnn_grad_floats": (_i64, [_vp]),
+    "ggnn_propagate_backward": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "ggnn_workspace_bytes": (C.c_size_t, [_vp, _i64, _i64, _i, _i]),
     "ggnn_launch_count": (_i64, [_vp]),
     "ggnn_profile_enable": (_i, [_vp, _i]),

@@ -1,6 +1,7 @@
 // api.cu -- the C ABI of libggnn_b200.so (see include/ggnn_b200.h for the contract).
 #include "plan.cuh"
 #include "tf32.cuh"
+#include "train.cuh"
 
 #include <new>
 #include <stdlib.h>
@@ -15,8 +16,10 @@ struct arena {
 // Two grow-only arenas per ctx: [0] compaction (bitmask, rowptr, scan), [1] col + plan + step
 // buffers.  They are separate because [1] is sized only after the edge count is known and
 // must not move [0].
+// [2] training tape (per-step activations), [3] backward scratch.
 struct ctx_ext {
-  arena ar[2];
+  arena ar[4];
+  ggnn_tape tape;
 };
 
 ctx_ext* ext_of(ggnn_ctx* c) { return reinterpret_cast<ctx_ext*>(c->ws); }
@@ -232,7 +235,26 @@ void take_step_bufs(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_step_bufs* s
 }
 
 int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& sb,
-              float* h_state, int T, int precision, cudaStream_t st) {
+              float* h_state, int T, int precision, unsigned flags, cudaStream_t st) {
+  ggnn_tape& tape = ext_of(ctx)->tape;
+  tape.valid = false;
+  if (flags & GGNN_FLAG_SAVE_TAPE) {      // training forward: keep h, x, r, u, c of every step
+    if (precision != GGNN_PREC_FP32) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE needs GGNN_PREC_FP32");
+    if (plan.dense_rows) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE: edge list is in dense-row mode (nnz >= N*2E)");
+    const size_t nh = (size_t)plan.N * ctx->h;
+    GGNN_TRY(arena_reserve(ctx, 2, (size_t)T * TAPE_ARRAYS * nh * 4 + 256, st));
+    tape.plan = plan; tape.T = T; tape.slot = slot; tape.h = ctx->h;
+    tape.acts = reinterpret_cast<float*>(ext_of(ctx)->ar[2].p);
+    for (int t = 0; t < T; ++t) {
+      GGNN_CUDA(ctx, cudaMemcpyAsync(tape.at(t, TAPE_H), h_state, nh * 4, cudaMemcpyDeviceToDevice, st));
+      ggnn_step_bufs tb = sb;
+      tb.acts = tape.at(t, TAPE_X); tb.u = tape.at(t, TAPE_U);
+      tb.tape_r = tape.at(t, TAPE_R); tb.tape_c = tape.at(t, TAPE_C);
+      GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, tb, h_state, st));
+    }
+    tape.valid = true;
+    return GGNN_OK;
+  }
   if (precision == GGNN_PREC_TF32 && T > 0)   // state is kept TF32-rounded between steps
     GGNN_TRY(ggnn_tf32_round_copy(ctx, h_state, h_state, plan.N * ctx->h, st));
   for (int t = 0; t < T; ++t) {
@@ -246,7 +268,7 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
 // `extra` = bytes at the front of arena 1 already in use (col of the dense path).
 int propagate_csr_chunk(ggnn_ctx* ctx, int slot, float* h_state, const int32_t* rowptr,
                         const int32_t* col, int64_t bc, int v, int64_t nnz, int T, int precision,
-                        size_t extra, cudaStream_t st) {
+                        unsigned flags, size_t extra, cudaStream_t st) {
   ggnn_plan plan;
   ggnn_step_bufs sb;
   {
@@ -263,7 +285,7 @@ int propagate_csr_chunk(ggnn_ctx* ctx, int slot, float* h_state, const int32_t* 
   a.off = extra;
   GGNN_TRY(ggnn_plan_from_csr(ctx, rowptr, col, bc, ctx->two_e, v, nnz, &plan, a, false, st));
   take_step_bufs(a, plan, ctx->h, &sb);
-  return run_steps(ctx, slot, plan, sb, h_state, T, precision, st);
+  return run_steps(ctx, slot, plan, sb, h_state, T, precision, flags, st);
 }
 
 size_t csr_chunk_bytes(ggnn_ctx* ctx, int64_t bc, int v, int64_t nnz, size_t extra) {
@@ -281,7 +303,7 @@ size_t csr_chunk_bytes(ggnn_ctx* ctx, int64_t bc, int v, int64_t nnz, size_t ext
 extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, const void* adj,
                                     int adj_dtype, const float* mask_or_null, int b, int v, int T,
                                     int precision, unsigned flags, float* h_out, void* stream) {
-  (void)mask_or_null; (void)flags;
+  (void)mask_or_null;
   if (!ctx) return GGNN_E_ARG;
   if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: bad sizes b=%d v=%d T=%d", b, v, T);
   if (b > 0 && (!h0 || !adj || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: null pointer");
@@ -299,6 +321,8 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
   int64_t chunk = ((int64_t)1 << 26) / rows_per_graph;
   if (chunk < 1) chunk = 1;
   if (chunk > b) chunk = b;
+  if ((flags & GGNN_FLAG_SAVE_TAPE) && chunk < b)
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE: batch of %d graphs needs more than one chunk (%lld graphs)", b, (long long)chunk);
   for (int64_t g0 = 0; g0 < b; g0 += chunk) {
     const int64_t bc = (b - g0 < chunk) ? b - g0 : chunk;
     const int64_t rows = bc * rows_per_graph;
@@ -318,7 +342,7 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
     int32_t* col = reinterpret_cast<int32_t*>(ext_of(ctx)->ar[1].p);
     GGNN_TRY(ggnn_compact_fill(ctx, rows, v, rowptr, col, nnz, tmp, st));
     GGNN_TRY(propagate_csr_chunk(ctx, slot, h_out + (size_t)g0 * v * h, rowptr, col, bc, v, nnz,
-                                 T, precision, col_bytes, st));
+                                 T, precision, flags, col_bytes, st));
   }
   return GGNN_OK;
 }
@@ -326,7 +350,6 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
 extern "C" int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0, const int32_t* rowptr,
                                   const int32_t* col, int b, int v, int T, int precision,
                                   unsigned flags, float* h_out, void* stream) {
-  (void)flags;
   if (!ctx) return GGNN_E_ARG;
   if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: bad sizes");
   if (b > 0 && (!h0 || !rowptr || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: null pointer");
@@ -344,13 +367,12 @@ extern "C" int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0, cons
   const int64_t nnz = *reinterpret_cast<int32_t*>(ctx->h_mail + 1);
   if (nnz < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: rowptr[last] is negative");
   if (nnz > 0 && !col) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: null col");
-  return propagate_csr_chunk(ctx, slot, h_out, rowptr, col, b, v, nnz, T, precision, 0, st);
+  return propagate_csr_chunk(ctx, slot, h_out, rowptr, col, b, v, nnz, T, precision, flags, 0, st);
 }
 
 extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, const int32_t* edges,
                                     int64_t nnz, int64_t N, int T, int precision, unsigned flags,
                                     float* h_out, void* stream) {
-  (void)flags;
   if (!ctx) return GGNN_E_ARG;
   if (nnz < 0 || N < 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: bad sizes");
   if ((N > 0 && (!h0 || !h_out)) || (nnz > 0 && !edges)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: null pointer");
@@ -375,7 +397,33 @@ extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, co
   int64_t bad = 0;
   GGNN_TRY(read_i64(ctx, ctx->d_mail + 2, &bad, st));   // planning sync: edge validation result
   if (bad) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: %lld edges have node or channel ids out of range", (long long)bad);
-  return run_steps(ctx, slot, plan, sb, h_out, T, precision, st);
+  return run_steps(ctx, slot, plan, sb, h_out, T, precision, flags, st);
+}
+
+// ---------------------------------------------------------------------------------------
+// config 5: backward of the last SAVE_TAPE forward
+extern "C" int64_t ggnn_grad_floats(const ggnn_ctx* ctx) {
+  if (!ctx || !ctx->gru_set) return 0;
+  return (int64_t)ggnn_grad_count(ctx->two_e, ctx->h);
+}
+
+extern "C" int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* d_h0, float* grads,
+                                       void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  ggnn_tape& tape = ext_of(ctx)->tape;
+  if (!tape.valid) GGNN_FAIL(ctx, GGNN_E_STATE, "propagate_backward: no tape (run a propagate call with GGNN_FLAG_SAVE_TAPE first)");
+  if (tape.plan.N > 0 && (!d_hT || !d_h0 || !grads)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_backward: null pointer");
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  ggnn_bwd_scratch sc;
+  {
+    ws_alloc dry(nullptr);
+    ggnn_bwd_take_scratch(dry, tape.plan, ctx->h, &sc);
+    GGNN_TRY(arena_reserve(ctx, 3, dry.off + 256, st));
+  }
+  ws_alloc a(ext_of(ctx)->ar[3].p);
+  ggnn_bwd_take_scratch(a, tape.plan, ctx->h, &sc);
+  return ggnn_backward_fp32(ctx, tape, sc, d_hT, d_h0, grads, st);
 }
 
 extern "C" size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h) {

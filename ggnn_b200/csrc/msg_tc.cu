@@ -114,24 +114,25 @@ msg_tc_kernel(const mparams p, const __grid_constant__ CUtensorMap tmW,
       for (int j = 0; j < 8; ++j) dst[j] = __ldg(p.msg_src + (size_t)tile * BM + rbase + 16 * j);
     };
     if (my_tiles > 0) load_idx(t_begin, src);
-    int cur_type = -1, w_gen = 0;
+    int cur_type = -1;
     for (int i = 0; i < my_tiles; ++i) {
       const int tile = t_begin + i;
       const int s = i % ASTAGES;
       if (i + 1 < my_tiles) load_idx(tile + 1, nsrc);
+      if (i >= ASTAGES) tc::mbar_wait(bar(BAR_A_EMPTY + s), ((i / ASTAGES) - 1) & 1);
       if (tid == 0) {                         // weights: reload when the edge type changes
         const int type = __ldg(p.tile_type + tile);
         if (type != cur_type) {
-          if (i > 0) tc::mbar_wait(bar(BAR_MMA_DONE), (i - 1) & 1);   // MMAs reading the old W are done
+          // MMAs reading the old W must be done.  Tile i-2 is known complete (stage wait above), so
+          // this thread is at most one phase behind MMA_DONE and the parity wait is unambiguous.
+          if (i > 0) tc::mbar_wait(bar(BAR_MMA_DONE), (i - 1) & 1);
           tc::mbar_arrive_expect_tx(bar(BAR_W_FULL), W_BYTES);
 #pragma unroll
           for (int kc = 0; kc < 4; ++kc)
             tc::tma_load_2d(sW + kc * CHUNK_BYTES, &tmW, kc * BKF, type * HP, bar(BAR_W_FULL));
           cur_type = type;
-          ++w_gen;
         }
       }
-      if (i >= ASTAGES) tc::mbar_wait(bar(BAR_A_EMPTY + s), ((i / ASTAGES) - 1) & 1);
       const uint32_t a_st = sA + s * A_BYTES;
 #pragma unroll
       for (int kc = 0; kc < 4; ++kc) {

@@ -10,6 +10,7 @@ struct ggnn_plan {
   int64_t N = 0;         // nodes (b*v for the dense path)
   int64_t nnz = 0;       // edges
   int64_t max_tiles = 0; // host-side bound on the number of message tiles
+  bool dense_rows = false; // message rows are ALL (node, channel) pairs and may feed several targets
   int32_t* n_tiles = nullptr;   // [1]  device: actual number of message tiles
   int32_t* msg_src = nullptr;   // [max_tiles*128] global source node of a message row, -1 = padding
   int32_t* tile_type = nullptr; // [max_tiles]     edge channel of a tile
@@ -32,6 +33,8 @@ struct ggnn_step_bufs {
   float* acts = nullptr;  // [N, h]
   float* rh = nullptr;    // [N, h]
   float* u = nullptr;     // [N, h]
+  float* tape_r = nullptr;  // training tape (FP32 path only): reset gate r of this step, or null
+  float* tape_c = nullptr;  // training tape: candidate c of this step, or null
 };
 int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
                    float* h_state, cudaStream_t st);

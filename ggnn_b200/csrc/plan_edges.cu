@@ -111,6 +111,7 @@ int ggnn_plan_from_edges(ggnn_ctx* ctx, const int32_t* edges, int64_t nnz, int64
   const int64_t Np = (int64_t)align_up((size_t)N, GGNN_TILE_M);
   plan->N = N;
   plan->nnz = nnz;
+  plan->dense_rows = dense_mode;
   plan->max_tiles = dense_mode ? Np / GGNN_TILE_M * two_e : nnz / GGNN_TILE_M + two_e + 1;
   if (plan->max_tiles * GGNN_TILE_M >= 0x7fffffffLL || nnz >= 0x7fffffffLL)
     GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "edge plan too large for int32 row ids; split the batch");

@@ -31,6 +31,8 @@ struct sgemm_params {
   float* out1;            // GATES: u [M, h]
   const float* hstate;    // GATES: h [M, h]
   const float* ubuf;      // CAND: u [M, h]
+  float* out_r;           // GATES, training tape: r [M, h] (or null)
+  float* out_c;           // CAND, training tape: c [M, h] (or null)
   int h;
 };
 
@@ -164,15 +166,17 @@ sgemm_kernel(const sgemm_params p) {
           float4 hv = *reinterpret_cast<const float4*>(p.hstate + row * p.h + n);
           *reinterpret_cast<float4*>(p.out0 + row * p.h + n) =
               make_float4(g[0] * hv.x, g[1] * hv.y, g[2] * hv.z, g[3] * hv.w);
+          if (p.out_r) *reinterpret_cast<float4*>(p.out_r + row * p.h + n) = make_float4(g[0], g[1], g[2], g[3]);
         } else {         // update gate
           *reinterpret_cast<float4*>(p.out1 + row * p.h + (n - p.h)) = make_float4(g[0], g[1], g[2], g[3]);
         }
       } else {           // MODE_CAND
         float4 hv = *reinterpret_cast<const float4*>(p.out0 + row * p.h + n);
         float4 uv = *reinterpret_cast<const float4*>(p.ubuf + row * p.h + n);
-        float hh[4] = {hv.x, hv.y, hv.z, hv.w}, uu[4] = {uv.x, uv.y, uv.z, uv.w}, o[4];
+        float hh[4] = {hv.x, hv.y, hv.z, hv.w}, uu[4] = {uv.x, uv.y, uv.z, uv.w}, o[4], cv[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) o[q] = uu[q] * hh[q] + (1.0f - uu[q]) * tanhf(v[q]);
+        for (int q = 0; q < 4; ++q) { cv[q] = tanhf(v[q]); o[q] = uu[q] * hh[q] + (1.0f - uu[q]) * cv[q]; }
+        if (p.out_c) *reinterpret_cast<float4*>(p.out_c + row * p.h + n) = make_float4(cv[0], cv[1], cv[2], cv[3]);
         *reinterpret_cast<float4*>(p.out0 + row * p.h + n) = make_float4(o[0], o[1], o[2], o[3]);
       }
     }
@@ -258,7 +262,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.A1 = bufs.acts; p.A2 = h_state; p.gather = nullptr;
     p.K1 = h; p.K2 = h; p.lda = h;
     p.Bmat = ctx->Wg; p.bias = ctx->bg; p.N = 2 * h; p.M = plan.N;
-    p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state; p.h = h;
+    p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state; p.h = h; p.out_r = bufs.tape_r;
     dim3 grid((2 * h + BN - 1) / BN, mt);
     sgemm_kernel<MODE_GATES><<<grid, NT, 0, st>>>(p);
     GGNN_LAUNCHED(ctx);
@@ -269,7 +273,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.A1 = bufs.acts; p.A2 = bufs.rh; p.gather = nullptr;
     p.K1 = h; p.K2 = h; p.lda = h;
     p.Bmat = ctx->Wc; p.bias = ctx->bc; p.N = h; p.M = plan.N;
-    p.out0 = h_state; p.ubuf = bufs.u; p.h = h;
+    p.out0 = h_state; p.ubuf = bufs.u; p.h = h; p.out_c = bufs.tape_c;
     dim3 grid((h + BN - 1) / BN, mt);
     sgemm_kernel<MODE_CAND><<<grid, NT, 0, st>>>(p);
     GGNN_LAUNCHED(ctx);

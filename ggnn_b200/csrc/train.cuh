@@ -1,0 +1,29 @@
+// train.cuh -- training tape + backward of the propagation path (strict FP32), declarations.
+#pragma once
+#include "plan.cuh"
+
+// per-step saved activations, each [N, h]: state before the step, aggregated messages, gates, candidate
+enum { TAPE_H = 0, TAPE_X = 1, TAPE_R = 2, TAPE_U = 3, TAPE_C = 4, TAPE_ARRAYS = 5 };
+
+struct ggnn_tape {
+  bool valid = false;
+  int T = 0, slot = 0;
+  ggnn_plan plan;              // lives in the step arena of the forward call
+  float* acts = nullptr;       // [T][TAPE_ARRAYS][N*h]
+  float* at(int t, int which) const { return acts + ((size_t)t * TAPE_ARRAYS + which) * (size_t)plan.N * h; }
+  int h = 0;
+};
+
+// scratch the backward needs, in floats / int32s (for the bump allocator)
+struct ggnn_bwd_scratch {
+  float *dh_a, *dh_b, *dx, *dzc, *rh, *dzg, *dxr;
+  int32_t* msg_tgt;
+};
+void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_bwd_scratch* s);
+
+// flat gradient layout: [dW 2E*h*h | dB 2E*h | dWg 2h*2h | dbg 2h | dWc 2h*h | dbc h]
+size_t ggnn_grad_count(int two_e, int h);
+
+// accumulates into `grads` (caller zeroes it); writes d_h0 [N, h]
+int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scratch& s,
+                       const float* d_hT, float* d_h0, float* grads, cudaStream_t st);

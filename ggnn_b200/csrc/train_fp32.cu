@@ -1,0 +1,443 @@
+// train_fp32.cu -- backward of the propagation path (BASELINE config 5), strict FP32.
+//
+// Forward (per step, tape = h, x, r, u, c):     reference chem_tensorflow_dense.py:391-437 + TF GRUCell
+//   m_j = h[src_j] @ W_e(j) + b_e(j);  x[n] = sum_{j -> n} m_j
+//   [r,u] = sigmoid([x,h] @ Wg + bg);  c = tanh([x, r*h] @ Wc + bc);  h' = u*h + (1-u)*c
+// Backward (per step, in reverse), given dh' (gradient w.r.t. the new state):
+//   dzc = dh' (1-u)(1-c^2)          dzu = dh' (h-c) u (1-u)            dh  = dh' u
+//   [dx | drh] = dzc @ Wc^T         dzr = drh h r (1-r)                dh += drh r
+//   [dx2 | dh2] = [dzr,dzu] @ Wg^T  dx += dx2                          dh += dh2
+//   dWc += [x, r*h]^T dzc           dWg += [x, h]^T [dzr,dzu]          dbc, dbg += column sums
+//   dm_j = dx[tgt_j]                dW_e += h[src_j]^T dm_j            db_e += dm_j
+//   dh[src_j] += dm_j @ W_e^T
+// Two FFMA GEMM kernels carry all contractions:
+//   nt_kernel   C[M,N]   = A[M,K] @ B[N,K]^T   (A rows optionally gathered, two K segments;
+//                                               store, or atomic scatter-add by a row map)
+//   tn_kernel   C[K1,N] += X[R,K1]^T @ D[R,N]  (rows of X and D optionally gathered, grouped by
+//                                               message tile type; split over row blocks, atomics)
+#include "plan.cuh"
+#include "train.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 8, NT = 256;
+
+// ---------------------------------------------------------------------------------------
+struct nt_params {
+  const float* A1; const float* A2;     // K segments (A2 may be null); row-major, lda
+  int K1, K2, lda;
+  const int32_t* a_rowmap;              // row of A1 per output row (-1 = zero row) or null
+  const float* B;                       // [N, K] row-major (per type when tile_type != null)
+  int ldb; int64_t b_type_stride;
+  int N; int64_t M;
+  const int32_t* tile_type; const int32_t* n_tiles;   // grouped mode (one type per 128-row tile)
+  float* C; int ldc;                    // store mode
+  const int32_t* c_rowmap;              // atomic scatter mode: C row per output row (-1 = skip)
+};
+
+__global__ void __launch_bounds__(NT)
+nt_kernel(const nt_params p) {
+  __shared__ __align__(16) float As[2][BK][BM + 4];
+  __shared__ __align__(16) float Bs[2][BK][BN + 4];
+  const int tid = threadIdx.x;
+  const int64_t row0 = (int64_t)blockIdx.y * BM;
+  const int col0 = blockIdx.x * BN;
+  const float* Bm = p.B;
+  if (p.tile_type) {
+    if ((int)blockIdx.y >= *p.n_tiles) return;
+    Bm += (size_t)p.tile_type[blockIdx.y] * p.b_type_stride;
+  }
+  const int K = p.K1 + p.K2;
+  const int lrow = tid >> 1, lk4 = (tid & 1) * 4;        // both loaders: row = tid/2, 4 consecutive k
+  const int64_t a_grow = row0 + lrow;
+  int64_t a_src = -1;
+  if (a_grow < p.M) a_src = p.a_rowmap ? (int64_t)p.a_rowmap[a_grow] : a_grow;
+  const int b_n = col0 + lrow;
+
+  auto load_a = [&](int k0) -> float4 {
+    const int k = k0 + lk4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k < K && a_src >= 0) {
+      if (k < p.K1) v = *reinterpret_cast<const float4*>(p.A1 + a_src * p.lda + k);
+      else v = *reinterpret_cast<const float4*>(p.A2 + a_src * p.lda + (k - p.K1));
+    }
+    return v;
+  };
+  auto load_b = [&](int k0) -> float4 {
+    const int k = k0 + lk4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k < K && b_n < p.N) v = __ldg(reinterpret_cast<const float4*>(Bm + (size_t)b_n * p.ldb + k));
+    return v;
+  };
+  auto store_t = [&](float (*S)[BM + 4], float4 v) {
+    S[lk4 + 0][lrow] = v.x; S[lk4 + 1][lrow] = v.y; S[lk4 + 2][lrow] = v.z; S[lk4 + 3][lrow] = v.w;
+  };
+
+  const int tx = tid & 15, ty = tid >> 4;
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+  float4 ra = load_a(0), rb = load_b(0);
+  store_t(As[0], ra); store_t(Bs[0], rb);
+  __syncthreads();
+  const int ktiles = (K + BK - 1) / BK;
+  for (int kt = 0; kt < ktiles; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < ktiles) { ra = load_a((kt + 1) * BK); rb = load_b((kt + 1) * BK); }
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][kk][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][kk][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][kk][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][kk][64 + tx * 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (kt + 1 < ktiles) { store_t(As[buf ^ 1], ra); store_t(Bs[buf ^ 1], rb); }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int64_t row = row0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+    if (row >= p.M) continue;
+    int64_t crow = row;
+    if (p.c_rowmap) { crow = p.c_rowmap[row]; if (crow < 0) continue; }
+#pragma unroll
+    for (int jh = 0; jh < 2; ++jh) {
+      const int n = col0 + (jh ? 64 + tx * 4 : tx * 4);
+      if (n >= p.N) continue;                       // N % 4 == 0
+      float* dst = p.C + crow * p.ldc + n;
+      if (p.c_rowmap) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) atomicAdd(dst + q, acc[i][jh * 4 + q]);
+      } else {
+        *reinterpret_cast<float4*>(dst) = make_float4(acc[i][jh * 4 + 0], acc[i][jh * 4 + 1],
+                                                      acc[i][jh * 4 + 2], acc[i][jh * 4 + 3]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+struct tn_params {
+  const float* X; int ldx; const int32_t* x_rowmap;   // [R, K1] (rows optionally gathered, -1 = zero)
+  const float* D; int ldd; const int32_t* d_rowmap;   // [R, N]
+  int K1, N; int64_t R;
+  int rows_per_cta;                                   // multiple of 128
+  float* C; int ldc;                                  // [K1, N] (+ type * c_type_stride in grouped mode)
+  const int32_t* tile_type; const int32_t* n_tiles; int64_t c_type_stride;
+};
+
+__global__ void __launch_bounds__(NT)
+tn_kernel(const tn_params p) {
+  __shared__ __align__(16) float Xs[2][BK][BM];
+  __shared__ __align__(16) float Ds[2][BK][BN];
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  int64_t r_begin = (int64_t)blockIdx.z * p.rows_per_cta;
+  int64_t r_end = r_begin + p.rows_per_cta;
+  int64_t R = p.R;
+  if (p.tile_type) R = (int64_t)(*p.n_tiles) * GGNN_TILE_M;
+  if (r_end > R) r_end = R;
+  if (r_begin >= r_end) return;
+
+  const int lk = tid >> 5, lc4 = (tid & 31) * 4;       // loaders: row k = tid/32, 4 consecutive columns
+  auto load_x = [&](int64_t r0) -> float4 {
+    const int64_t r = r0 + lk;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < r_end && m0 + lc4 < p.K1) {
+      const int64_t src = p.x_rowmap ? (int64_t)p.x_rowmap[r] : r;
+      if (src >= 0) v = *reinterpret_cast<const float4*>(p.X + src * p.ldx + m0 + lc4);
+    }
+    return v;
+  };
+  auto load_d = [&](int64_t r0) -> float4 {
+    const int64_t r = r0 + lk;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < r_end && n0 + lc4 < p.N) {
+      const int64_t src = p.d_rowmap ? (int64_t)p.d_rowmap[r] : r;
+      if (src >= 0) v = *reinterpret_cast<const float4*>(p.D + src * p.ldd + n0 + lc4);
+    }
+    return v;
+  };
+
+  const int tx = tid & 15, ty = tid >> 4;
+  float acc[8][8];
+  auto zero = [&]() {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+  };
+  auto flush = [&](int type) {
+    float* Cb = p.C + (size_t)type * p.c_type_stride;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+      if (m >= p.K1) continue;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int n = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+        if (n < p.N && acc[i][j] != 0.f) atomicAdd(Cb + (size_t)m * p.ldc + n, acc[i][j]);
+      }
+    }
+  };
+  zero();
+  int cur_type = p.tile_type ? p.tile_type[r_begin / GGNN_TILE_M] : 0;
+
+  float4 rx = load_x(r_begin), rd = load_d(r_begin);
+  *reinterpret_cast<float4*>(&Xs[0][lk][lc4]) = rx;
+  *reinterpret_cast<float4*>(&Ds[0][lk][lc4]) = rd;
+  __syncthreads();
+  int buf = 0;
+  for (int64_t r0 = r_begin; r0 < r_end; r0 += BK) {
+    const bool more = r0 + BK < r_end;
+    if (more) { rx = load_x(r0 + BK); rd = load_d(r0 + BK); }
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&Xs[buf][kk][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&Xs[buf][kk][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Ds[buf][kk][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Ds[buf][kk][64 + tx * 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (more) {
+      *reinterpret_cast<float4*>(&Xs[buf ^ 1][lk][lc4]) = rx;
+      *reinterpret_cast<float4*>(&Ds[buf ^ 1][lk][lc4]) = rd;
+    }
+    __syncthreads();
+    buf ^= 1;
+    // grouped mode: a new 128-row tile may belong to another edge type -> flush and restart
+    if (p.tile_type && more && ((r0 + BK) % GGNN_TILE_M) == 0) {
+      const int t = p.tile_type[(r0 + BK) / GGNN_TILE_M];
+      if (t != cur_type) { flush(cur_type); zero(); cur_type = t; }
+    }
+  }
+  flush(cur_type);
+}
+
+// column sums of D rows (optionally gathered), grouped by tile type: out[type][n] += sum_r D[map(r)][n]
+__global__ void __launch_bounds__(256)
+colsum_kernel(const float* __restrict__ D, int ldd, const int32_t* __restrict__ d_rowmap, int N,
+              int64_t R, int rows_per_cta, float* __restrict__ out, const int32_t* __restrict__ tile_type,
+              const int32_t* __restrict__ n_tiles, int out_type_stride) {
+  int64_t r_begin = (int64_t)blockIdx.y * rows_per_cta, r_end = r_begin + rows_per_cta;
+  if (tile_type) R = (int64_t)(*n_tiles) * GGNN_TILE_M;
+  if (r_end > R) r_end = R;
+  const int n = blockIdx.x * 256 + threadIdx.x;
+  if (r_begin >= r_end || n >= N) return;
+  int cur_type = tile_type ? tile_type[r_begin / GGNN_TILE_M] : 0;
+  float s = 0.f;
+  for (int64_t r = r_begin; r < r_end; ++r) {
+    if (tile_type && r > r_begin && (r % GGNN_TILE_M) == 0) {
+      const int t = tile_type[r / GGNN_TILE_M];
+      if (t != cur_type) { if (s != 0.f) atomicAdd(out + (size_t)cur_type * out_type_stride + n, s); s = 0.f; cur_type = t; }
+    }
+    const int64_t src = d_rowmap ? (int64_t)d_rowmap[r] : r;
+    if (src >= 0) s += D[src * ldd + n];
+  }
+  if (s != 0.f) atomicAdd(out + (size_t)cur_type * out_type_stride + n, s);
+}
+
+// ---- pointwise pieces of the GRU backward -------------------------------------------------
+// dzc = dh'(1-u)(1-c^2);  dzu -> dzg[:, h:];  dh = dh' u;  rh = r*h (recomputed operand of dWc)
+__global__ void gru_bwd_pw1_kernel(const float* __restrict__ dhn, const float* __restrict__ hs,
+                                   const float* __restrict__ r, const float* __restrict__ u,
+                                   const float* __restrict__ c, float* __restrict__ dzc,
+                                   float* __restrict__ dzg, float* __restrict__ dh, float* __restrict__ rh,
+                                   int64_t N, int h) {
+  const int64_t total = N * h;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / h; const int k = (int)(i % h);
+    const float g = dhn[i], uu = u[i], cc = c[i], hh = hs[i];
+    dzc[i] = g * (1.f - uu) * (1.f - cc * cc);
+    dzg[n * 2 * h + h + k] = g * (hh - cc) * uu * (1.f - uu);
+    dh[i] = g * uu;
+    rh[i] = r[i] * hh;
+  }
+}
+// dxr = [dx | drh]:  dzr -> dzg[:, :h];  dh += drh r;  dx = dxr[:, :h]
+__global__ void gru_bwd_pw2_kernel(const float* __restrict__ dxr, const float* __restrict__ hs,
+                                   const float* __restrict__ r, float* __restrict__ dzg,
+                                   float* __restrict__ dh, float* __restrict__ dx, int64_t N, int h) {
+  const int64_t total = N * h;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / h; const int k = (int)(i % h);
+    const float drh = dxr[n * 2 * h + h + k], rr = r[i];
+    dzg[n * 2 * h + k] = drh * hs[i] * rr * (1.f - rr);
+    dh[i] += drh * rr;
+    dx[i] = dxr[n * 2 * h + k];
+  }
+}
+// dxh = [dx2 | dh2]:  dx += dx2;  dh += dh2
+__global__ void gru_bwd_pw3_kernel(const float* __restrict__ dxh, float* __restrict__ dx,
+                                   float* __restrict__ dh, int64_t N, int h) {
+  const int64_t total = N * h;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / h; const int k = (int)(i % h);
+    dx[i] += dxh[n * 2 * h + k];
+    dh[i] += dxh[n * 2 * h + h + k];
+  }
+}
+
+// msg_tgt[message row] = target node (from the target CSR); padding rows keep -1
+__global__ void msg_tgt_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg,
+                               int64_t N, int32_t* __restrict__ msg_tgt) {
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  for (int j = tptr[n]; j < tptr[n + 1]; ++j) msg_tgt[tmsg[j]] = (int32_t)n;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+size_t ggnn_grad_count(int two_e, int h) {
+  return (size_t)two_e * h * h + (size_t)two_e * h + (size_t)4 * h * h + 2 * h + (size_t)2 * h * h + h;
+}
+
+void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_bwd_scratch* s) {
+  const size_t nh = (size_t)plan.N * h;
+  s->dh_a = a.take<float>(nh);
+  s->dh_b = a.take<float>(nh);
+  s->dx = a.take<float>(nh);
+  s->dzc = a.take<float>(nh);
+  s->rh = a.take<float>(nh);
+  s->dzg = a.take<float>(2 * nh);
+  s->dxr = a.take<float>(2 * nh);
+  s->msg_tgt = a.take<int32_t>((size_t)plan.max_tiles * GGNN_TILE_M);
+}
+
+namespace {
+
+int launch_nt(ggnn_ctx* ctx, const nt_params& p, unsigned mtiles, cudaStream_t st) {
+  if (mtiles == 0 || p.N == 0) return GGNN_OK;
+  dim3 grid((p.N + BN - 1) / BN, mtiles);
+  nt_kernel<<<grid, NT, 0, st>>>(p);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+int launch_tn(ggnn_ctx* ctx, const tn_params& p, int64_t rows_bound, cudaStream_t st) {
+  if (rows_bound <= 0) return GGNN_OK;
+  dim3 grid((p.N + BN - 1) / BN, (p.K1 + BM - 1) / BM, (unsigned)ceil_div64(rows_bound, p.rows_per_cta));
+  tn_kernel<<<grid, NT, 0, st>>>(p);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+int launch_colsum(ggnn_ctx* ctx, const float* D, int ldd, const int32_t* map, int N, int64_t R,
+                  float* out, const int32_t* tile_type, const int32_t* n_tiles, int stride, cudaStream_t st) {
+  if (R <= 0) return GGNN_OK;
+  const int rows_per_cta = 1024;
+  dim3 grid((N + 255) / 256, (unsigned)ceil_div64(R, rows_per_cta));
+  colsum_kernel<<<grid, 256, 0, st>>>(D, ldd, map, N, R, rows_per_cta, out, tile_type, n_tiles, stride);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+}  // namespace
+
+int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scratch& s,
+                       const float* d_hT, float* d_h0, float* grads, cudaStream_t st) {
+  const ggnn_plan& plan = tape.plan;
+  const int h = ctx->h, two_e = ctx->two_e;
+  const int64_t N = plan.N;
+  const ggnn_edge_weights& ew = ctx->edge[tape.slot];
+  float* gW = grads;
+  float* gB = gW + (size_t)two_e * h * h;
+  float* gWg = gB + (size_t)two_e * h;
+  float* gbg = gWg + (size_t)4 * h * h;
+  float* gWc = gbg + 2 * h;
+  float* gbc = gWc + (size_t)2 * h * h;
+  const size_t nh = (size_t)N * h;
+  if (N == 0) return GGNN_OK;
+  if (tape.T == 0) {
+    GGNN_CUDA(ctx, cudaMemcpyAsync(d_h0, d_hT, nh * 4, cudaMemcpyDeviceToDevice, st));
+    return GGNN_OK;
+  }
+  prof_scope ps(ctx, GGNN_STAGE_OTHER, st);
+  const int64_t mrows = plan.max_tiles * GGNN_TILE_M;
+  const bool have_msgs = plan.max_tiles > 0 && plan.nnz > 0;
+  if (have_msgs) {
+    GGNN_CUDA(ctx, cudaMemsetAsync(s.msg_tgt, 0xFF, (size_t)mrows * 4, st));
+    msg_tgt_kernel<<<(unsigned)ceil_div64(N, 256), 256, 0, st>>>(plan.tptr, plan.tmsg, N, s.msg_tgt);
+    GGNN_LAUNCHED(ctx);
+  }
+  const unsigned mt = (unsigned)ceil_div64(N, BM);
+  const int pw_grid = ctx->sm_count * 8;
+  const int tn_rows = 2048;
+  const float* dhn = d_hT;
+  float* dh = s.dh_a;
+  for (int t = tape.T - 1; t >= 0; --t) {
+    const float *ht = tape.at(t, TAPE_H), *xt = tape.at(t, TAPE_X), *rt = tape.at(t, TAPE_R),
+                *ut = tape.at(t, TAPE_U), *ct = tape.at(t, TAPE_C);
+    gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h);
+    GGNN_LAUNCHED(ctx);
+    {  // [dx | drh] = dzc @ Wc^T
+      nt_params p{};
+      p.A1 = s.dzc; p.K1 = h; p.lda = h; p.B = ctx->Wc; p.ldb = h; p.N = 2 * h; p.M = N;
+      p.C = s.dxr; p.ldc = 2 * h;
+      GGNN_TRY(launch_nt(ctx, p, mt, st));
+    }
+    for (int part = 0; part < 2; ++part) {   // dWc += [x, rh]^T dzc
+      tn_params p{};
+      p.X = part ? s.rh : xt; p.ldx = h; p.D = s.dzc; p.ldd = h; p.K1 = h; p.N = h; p.R = N;
+      p.rows_per_cta = tn_rows; p.C = gWc + (size_t)part * h * h; p.ldc = h;
+      GGNN_TRY(launch_tn(ctx, p, N, st));
+    }
+    GGNN_TRY(launch_colsum(ctx, s.dzc, h, nullptr, h, N, gbc, nullptr, nullptr, 0, st));
+    gru_bwd_pw2_kernel<<<pw_grid, 256, 0, st>>>(s.dxr, ht, rt, s.dzg, dh, s.dx, N, h);
+    GGNN_LAUNCHED(ctx);
+    {  // [dx2 | dh2] = [dzr, dzu] @ Wg^T
+      nt_params p{};
+      p.A1 = s.dzg; p.K1 = 2 * h; p.lda = 2 * h; p.B = ctx->Wg; p.ldb = 2 * h; p.N = 2 * h; p.M = N;
+      p.C = s.dxr; p.ldc = 2 * h;
+      GGNN_TRY(launch_nt(ctx, p, mt, st));
+    }
+    for (int part = 0; part < 2; ++part) {   // dWg += [x, h]^T [dzr, dzu]
+      tn_params p{};
+      p.X = part ? ht : xt; p.ldx = h; p.D = s.dzg; p.ldd = 2 * h; p.K1 = h; p.N = 2 * h; p.R = N;
+      p.rows_per_cta = tn_rows; p.C = gWg + (size_t)part * h * 2 * h; p.ldc = 2 * h;
+      GGNN_TRY(launch_tn(ctx, p, N, st));
+    }
+    GGNN_TRY(launch_colsum(ctx, s.dzg, 2 * h, nullptr, 2 * h, N, gbg, nullptr, nullptr, 0, st));
+    gru_bwd_pw3_kernel<<<pw_grid, 256, 0, st>>>(s.dxr, s.dx, dh, N, h);
+    GGNN_LAUNCHED(ctx);
+    if (have_msgs) {
+      {  // dh[src_j] += dx[tgt_j] @ W_e^T
+        nt_params p{};
+        p.A1 = s.dx; p.K1 = h; p.lda = h; p.a_rowmap = s.msg_tgt;
+        p.B = ew.W; p.ldb = h; p.b_type_stride = (int64_t)h * h; p.N = h; p.M = mrows;
+        p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
+        p.C = dh; p.ldc = h; p.c_rowmap = plan.msg_src;
+        GGNN_TRY(launch_nt(ctx, p, (unsigned)plan.max_tiles, st));
+      }
+      {  // dW_e += h[src_j]^T dx[tgt_j]
+        tn_params p{};
+        p.X = ht; p.ldx = h; p.x_rowmap = plan.msg_src; p.D = s.dx; p.ldd = h; p.d_rowmap = s.msg_tgt;
+        p.K1 = h; p.N = h; p.R = mrows; p.rows_per_cta = 8 * GGNN_TILE_M;
+        p.C = gW; p.ldc = h; p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
+        p.c_type_stride = (int64_t)h * h;
+        GGNN_TRY(launch_tn(ctx, p, mrows, st));
+      }
+      GGNN_TRY(launch_colsum(ctx, s.dx, h, s.msg_tgt, h, mrows, gB, plan.tile_type, plan.n_tiles, h, st));
+    }
+    dhn = dh;
+    dh = (dh == s.dh_a) ? s.dh_b : s.dh_a;
+  }
+  GGNN_CUDA(ctx, cudaMemcpyAsync(d_h0, dhn, nh * 4, cudaMemcpyDeviceToDevice, st));
+  return GGNN_OK;
+}

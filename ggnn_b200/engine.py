@@ -21,6 +21,10 @@ def _ptr(t: Optional[torch.Tensor]):
     return C.c_void_p(0 if t is None else t.data_ptr())
 
 
+def _flags(save_tape: bool) -> int:
+    return _lib.FLAG_SAVE_TAPE if save_tape else 0
+
+
 def _stream_ptr(device) -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
@@ -172,7 +176,8 @@ class Propagator:
         return h0.contiguous()
 
     def propagate_dense(self, h0: torch.Tensor, adj: torch.Tensor, num_timesteps=None, fixed_ts=None,
-                        precision: str = "fp32", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                        precision: str = "fp32", out: Optional[torch.Tensor] = None,
+                        save_tape: bool = False) -> torch.Tensor:
         if precision not in _PREC:
             raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
         h0 = self._state(h0, 3)
@@ -186,11 +191,13 @@ class Propagator:
             out = torch.empty_like(h0)
         with torch.cuda.device(self.device):
             rc = self._l.ggnn_propagate_dense(self._ctx, slot, _ptr(h0), _ptr(adj), dt, None, b, v, T,
-                                              _PREC[precision], 0, _ptr(out), _stream_ptr(self.device))
+                                              _PREC[precision], _flags(save_tape), _ptr(out),
+                                              _stream_ptr(self.device))
         self._check(rc, "ggnn_propagate_dense")
         return out
 
-    def propagate_csr(self, h0, rowptr, col, num_timesteps=None, fixed_ts=None, precision="fp32", out=None):
+    def propagate_csr(self, h0, rowptr, col, num_timesteps=None, fixed_ts=None, precision="fp32", out=None,
+                      save_tape=False):
         if precision not in _PREC:
             raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
         h0 = self._state(h0, 3)
@@ -205,12 +212,13 @@ class Propagator:
             out = torch.empty_like(h0)
         with torch.cuda.device(self.device):
             rc = self._l.ggnn_propagate_csr(self._ctx, slot, _ptr(h0), _ptr(rowptr.contiguous()),
-                                            _ptr(col.contiguous()), b, v, T, _PREC[precision], 0,
-                                            _ptr(out), _stream_ptr(self.device))
+                                            _ptr(col.contiguous()), b, v, T, _PREC[precision],
+                                            _flags(save_tape), _ptr(out), _stream_ptr(self.device))
         self._check(rc, "ggnn_propagate_csr")
         return out
 
-    def propagate_edges(self, h0, edges, num_timesteps=None, fixed_ts=None, precision="fp32", out=None):
+    def propagate_edges(self, h0, edges, num_timesteps=None, fixed_ts=None, precision="fp32", out=None,
+                        save_tape=False):
         if precision not in _PREC:
             raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
         h0 = self._state(h0, 2)
@@ -224,7 +232,45 @@ class Propagator:
             out = torch.empty_like(h0)
         with torch.cuda.device(self.device):
             rc = self._l.ggnn_propagate_edges(self._ctx, slot, _ptr(h0), _ptr(edges.contiguous()),
-                                              edges.shape[0], h0.shape[0], T, _PREC[precision], 0,
-                                              _ptr(out), _stream_ptr(self.device))
+                                              edges.shape[0], h0.shape[0], T, _PREC[precision],
+                                              _flags(save_tape), _ptr(out), _stream_ptr(self.device))
         self._check(rc, "ggnn_propagate_edges")
+        return out
+
+    # -- config 5: backward ---------------------------------------------------------------
+    @property
+    def grad_floats(self) -> int:
+        return int(self._l.ggnn_grad_floats(self._ctx))
+
+    def backward(self, d_hT: torch.Tensor, grads: Optional[torch.Tensor] = None
+                 ) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Backward of the last ``save_tape=True`` propagate call.  ``d_hT``: gradient w.r.t. the
+        returned node representations (same shape).  Returns (d_h0, flat gradient buffer); the
+        weight gradients are ACCUMULATED into ``grads`` when given (float32 [grad_floats])."""
+        if d_hT.dtype != torch.float32 or d_hT.device != self.device:
+            raise ValueError("d_hT must be a float32 tensor on the ctx device")
+        d_hT = d_hT.contiguous()
+        if grads is None:
+            grads = torch.zeros(self.grad_floats, dtype=torch.float32, device=self.device)
+        elif grads.dtype != torch.float32 or grads.numel() != self.grad_floats or not grads.is_contiguous():
+            raise ValueError(f"grads must be contiguous float32 [{self.grad_floats}]")
+        d_h0 = torch.empty_like(d_hT)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_propagate_backward(self._ctx, _ptr(d_hT), _ptr(d_h0), _ptr(grads),
+                                                 _stream_ptr(self.device))
+        self._check(rc, "ggnn_propagate_backward")
+        return d_h0, grads
+
+    def split_grads(self, flat: torch.Tensor) -> dict:
+        """Views of the flat gradient buffer, keyed like GGNNWeights fields."""
+        w = self.weights
+        e2, h = w.two_e, w.hidden_size
+        sizes = [("edge_weights", (e2, h, h)), ("edge_biases", (e2, h)), ("gru_gate_kernel", (2 * h, 2 * h)),
+                 ("gru_gate_bias", (2 * h,)), ("gru_cand_kernel", (2 * h, h)), ("gru_cand_bias", (h,))]
+        out, off = {}, 0
+        for name, shp in sizes:
+            n = int(np.prod(shp))
+            out[name] = flat[off:off + n].view(*shp)
+            off += n
+        assert off == flat.numel()
         return out

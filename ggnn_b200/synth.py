@@ -98,6 +98,17 @@ def global_edge_list(triples: torch.Tensor, v: int, num_edge_types: int) -> torc
     return torch.stack([g * v + s, ch, g * v + t], dim=1).to(torch.int32)
 
 
+def packed_edge_list(triples: torch.Tensor, rows_per_graph: torch.Tensor, num_edge_types: int):
+    """Edge list for ragged graphs packed back to back: graph g owns node rows
+    [offsets[g], offsets[g+1]) with rows_per_graph[g] rows (its bucket size, padded rows included
+    as in the reference).  Returns (int32 [nnz, 3] (src, channel, dst), int64 offsets [b+1])."""
+    e = edges_from_triples(triples, 0, num_edge_types).long()
+    off = torch.zeros(triples.shape[0] + 1, dtype=torch.long, device=triples.device)
+    off[1:] = torch.cumsum(rows_per_graph.long().to(triples.device), 0)
+    base = off[e[:, 0]]
+    return torch.stack([base + e[:, 3], e[:, 1], base + e[:, 2]], dim=1).to(torch.int32), off
+
+
 def random_multigraph(n_graphs: int, nodes: int, base_edges: int, num_types: int, seed: int = 0,
                       device="cpu") -> torch.Tensor:
     """C4-style graphs: per graph `base_edges` uniform random (src, dst, type) edges plus their

@@ -62,6 +62,8 @@ extern "C" {
 
 /* flags */
 #define GGNN_FLAG_LOOP_ORDER  1u  /* reserved: summation order of compute_timestep_normal */
+#define GGNN_FLAG_SAVE_TAPE   2u  /* training forward: keep every step's activations in the ctx for
+                                   * ggnn_propagate_backward (GGNN_PREC_FP32 only, one chunk)      */
 
 typedef struct ggnn_ctx ggnn_ctx;
 
@@ -119,6 +121,18 @@ int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0,
                          const int32_t* edges, int64_t nnz, int64_t N,
                          int T, int precision, unsigned flags,
                          float* h_out, void* stream);
+
+/* Training (BASELINE config 5): backward of the LAST propagate call that ran with
+ * GGNN_FLAG_SAVE_TAPE on this ctx -- what tf.gradients builds over the unrolled path for
+ * make_train_step (chem_tensorflow.py:483-506), dropout keep-probabilities 1.0.
+ *   d_hT  [N, h]  gradient w.r.t. the final node representations (in)
+ *   d_h0  [N, h]  gradient w.r.t. the initial node representations (out)
+ *   grads         flat FP32 buffer of ggnn_grad_floats() elements, ACCUMULATED into (zero it first):
+ *                 [dW 2E*h*h | dB 2E*h | dWg 2h*2h | dbg 2h | dWc 2h*h | dbc h]  (layouts of set_weights)
+ * This buffer is what the data-parallel trainer all-reduces with NCCL.  Weight gradients are
+ * summed with float atomics (order not fixed).  No synchronisation. */
+int64_t ggnn_grad_floats(const ggnn_ctx* ctx);
+int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* d_h0, float* grads, void* stream);
 
 /* bytes of ctx-owned scratch a propagate call of this size will hold */
 size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h);

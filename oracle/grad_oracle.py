@@ -1,0 +1,58 @@
+"""Gradient oracle for the training configuration (BASELINE config 5).
+
+THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE (same rule as ggnn_oracle.py).
+
+The reference obtains gradients from TensorFlow's autodiff over the unrolled path
+(``make_train_step``, chem_tensorflow.py:483-506: ``tf.gradients`` via
+``AdamOptimizer.compute_gradients``); there is no hand-written backward to restate.  The
+oracle therefore is torch-CPU FP64 autograd over the same restatement of the forward that
+ggnn_oracle.py holds (edge-list form, chem_tensorflow_dense.py:391-437 + TF GRUCell), with both
+dropouts at keep-probability 1.0 (or with externally supplied edge-weight masks).
+
+PARITY UNPINNED for the floating-point path (see ggnn_oracle.py): pinned only against the
+forward oracle (the FP64 forward here must equal ggnn_oracle.propagate_edges to 1e-12).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+KEYS = ("edge_weights", "edge_biases", "gru_gate_kernel", "gru_gate_bias", "gru_cand_kernel", "gru_cand_bias")
+
+
+def forward_torch(h0, edges, wt, T, use_bias=True):
+    """h0 [N,H] tensor, edges int64 tensor [nnz,3] (src, ch, dst), wt dict of tensors."""
+    H = h0.shape[1]
+    src, ch, dst = edges[:, 0], edges[:, 1], edges[:, 2]
+    h = h0
+    Wg, bg, Wc, bc = wt["gru_gate_kernel"], wt["gru_gate_bias"], wt["gru_cand_kernel"], wt["gru_cand_bias"]
+    for _ in range(T):
+        x = torch.zeros_like(h)
+        if len(edges):
+            # m_j = h[src_j] @ W[ch_j] + b[ch_j]   (bias per edge)
+            m = torch.bmm(h[src].unsqueeze(1), wt["edge_weights"][ch]).squeeze(1)
+            if use_bias:
+                m = m + wt["edge_biases"].reshape(-1, H)[ch]
+            x = x.index_add(0, dst, m)
+        g = torch.sigmoid(torch.cat([x, h], 1) @ Wg + bg)
+        r, u = g[:, :H], g[:, H:]
+        c = torch.tanh(torch.cat([x, r * h], 1) @ Wc + bc)
+        h = u * h + (1 - u) * c
+    return h
+
+
+def grads(h0, edges, w, T, d_hT, use_bias=True, dtype=torch.float64):
+    """Returns (h_T, d_h0, {key: gradient}) as numpy, for L = sum(h_T * d_hT)."""
+    wt = {k: torch.tensor(np.asarray(w[k]), dtype=dtype, requires_grad=True) for k in KEYS if k in w}
+    if "edge_biases" not in wt:
+        use_bias = False
+    h0t = torch.tensor(np.asarray(h0), dtype=dtype, requires_grad=True)
+    e = torch.tensor(np.asarray(edges), dtype=torch.int64).reshape(-1, 3)
+    hT = forward_torch(h0t, e, wt, T, use_bias)
+    loss = (hT * torch.tensor(np.asarray(d_hT), dtype=dtype)).sum()
+    loss.backward()
+    out = {}
+    for k, t in wt.items():
+        g = t.grad if t.grad is not None else torch.zeros_like(t)
+        out[k] = g.detach().numpy()
+    return hT.detach().numpy(), h0t.grad.detach().numpy(), out

@@ -1,0 +1,101 @@
+"""GPU parity of the backward pass (BASELINE config 5) against the torch-CPU FP64 autograd oracle,
+through the C ABI (ggnn_propagate_* with GGNN_FLAG_SAVE_TAPE + ggnn_propagate_backward).
+
+Tolerance: strict FP32 arithmetic -> norm-wise max|g - ref| / max|ref| <= 2e-5 per gradient tensor
+(measured ~1e-6; float atomics make the summation order vary run to run)."""
+import numpy as np
+import pytest
+import torch
+
+import ggnn_b200
+from ggnn_b200 import Propagator, synth
+from oracle import ggnn_oracle as O
+from oracle import grad_oracle as G
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-5
+
+
+def _case(b, v, E, h, seed, lengths=None, bias=True):
+    tri = synth.random_trees(b, v - 1, E, seed=seed, lengths=lengths)
+    edges = synth.global_edge_list(tri, v, E)
+    w = O.make_weights(2 * E, h, seed)
+    if not bias:
+        w.pop("edge_biases")
+    rng = np.random.default_rng(seed + 1)
+    h0 = rng.uniform(-0.3, 0.3, (b * v, h)).astype(np.float32)
+    d = rng.standard_normal((b * v, h)).astype(np.float32)
+    return tri, edges, w, h0, d
+
+
+def _check(prop, w, hT, dh0, flat, ref):
+    rT, rh0, rg = ref
+    assert O.normwise_err(hT.cpu().numpy(), rT) <= 1e-5
+    assert O.normwise_err(dh0.cpu().numpy(), rh0) <= TOL
+    g = prop.split_grads(flat)
+    for k, r in rg.items():
+        got = g[k].cpu().numpy().reshape(r.shape)
+        if np.abs(r).max() == 0:
+            assert np.abs(got).max() == 0, k
+            continue
+        assert O.normwise_err(got, r) <= TOL, (k, O.normwise_err(got, r))
+    if "edge_biases" not in w:
+        pass  # dB segment is still produced (gradient of a zero bias); nothing to compare it with
+
+
+@pytest.mark.parametrize("b,v,E,h,T", [(4, 16, 5, 64, 3), (3, 32, 10, 100, 4), (2, 128, 46, 128, 2), (6, 24, 8, 400, 2)])
+def test_backward_edges(b, v, E, h, T):
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=b + T)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    _check(prop, w, hT, dh0, flat, G.grads(h0, edges.numpy(), w, T, d))
+
+
+def test_backward_dense_adjacency_ragged_no_bias_and_accumulation():
+    b, v, E, h, T = 5, 20, 6, 96, 3
+    lengths = torch.tensor([19, 3, 11, 1, 7])
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=9, lengths=lengths, bias=False)
+    adj = synth.dense_adjacency(tri, v, E).cuda()
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    hT = prop.propagate_dense(torch.from_numpy(h0).cuda().view(b, v, h), adj, num_timesteps=T, save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda().view(b, v, h))
+    ref = G.grads(h0, O.dense_to_edges(adj.cpu().numpy()), w, T, d)
+    _check(prop, w, hT.view(b * v, h), dh0.view(b * v, h), flat, ref)
+    # a second backward over the same tape accumulates into the same buffer: exactly doubles
+    _, flat2 = prop.backward(torch.from_numpy(d).cuda().view(b, v, h), flat.clone())
+    assert O.normwise_err(flat2.cpu().numpy(), 2 * flat.cpu().numpy()) <= 1e-5
+
+
+def test_backward_edge_cases():
+    w = O.make_weights(6, 32, 0)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    h0 = torch.rand(7, 32, device="cuda") - 0.5
+    d = torch.randn(7, 32, device="cuda")
+    with pytest.raises(RuntimeError):                      # no tape yet
+        prop.backward(d)
+    # no edges at all: GRU-only gradients
+    e0 = torch.zeros(0, 3, dtype=torch.int32, device="cuda")
+    hT = prop.propagate_edges(h0, e0, num_timesteps=2, save_tape=True)
+    dh0, flat = prop.backward(d)
+    ref = G.grads(h0.cpu().numpy(), np.zeros((0, 3), np.int64), w, 2, d.cpu().numpy())
+    _check(prop, w, hT, dh0, flat, ref)
+    # T = 0: identity
+    prop.propagate_edges(h0, e0, num_timesteps=0, save_tape=True)
+    dh0, flat = prop.backward(d)
+    assert torch.equal(dh0, d) and float(flat.abs().max()) == 0.0
+    # the tape is dropped by a non-tape call; TF32 cannot tape
+    prop.propagate_edges(h0, e0, num_timesteps=1)
+    with pytest.raises(RuntimeError):
+        prop.backward(d)
+    with pytest.raises(RuntimeError):
+        prop.propagate_edges(h0, e0, num_timesteps=1, precision="tf32", save_tape=True)
+
+
+def test_train_step_helper_single_process():
+    from ggnn_b200 import dist as gdist
+    tri, edges, w, h0, d = _case(3, 12, 4, 64, seed=2)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    dt = torch.from_numpy(d).cuda()
+    hT, dh0, flat = gdist.train_step(prop, torch.from_numpy(h0).cuda(), edges.cuda(), lambda hT: dt, 3)
+    _check(prop, w, hT, dh0, flat, G.grads(h0, edges.numpy(), w, 3, d))

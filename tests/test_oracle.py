@@ -149,3 +149,35 @@ def test_tf32_emulation_sets_the_tolerance():
     assert e_tf32 < 2e-3 < e_bf16
     assert np.array_equal(O.round_mantissa(np.float32([1.0, 1.0 + 2 ** -11, 1.0 + 3 * 2 ** -11])),
                           np.float32([1.0, 1.0, 1.0 + 2 ** -9]))
+
+
+def test_grad_oracle_forward_and_finite_differences():
+    """The autograd twin (oracle/grad_oracle.py) reproduces the forward oracle and its gradients
+    agree with central finite differences of the forward oracle."""
+    from oracle import grad_oracle as G
+    from ggnn_b200 import synth
+    b, v, E, h, T = 2, 6, 3, 8, 3
+    tri = synth.random_trees(b, v - 1, E, seed=3)
+    edges = synth.global_edge_list(tri, v, E).numpy()
+    w = O.make_weights(2 * E, h, 5)
+    rng = np.random.default_rng(0)
+    h0 = rng.uniform(-0.5, 0.5, (b * v, h))
+    d = rng.standard_normal((b * v, h))
+    hT, dh0, g = G.grads(h0, edges, w, T, d)
+    ref = O.propagate_edges(h0, edges, w, T)
+    assert np.abs(hT - ref).max() < 1e-12
+    loss = lambda ww, hh: float((O.propagate_edges(hh, edges, ww, T) * d).sum())
+    eps = 1e-6
+    for key, idx in (("edge_weights", (1, 2, 3)), ("edge_biases", (4, 0, 5)), ("gru_gate_kernel", (3, 9)),
+                     ("gru_gate_bias", (11,)), ("gru_cand_kernel", (12, 2)), ("gru_cand_bias", (7,))):
+        wp = {k: np.array(a, dtype=np.float64) for k, a in w.items()}
+        wm = {k: np.array(a, dtype=np.float64) for k, a in w.items()}
+        wp[key][idx] += eps
+        wm[key][idx] -= eps
+        fd = (loss(wp, h0) - loss(wm, h0)) / (2 * eps)
+        assert abs(fd - g[key][idx]) < 1e-6 * max(1.0, abs(fd)), (key, fd, g[key][idx])
+    hp, hm = h0.copy(), h0.copy()
+    hp[5, 2] += eps
+    hm[5, 2] -= eps
+    fd = (loss(w, hp) - loss(w, hm)) / (2 * eps)
+    assert abs(fd - dh0[5, 2]) < 1e-6 * max(1.0, abs(fd))
