@@ -279,6 +279,10 @@ def run_gpu(args):
             "gru_gates": ("tensor", steps_g * T * FLOP_GATES_PER_GRAPH_STEP / 1e12, "TFLOP/s", tf32_peak),
             "gru_cand": ("tensor", steps_g * T * FLOP_CAND_PER_GRAPH_STEP / 1e12, "TFLOP/s", tf32_peak),
         }
+        if st_ms.get("gru_cand", 0) == 0 and st_ms.get("gru_gates", 0) > 0:
+            # fused aggregation + GRU kernel: one launch does the gate and candidate contractions
+            b_, w_, u_, p_ = cand["gru_gates"]
+            cand["gru_gates"] = (b_, w_ + cand["gru_cand"][1], u_, p_)
         per_stage = {}
         for k, (bound, work, unit, peak) in cand.items():
             if st_ms.get(k, 0) > 0:
