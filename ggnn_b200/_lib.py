@@ -35,6 +35,8 @@ SIGNATURES = {
     "ggnn_propagate_edges": (_i, [_vp, _i, _vp, _vp, _i64, _i64, _i, _i, _u, _vp, _vp]),
     "ggnn_grad_floats": (_i64, [_vp]),
     "ggnn_propagate_backward": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "ggnn_embed_nodes": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "ggnn_heads_decode": (_i, [_vp, _vp, _vp, _i64, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "ggnn_workspace_bytes": (C.c_size_t, [_vp, _i64, _i64, _i, _i]),
     "ggnn_launch_count": (_i64, [_vp]),
     "ggnn_profile_enable": (_i, [_vp, _i]),

@@ -2,6 +2,7 @@
 #include "plan.cuh"
 #include "tf32.cuh"
 #include "train.cuh"
+#include "heads.cuh"
 
 #include <new>
 #include <stdlib.h>
@@ -424,6 +425,51 @@ extern "C" int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* 
   ws_alloc a(ext_of(ctx)->ar[3].p);
   ggnn_bwd_take_scratch(a, tape.plan, ctx->h, &sc);
   return ggnn_backward_fp32(ctx, tape, sc, d_hT, d_h0, grads, st);
+}
+
+// ---------------------------------------------------------------------------------------
+// N1 / N2: the rows either side of the path (evaluation mode)
+extern "C" int ggnn_embed_nodes(ggnn_ctx* ctx, const int32_t* idx, int64_t N, const float* loc_tab,
+                                int loc_rows, int loc_dim, const float* pos_tab, int pos_rows, int pos_dim,
+                                const float* word_tab, int word_rows, int word_dim, int h, float* h0,
+                                void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (N < 0 || h <= 0 || loc_dim < 0 || pos_dim < 0 || word_dim < 0 || loc_rows <= 0 || pos_rows <= 0 || word_rows <= 0)
+    GGNN_FAIL(ctx, GGNN_E_ARG, "embed_nodes: bad sizes");
+  if (2 * loc_dim + pos_dim + word_dim > h)
+    GGNN_FAIL(ctx, GGNN_E_SHAPE, "embed_nodes: embeddings (%d) wider than the hidden size %d (the reference pads with h - width zeros, chem_tensorflow_dense.py:304-306)",
+              2 * loc_dim + pos_dim + word_dim, h);
+  if (N > 0 && (!idx || !loc_tab || !pos_tab || !word_tab || !h0)) GGNN_FAIL(ctx, GGNN_E_ARG, "embed_nodes: null pointer");
+  if (N == 0) return GGNN_OK;
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  int* bad = reinterpret_cast<int*>(ctx->d_mail + 3);
+  GGNN_CUDA(ctx, cudaMemsetAsync(bad, 0, sizeof(int64_t), st));
+  GGNN_TRY(ggnn_embed_launch(ctx, idx, N, loc_tab, loc_rows, loc_dim, pos_tab, pos_rows, pos_dim, word_tab,
+                             word_rows, word_dim, h, h0, bad, st));
+  int64_t nbad = 0;
+  GGNN_TRY(read_i64(ctx, ctx->d_mail + 3, &nbad, st));
+  if (nbad) GGNN_FAIL(ctx, GGNN_E_ARG, "embed_nodes: %lld nodes have an index outside its embedding table", (long long)nbad);
+  return GGNN_OK;
+}
+
+extern "C" int ggnn_heads_decode(ggnn_ctx* ctx, const float* hT, const float* h0, int64_t N, int h,
+                                 const float* Wcat, const float* bcat, int ncat, int n_head, int n_lab,
+                                 int lab_off, const int32_t* n_active, int32_t* pred, float* p_head,
+                                 float* p_lab, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (N < 0 || h <= 0 || h % 4 || ncat <= 0 || ncat % 4 || n_head <= 0 || n_lab <= 0 || lab_off < n_head ||
+      lab_off % 4 || lab_off + n_lab > ncat)
+    GGNN_FAIL(ctx, GGNN_E_ARG, "heads_decode: bad sizes (h=%d ncat=%d n_head=%d n_lab=%d lab_off=%d)", h, ncat, n_head, n_lab, lab_off);
+  if (N > 0 && (!hT || !h0 || !Wcat || !bcat || !n_active || !pred)) GGNN_FAIL(ctx, GGNN_E_ARG, "heads_decode: null pointer");
+  if (N == 0) return GGNN_OK;
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  GGNN_TRY(arena_reserve(ctx, 3, (size_t)N * ncat * 4 + 256, st));
+  float* logits = reinterpret_cast<float*>(ext_of(ctx)->ar[3].p);
+  prof_scope ps(ctx, GGNN_STAGE_OTHER, st);
+  GGNN_TRY(ggnn_sgemm_concat(ctx, hT, h0, h, h, h, Wcat, bcat, ncat, N, logits, st));
+  return ggnn_decode_launch(ctx, logits, ncat, N, n_head, n_lab, lab_off, n_active, pred, p_head, p_lab, st);
 }
 
 extern "C" size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h) {

@@ -8,12 +8,13 @@
 //   CAND   c = tanh([acts, rh] @ Wc + bc);  h' = u*h + (1-u)*c
 #include "plan.cuh"
 #include "tc.cuh"
+#include "heads.cuh"
 
 namespace {
 
 constexpr int BM = 128, BN = 128, BK = 8, NT = 256;
 
-enum { MODE_MSG = 0, MODE_GATES = 1, MODE_CAND = 2 };
+enum { MODE_MSG = 0, MODE_GATES = 1, MODE_CAND = 2, MODE_PLAIN = 3 };
 
 struct sgemm_params {
   const float* A1;        // [*, lda] first K1 columns of A
@@ -156,7 +157,7 @@ sgemm_kernel(const sgemm_params p) {
         float4 bb = __ldg(reinterpret_cast<const float4*>(bias + n));
         v[0] += bb.x; v[1] += bb.y; v[2] += bb.z; v[3] += bb.w;
       }
-      if (MODE == MODE_MSG) {
+      if (MODE == MODE_MSG || MODE == MODE_PLAIN) {
         *reinterpret_cast<float4*>(p.out0 + row * p.N + n) = make_float4(v[0], v[1], v[2], v[3]);
       } else if (MODE == MODE_GATES) {
         float g[4];
@@ -231,6 +232,18 @@ int ggnn_aggregate(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float
   const int64_t threads = plan.N * 32;
   aggregate_kernel<<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(plan.tptr, plan.tmsg, msg,
                                                                       acts, plan.N, h, round_tf32 ? 1 : 0);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+int ggnn_sgemm_concat(ggnn_ctx* ctx, const float* A1, const float* A2, int K1, int K2, int lda,
+                      const float* B, const float* bias, int N, int64_t M, float* out, cudaStream_t st) {
+  if (M == 0 || N == 0) return GGNN_OK;
+  sgemm_params p{};
+  p.A1 = A1; p.A2 = A2; p.gather = nullptr; p.K1 = K1; p.K2 = K2; p.lda = lda;
+  p.Bmat = B; p.bias = bias; p.N = N; p.M = M; p.out0 = out; p.h = N;
+  dim3 grid((N + BN - 1) / BN, (unsigned)ceil_div64(M, BM));
+  sgemm_kernel<MODE_PLAIN><<<grid, NT, 0, st>>>(p);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

@@ -138,3 +138,26 @@ def bucket_size(max_node_id: int) -> int:
         if s > max_node_id:
             return s
     raise ValueError(f"node id {max_node_id} exceeds the reference's largest bucket (198)")
+
+
+def wsj_like_corpus(n_sentences: int, num_edge_types: int, num_out_labels: int, pos_size: int = 45,
+                    vocab: int = 5000, seed: int = 0, max_len: int = 140, agree: float = 0.8):
+    """Synthetic sentences in the reference's JSON record format (parser/to_graph.py:68-85): 'graph'
+    = input-bank tree as (head, label, word) triples, 'targets' = output-bank (head, label) per word
+    (agreeing with the input head with probability `agree`), 'node_features' = POS id per node (ROOT
+    first), 'words_index' = vocabulary id per node.  Lengths follow wsj_like_lengths."""
+    lengths = wsj_like_lengths(n_sentences, seed=seed, max_len=max_len)
+    tri = random_trees(n_sentences, int(lengths.max()), num_edge_types, seed=seed, lengths=lengths)
+    alt = random_trees(n_sentences, int(lengths.max()), num_out_labels + 1, seed=seed + 1, lengths=lengths)
+    g = torch.Generator().manual_seed(seed + 2)
+    recs = []
+    for i in range(n_sentences):
+        n = int(lengths[i])
+        graph = tri[i, :n].tolist()
+        keep = torch.rand(n, generator=g) < agree
+        targets = [[graph[j][0] if keep[j] else alt[i, j, 0].item(), int(alt[i, j, 1])] for j in range(n)]
+        recs.append({"graph": graph, "targets": targets,
+                     "node_features": torch.randint(0, pos_size, (n + 1,), generator=g).tolist(),
+                     "words_index": torch.randint(0, vocab, (n + 1,), generator=g).tolist(),
+                     "id": i})
+    return recs

@@ -134,6 +134,28 @@ int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0,
 int64_t ggnn_grad_floats(const ggnn_ctx* ctx);
 int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* d_h0, float* grads, void* stream);
 
+/* "Next" rows either side of the path, evaluation mode --------------------
+ * N1: get_initial_node_representation (chem_tensorflow_dense.py:264-310).  idx int32 [N, 4] =
+ *     (loc, pos, word, head_loc) -- columns 0-3 of the reference's word_inputs (:825-842);
+ *     h0[n] = concat(loc_tab[loc] | pos_tab[pos] | word_tab[word] | loc_tab[head_loc]) zero-padded
+ *     to h.  An index outside its table is GGNN_E_ARG.  Synchronises `stream` once.
+ * N2: gated_regression, btb branch (:439-505) + masks (:633-661) + decode (:106-131):
+ *     logits = [hT | h0] @ Wcat + bcat with Wcat [2h, ncat] holding the head-position layer in
+ *     columns [0, n_head) and the label layer in [lab_off, lab_off + n_lab) (ncat, lab_off % 4 == 0,
+ *     padding columns zero); softmax per group; n_active [N] = number of active nodes of the row's
+ *     graph for an active row, 0 for a padded row; pred [N, 2] = (first arg-max head position among
+ *     s < n_active, first arg-max label), -1 for padded rows.  p_head [N, n_head] / p_lab [N, n_lab]
+ *     (optional) receive the masked probabilities.  No synchronisation. */
+int ggnn_embed_nodes(ggnn_ctx* ctx, const int32_t* idx, int64_t N,
+                     const float* loc_tab, int loc_rows, int loc_dim,
+                     const float* pos_tab, int pos_rows, int pos_dim,
+                     const float* word_tab, int word_rows, int word_dim,
+                     int h, float* h0, void* stream);
+int ggnn_heads_decode(ggnn_ctx* ctx, const float* hT, const float* h0, int64_t N, int h,
+                      const float* Wcat, const float* bcat, int ncat, int n_head, int n_lab, int lab_off,
+                      const int32_t* n_active, int32_t* pred, float* p_head_or_null, float* p_lab_or_null,
+                      void* stream);
+
 /* bytes of ctx-owned scratch a propagate call of this size will hold */
 size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h);
 

@@ -181,3 +181,63 @@ def test_grad_oracle_forward_and_finite_differences():
     hm[5, 2] -= eps
     fd = (loss(w, hp) - loss(w, hm)) / (2 * eps)
     assert abs(fd - dh0[5, 2]) < 1e-6 * max(1.0, abs(fd))
+
+
+def test_parser_oracle_pinned_by_reference_decode(golden_dir):
+    """masks, target formatting, decode and LAS/UAS against the reference's own NumPy code
+    (tests/golden/parser_decode.npz, scripts/make_golden_parser.py), incl. first-maximum ties."""
+    from oracle import parser_oracle as P
+    d = np.load(os.path.join(golden_dir, "parser_decode.npz"))
+    E_out, Osz = int(d["E_out"]), int(d["O"])
+    for ci in range(3):
+        v = int(d[f"c{ci}_v"])
+        na, tg = d[f"c{ci}_n_active"], d[f"c{ci}_targets"]
+        masks = np.stack([P.get_mask(int(n), v, E_out, Osz) for n in na])
+        masks_e = np.stack([P.get_mask(int(n), v, E_out, Osz, is_edge=True) for n in na])
+        assert np.array_equal(masks.astype(np.float32), d[f"c{ci}_mask"])
+        assert np.array_equal(masks_e.astype(np.float32), d[f"c{ci}_mask_edges"])
+        labels = [P.target_to_adj_mat([list(t) for t in tg[g][: na[g] - 1]], v, E_out, v) for g in range(len(na))]
+        tv, tve = P.target_values(labels, Osz), P.target_values_edges(labels)
+        assert np.array_equal(tv.astype(np.float32), d[f"c{ci}_target_values"])
+        assert np.array_equal(tve.astype(np.float32), d[f"c{ci}_target_values_edges"])
+        b = len(na)
+        scores, _ = P.score_batch(tv, d[f"c{ci}_ph"].reshape(b, -1), masks, tve, d[f"c{ci}_pe"].reshape(b, -1),
+                                  masks_e, v, E_out, Osz)
+        assert np.allclose(scores.mean(0), d[f"c{ci}_scores"], rtol=0, atol=1e-15)
+    wi = np.zeros((2, 6)); wi[0, :3] = [3, 1, 2]; wi[1, :1] = [5]
+    assert np.array_equal(wi, d["word_inputs_padded"])
+
+
+def test_host_scorer_and_batch_builder_match_the_oracle(golden_dir):
+    """ggnn_b200.parser_eval's vectorised scorer == the reference-shaped decode+scorer, and its
+    batch builder == graph_to_adj_mat_bd / the reference's word_inputs columns."""
+    from oracle import parser_oracle as P
+    from ggnn_b200 import parser_eval as PE, synth
+    d = np.load(os.path.join(golden_dir, "parser_decode.npz"))
+    E_out, Osz = int(d["E_out"]), int(d["O"])
+    for ci in range(3):
+        v, na, tg = int(d[f"c{ci}_v"]), d[f"c{ci}_n_active"], d[f"c{ci}_targets"]
+        b = len(na)
+        ph, pe = d[f"c{ci}_ph"], d[f"c{ci}_pe"]
+        pred = np.full((b, v, 2), -1, np.int32)
+        targets = np.full((b, v, 2), -1, np.int32)
+        for g in range(b):
+            n = int(na[g])
+            pred[g, :n, 0] = ph[g, :n, :n].argmax(-1)      # first maximum among s < n_active
+            pred[g, :n, 1] = pe[g, :n].argmax(-1) + 1
+            targets[g, 1:n] = tg[g, : n - 1]
+        per = PE.las_uas(pred, targets, na)
+        assert np.allclose(per.mean(0), d[f"c{ci}_scores"], rtol=0, atol=1e-15)
+    E = 6
+    recs = synth.wsj_like_corpus(12, E, 5, pos_size=9, vocab=50, seed=4, max_len=20)
+    for v, items in PE.make_batches(recs, batch_size=5):
+        idx, edges, n_active, targets = PE.batch_arrays(v, items, E)
+        adj = PE.dense_adjacency_from_edges(edges, len(items), v, 2 * E)
+        for g, r in enumerate(items):
+            assert v == synth.bucket_size(max(max(e[0], e[2]) for e in r["graph"]))
+            assert np.array_equal(adj[g], O.graph_to_adj_mat_bd(r["graph"], v, E).astype(np.float32))
+            n = len(r["node_features"])
+            assert n_active[g] == n and list(idx[g, :n, 0]) == list(range(n))
+            assert list(idx[g, :n, 1]) == r["node_features"] and list(idx[g, :n, 2]) == r["words_index"]
+            assert list(idx[g, :n, 3]) == [0] + [e[0] for e in r["graph"]]
+            assert np.array_equal(targets[g, 1:n], np.array(r["targets"]))
