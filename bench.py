@@ -418,6 +418,93 @@ def run_c5(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------
+# secondary workload: BASELINE config 4 (large graphs through the edge-list path)
+# ---------------------------------------------------------------------------------------
+def run_c4(args):
+    import torch.distributed as dist
+    import ggnn_b200
+    from ggnn_b200 import synth
+    from oracle import ggnn_oracle as O
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    Vn, CH, BASE, Hc, Tc = 4096, 8, 32768, 256, 8
+    per_gpu = args.c4_graphs
+    wd = O.make_weights(CH, Hc, 0)
+    prop = ggnn_b200.Propagator(ggnn_b200.from_dict(wd), dev)
+    edges = synth.random_multigraph(per_gpu, Vn, BASE, CH // 2, seed=1000 + rank).to(dev)
+    gen = torch.Generator(device=dev).manual_seed(1 + rank)
+    h0 = (torch.rand(per_gpu * Vn, Hc, device=dev, generator=gen) - 0.5) * 0.2
+    out = torch.empty_like(h0)
+
+    def step():
+        prop.propagate_edges(h0, edges, num_timesteps=Tc, precision=args.precision, out=out)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    prop.profile(True)
+    l0 = prop.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = prop.launches - l0
+    stages = prop.profile_read()
+    if world > 1:
+        tms = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    ms_per_step = ms / args.steps
+    if rank == 0:
+        flop_graph = Tc * (min(2 * BASE, Vn * CH) * 2 * Hc * Hc + Vn * 12 * Hc * Hc)     # 60.13 GFLOP
+        val = per_gpu * world / (ms_per_step * 1e-3)
+        line = {"metric": "GGNN propagation graphs/sec (T=8 steps)", "value": val, "unit": "graphs/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32" if args.precision == "fp32" else "tf32-in/f32-acc", "data": "synthetic",
+                "config": {"workload": "C4 synthetic large graphs v=4096, 8 channels, nnz=65536/graph, h=256, T=8, edge-list path",
+                           "graphs_per_gpu": per_gpu, "precision": args.precision},
+                "node_updates_per_s": val * Vn * Tc,
+                "achieved_tflops_algorithmic_per_gpu": flop_graph * per_gpu / (ms_per_step * 1e-3) / 1e12,
+                "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items() if v[0] > 0},
+                "clocks": clocks, "gpu_launches": int(launches)}
+        if world == 1 and not args.no_cpu:
+            from oracle import cpu_reference as R
+            torch.set_num_threads(os.cpu_count() or 1)
+            n = 2
+            ec = synth.random_multigraph(n, Vn, BASE, CH // 2, seed=7)
+            hc = (torch.rand(n * Vn, Hc) - 0.5) * 0.2
+            with torch.no_grad():
+                t0 = time.perf_counter()
+                R.propagate_edges_torch_cpu(hc, ec, wd, Tc)
+                dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": n / dt, "unit": "graphs/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"{n} C4 graphs, torch-CPU FP32 edge-list restatement"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -430,14 +517,17 @@ def main():
     ap.add_argument("--e2e-graphs", type=int, default=256)
     ap.add_argument("--ref-graphs", type=int, default=64, help="graphs per step of the CPU reference arm")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--workload", default="c3", choices=["c3", "c5"],
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c3 = the headline forward benchmark; c5 = training step (secondary line)")
+    ap.add_argument("--c4-graphs", type=int, default=64, help="graphs per GPU of the c4 workload")
     ap.add_argument("--c5-graphs", type=int, default=2048, help="graphs per GPU of the c5 workload")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "c5":
         run_c5(args)
+    elif args.workload == "c4":
+        run_c4(args)
     else:
         run_gpu(args)
 
