@@ -267,6 +267,45 @@ def run_gpu(args):
            "note": "ggnn_b200.compute_final_node_representations on pinned host tensors: dense "
                    "FP32 adjacency (6.03 MB/graph, the reference's feed format) + states H2D, result D2H"}
 
+    # same graphs handed over as (src, channel, dst) triples: no dense adjacency on the bus
+    edges_host = synth.global_edge_list(tri[:ne].cpu(), V, E).pin_memory()
+    h0_flat = h0_host.view(ne * V, H)
+    for _ in range(2):
+        ggnn_b200.compute_final_node_representations_sparse(h0_flat, edges_host, weights=prop,
+                                                            num_timesteps=T, precision=precision)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res2 = ggnn_b200.compute_final_node_representations_sparse(h0_flat, edges_host, weights=prop,
+                                                                   num_timesteps=T, precision=precision)
+    torch.cuda.synchronize()
+    e2e_edges_s = (time.perf_counter() - t0) / args.steps
+    e2e_edges = {"value": ne / e2e_edges_s, "unit": "graphs/s (this rank)",
+                 "h2d_bytes_per_step": int(edges_host.numel() * 4 + h0_flat.numel() * 4),
+                 "d2h_bytes_per_step": int(res2.numel() * 4), "graphs_per_step": ne,
+                 "note": "compute_final_node_representations_sparse on pinned host tensors: edge list "
+                         "(6 KB/graph) + states H2D, result D2H"}
+
+    # strict-FP32 mode of the same workload (one pass over this rank's graphs), for the record
+    fp32_strict = None
+    if precision != "fp32" and not args.no_fp32:
+        prop.propagate_dense(h0[:pool], adj[:pool], num_timesteps=T, precision="fp32", out=out[:pool])
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for c in range(0, graphs_rank, pool):
+            n = min(pool, graphs_rank - c)
+            prop.propagate_dense(h0[c:c + n], adj[:n], num_timesteps=T, precision="fp32", out=out[c:c + n])
+        f1.record()
+        barrier()
+        fms = f0.elapsed_time(f1)
+        if world > 1:
+            tf_ = torch.tensor([fms], device=dev, dtype=torch.float64)
+            dist.all_reduce(tf_, op=dist.ReduceOp.MAX)
+            fms = float(tf_.item())
+        fp32_strict = {"value": args.graphs / (fms * 1e-3), "unit": "graphs/s", "ms_per_step": fms, "steps": 1,
+                       "note": "GGNN_PREC_FP32 (<= 1e-5 norm-wise vs the FP64 oracle), same inputs"}
+
     if rank == 0:
         steps_g = args.steps * graphs_rank                 # graph passes timed on this rank
         st_ms = {k: v[0] for k, v in stages.items()}
@@ -312,7 +351,8 @@ def run_gpu(args):
                        "parallelism": f"graph-sharded x{world}, no forward collective",
                        "cache": "inputs (>=24 GB per pass) far exceed the 126 MB L2; no flush needed"},
             "node_updates_per_s": value * V * T,
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks, "e2e": e2e, "e2e_edges": e2e_edges, "fp32_strict": fp32_strict,
+            "gpu_launches": int(launches),
             "roofline": roofline, "stages": per_stage,
         }
         if world == 1 and not args.no_cpu:
@@ -517,6 +557,7 @@ def main():
     ap.add_argument("--e2e-graphs", type=int, default=256)
     ap.add_argument("--ref-graphs", type=int, default=64, help="graphs per step of the CPU reference arm")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the strict-FP32 pass of the c3 workload")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c3 = the headline forward benchmark; c5 = training step (secondary line)")
     ap.add_argument("--c4-graphs", type=int, default=64, help="graphs per GPU of the c4 workload")
