@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libggnn_b200.so")
 
 OK, E_ARG, E_SHAPE, E_CAPACITY, E_CUDA, E_UNSUPPORTED, E_STATE = 0, -1, -2, -3, -4, -5, -6
 ADJ_F32, ADJ_U8 = 0, 1
-PREC_FP32, PREC_TF32 = 0, 1
+PREC_FP32, PREC_TF32, PREC_F16 = 0, 1, 2
 SLOT_MAIN, SLOT_FIXED = 0, 1
 FLAG_SAVE_TAPE = 2
 STAGES = ("compact_mask", "compact_rest", "plan", "msg", "agg", "gru_gates", "gru_cand", "other")

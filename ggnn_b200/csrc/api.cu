@@ -3,6 +3,7 @@
 #include "tf32.cuh"
 #include "train.cuh"
 #include "heads.cuh"
+#include "f16.cuh"
 
 #include <new>
 #include <stdlib.h>
@@ -17,9 +18,9 @@ struct arena {
 // Two grow-only arenas per ctx: [0] compaction (bitmask, rowptr, scan), [1] col + plan + step
 // buffers.  They are separate because [1] is sized only after the edge count is known and
 // must not move [0].
-// [2] training tape (per-step activations), [3] backward scratch.
+// [2] training tape (per-step activations), [3] backward scratch, [4] FP16 node states.
 struct ctx_ext {
-  arena ar[4];
+  arena ar[5];
   ggnn_tape tape;
 };
 
@@ -101,8 +102,11 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
     free_dev(c, c->edge[s].W);
     free_dev(c, c->edge[s].B);
     free_dev(c, c->edge[s].Wt_tf32);
+    if (c->edge[s].Wt_f16) { cudaFree(c->edge[s].Wt_f16); c->edge[s].Wt_f16 = nullptr; }
   }
   free_dev(c, c->Wg); free_dev(c, c->bg); free_dev(c, c->Wc); free_dev(c, c->bc);
+  if (c->Wgt_f16) cudaFree(c->Wgt_f16);
+  if (c->Wct_f16) cudaFree(c->Wct_f16);
   free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
   if (c->ws) {
     ctx_ext* e = ext_of(c);
@@ -183,6 +187,7 @@ extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const
     ctx->gru_set = true;
   }
   GGNN_TRY(ggnn_tf32_pack_weights(ctx, slot, has_gru, st));
+  GGNN_TRY(ggnn_f16_pack_weights(ctx, slot, has_gru, st));
   ew.set = true;
   return GGNN_OK;
 }
@@ -214,16 +219,47 @@ namespace {
 int check_ready(ggnn_ctx* ctx, int slot, int precision) {
   if (slot < 0 || slot >= GGNN_MAX_SLOTS) GGNN_FAIL(ctx, GGNN_E_ARG, "bad weight slot %d", slot);
   if (!ctx->gru_set || !ctx->edge[slot].set) GGNN_FAIL(ctx, GGNN_E_STATE, "weights for slot %d not set", slot);
-  if (precision != GGNN_PREC_FP32 && precision != GGNN_PREC_TF32) GGNN_FAIL(ctx, GGNN_E_ARG, "bad precision %d", precision);
+  if (precision != GGNN_PREC_FP32 && precision != GGNN_PREC_TF32 && precision != GGNN_PREC_F16)
+    GGNN_FAIL(ctx, GGNN_E_ARG, "bad precision %d", precision);
+  if (precision == GGNN_PREC_F16 && !ggnn_f16_supported(ctx))
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "F16 path needs a hidden size in (96, 128], got h=%d", ctx->h);
   if (precision == GGNN_PREC_TF32 && !ggnn_tf32_supported(ctx))
     GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "TF32 path does not support h=%d", ctx->h);
   return GGNN_OK;
 }
 
+// read one slot of the device mailbox; the whole mailbox (8 slots) comes back with it so the
+// FP16 range statistics (slots 4-6) ride on the same synchronisation
 int read_i64(ggnn_ctx* ctx, const int64_t* dev, int64_t* out, cudaStream_t st) {
-  GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->h_mail, dev, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->h_mail, ctx->d_mail, 8 * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   GGNN_CUDA(ctx, cudaStreamSynchronize(st));
-  *out = ctx->h_mail[0];
+  *out = ctx->h_mail[dev - ctx->d_mail];
+  return GGNN_OK;
+}
+
+// GGNN_PREC_F16: before the planning synchronisation, convert the states to FP16 and collect
+// max|h0| (slot 6) and, once per weight set, max|W| / max|B| (slots 4, 5)
+int f16_prologue(ggnn_ctx* ctx, int slot, const float* h0, int64_t N, cudaStream_t st) {
+  GGNN_TRY(arena_reserve(ctx, 4, (size_t)N * 256 + 256, st));
+  GGNN_CUDA(ctx, cudaMemsetAsync(ctx->d_mail + 4, 0, 3 * sizeof(int64_t), st));
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  if (ew.absmax_w < 0.f) {
+    GGNN_TRY(ggnn_absmax(ctx, ew.W, (int64_t)ctx->two_e * ctx->h * ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 4), st));
+    if (ew.B) GGNN_TRY(ggnn_absmax(ctx, ew.B, (int64_t)ctx->two_e * ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 5), st));
+  }
+  return ggnn_f16_state_in(ctx, h0, ext_of(ctx)->ar[4].p, N, reinterpret_cast<unsigned*>(ctx->d_mail + 6), st);
+}
+
+// after the synchronisation: refuse inputs that could leave the FP16 range (include/ggnn_b200.h)
+int f16_check(ggnn_ctx* ctx, int slot) {
+  auto f = [&](int i) { unsigned u = (unsigned)ctx->h_mail[i]; float v; memcpy(&v, &u, 4); return v; };
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  if (ew.absmax_w < 0.f) { ew.absmax_w = f(4); ew.absmax_b = f(5); }
+  const float hmax = f(6);
+  const float bound = ctx->h * ew.absmax_w * (hmax > 1.f ? hmax : 1.f) + ew.absmax_b;
+  if (!(bound < 64.f))
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "F16 mode: h*max|W|*max(max|h0|,1)+max|B| = %g >= 64 (max|W|=%g max|h0|=%g): values may leave the FP16 range; use GGNN_PREC_TF32",
+              bound, ew.absmax_w, hmax);
   return GGNN_OK;
 }
 
@@ -254,6 +290,11 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
       GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, tb, h_state, st));
     }
     tape.valid = true;
+    return GGNN_OK;
+  }
+  if (precision == GGNN_PREC_F16) {           // states already converted by f16_prologue (arena 4)
+    for (int t = 0; t < T; ++t)
+      GGNN_TRY(ggnn_step_f16(ctx, slot, plan, sb.msg, ext_of(ctx)->ar[4].p, h_state, t == T - 1, st));
     return GGNN_OK;
   }
   if (precision == GGNN_PREC_TF32 && T > 0)   // state is kept TF32-rounded between steps
@@ -333,9 +374,11 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
     GGNN_TRY(arena_reserve(ctx, 0, rp_bytes + ggnn_compact_tmp_bytes(rows * v, rows), st));
     int32_t* rowptr = reinterpret_cast<int32_t*>(ext_of(ctx)->ar[0].p);
     char* tmp = ext_of(ctx)->ar[0].p + rp_bytes;
+    if (precision == GGNN_PREC_F16) GGNN_TRY(f16_prologue(ctx, slot, h_out + (size_t)g0 * v * h, bc * v, st));
     GGNN_TRY(ggnn_compact_count(ctx, adj_c, adj_dtype, rows, v, rowptr, ctx->d_mail, tmp, st));
     int64_t nnz = 0;
     GGNN_TRY(read_i64(ctx, ctx->d_mail, &nnz, st));     // the one planning sync
+    if (precision == GGNN_PREC_F16) GGNN_TRY(f16_check(ctx, slot));
     if (nnz >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "chunk has %lld edges", (long long)nnz);
     // arena 1: [col][plan][step buffers]
     const size_t col_bytes = align_up((size_t)(nnz + 1) * 4, 256);
@@ -362,6 +405,12 @@ extern "C" int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0, cons
   cudaStream_t st = (cudaStream_t)stream;
   if (h_out != h0)
     GGNN_CUDA(ctx, cudaMemcpyAsync(h_out, h0, (size_t)b * v * ctx->h * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  if (precision == GGNN_PREC_F16) {
+    int64_t dummy = 0;
+    GGNN_TRY(f16_prologue(ctx, slot, h_out, (int64_t)b * v, st));
+    GGNN_TRY(read_i64(ctx, ctx->d_mail, &dummy, st));
+    GGNN_TRY(f16_check(ctx, slot));
+  }
   // nnz = rowptr[rows]
   GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->h_mail + 1, rowptr + rows, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   GGNN_CUDA(ctx, cudaStreamSynchronize(st));
@@ -384,6 +433,7 @@ extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, co
   cudaStream_t st = (cudaStream_t)stream;
   if (h_out != h0)
     GGNN_CUDA(ctx, cudaMemcpyAsync(h_out, h0, (size_t)N * ctx->h * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  if (precision == GGNN_PREC_F16) GGNN_TRY(f16_prologue(ctx, slot, h_out, N, st));
   ggnn_plan plan;
   ggnn_step_bufs sb;
   {
@@ -398,6 +448,7 @@ extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, co
   int64_t bad = 0;
   GGNN_TRY(read_i64(ctx, ctx->d_mail + 2, &bad, st));   // planning sync: edge validation result
   if (bad) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: %lld edges have node or channel ids out of range", (long long)bad);
+  if (precision == GGNN_PREC_F16) GGNN_TRY(f16_check(ctx, slot));
   return run_steps(ctx, slot, plan, sb, h_out, T, precision, flags, st);
 }
 

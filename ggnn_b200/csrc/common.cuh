@@ -17,6 +17,10 @@ struct ggnn_edge_weights {
   float* W = nullptr;      // [two_e, h, h]  FP32, reference layout (K rows, N cols)
   float* B = nullptr;      // [two_e, h] or nullptr
   float* Wt_tf32 = nullptr;// [two_e, hp, hp] TF32-rounded, transposed ([n][k]), zero padded to hp
+  void*  Wt_f16 = nullptr; // [two_e, 128, 128] FP16, transposed ([n][k]), zero padded (hp == 128 only)
+  CUtensorMap tm_Wt16;     // TMA view of Wt_f16 as [two_e*128 rows, 128 cols], box 64 x 128
+  float  absmax_w = -1.f;  // max|W|, max|B| of this slot (host copy, < 0 = not computed yet)
+  float  absmax_b = 0.f;
   CUtensorMap tm_Wt;       // TMA view of Wt_tf32 as [two_e*hp rows, hp cols], box 32 x tm_rows
   int    tm_rows = 0;
   bool   set = false;
@@ -36,6 +40,9 @@ struct ggnn_ctx {
   float* bc = nullptr;     // [h]
   float* Wgt_tf32 = nullptr; // [2hp, 2hp] transposed + padded + TF32-rounded
   float* Wct_tf32 = nullptr; // [hp, 2hp]
+  void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
+  void* Wct_f16 = nullptr;   // [128, 256]
+  CUtensorMap tm_Wg16, tm_Wc16;
   CUtensorMap tm_Wg, tm_Wc, tm_Wg256;  // TMA views of the packed GRU kernels (256-row box: fused kernel)
   unsigned long long* dbg_trace = nullptr;   // device buffer for kernel phase traces (ggnn_debug_trace)
   bool   no_fused = false;   // debugging / A-B switch (GGNN_NO_FUSED=1)

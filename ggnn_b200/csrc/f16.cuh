@@ -1,0 +1,18 @@
+// f16.cuh -- GGNN_PREC_F16 timestep (tcgen05 kind::f16, FP16 operands in 16-bit containers,
+// FP32 accumulate), hidden size padded to 128: declarations.
+#pragma once
+#include "plan.cuh"
+
+bool ggnn_f16_supported(const ggnn_ctx* ctx);
+// pack the weights of `slot` (and the GRU cell) into K-major FP16 tiles + TMA maps
+int ggnn_f16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st);
+// state16 [N, 128] FP16 = h [N, h] FP32 rounded to nearest, columns >= h zero; max|h| is
+// atomicMax-ed (as float bits) into *absmax_bits when given
+int ggnn_f16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, unsigned* absmax_bits,
+                      cudaStream_t st);
+// max|x| over n floats, accumulated into *out_bits (float bits, atomicMax; caller zeroes)
+int ggnn_absmax(ggnn_ctx* ctx, const float* x, int64_t n, unsigned* out_bits, cudaStream_t st);
+// one timestep: msg16 [max_tiles*128, 128] FP16 scratch; state16 in/out; on the last step the
+// unrounded FP32 state is also written to h_out [N, h]
+int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16,
+                  float* h_out, bool last_step, cudaStream_t st);

@@ -14,7 +14,7 @@ import torch
 from . import _lib
 from .weights import GGNNWeights, as_weights
 
-_PREC = {"fp32": _lib.PREC_FP32, "tf32": _lib.PREC_TF32}
+_PREC = {"fp32": _lib.PREC_FP32, "tf32": _lib.PREC_TF32, "f16": _lib.PREC_F16}
 
 
 def _ptr(t: Optional[torch.Tensor]):

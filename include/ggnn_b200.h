@@ -52,6 +52,11 @@ extern "C" {
 /* arithmetic mode of the message / GRU contractions */
 #define GGNN_PREC_FP32  0   /* strict: FP32 FFMA, <= 1e-5 norm-wise vs the FP64 oracle  */
 #define GGNN_PREC_TF32  1   /* tcgen05 kind::tf32, FP32 accumulate, <= 2e-3 norm-wise   */
+#define GGNN_PREC_F16   2   /* tcgen05 kind::f16: operands rounded to FP16 (the same 11-bit significand
+                             * as TF32) and held in 16-bit containers, FP32 accumulate, FP32 gate math,
+                             * FP32 result; <= 2e-3 norm-wise.  Hidden size <= 128.  Needs
+                             * h*max|W|*max(max|h0|,1) + max|B| < 64 so nothing leaves the FP16 range;
+                             * otherwise the call returns GGNN_E_UNSUPPORTED (use GGNN_PREC_TF32).    */
 
 /* weight slot: 0 = edge_weights / edge_biases (chem_tensorflow_dense.py:202-206),
  *              1 = edge_weights_fixed / edge_biases_fixed (:208-212), used when the

@@ -1,0 +1,103 @@
+"""GPU parity of GGNN_PREC_F16 (tcgen05 kind::f16: FP16 operands -- the TF32 significand in 16-bit
+containers -- FP32 accumulate, FP32 result) against the FP64 oracle, through the C ABI.
+Tolerance: the north_star's reduced-precision bound, <= 2e-3 norm-wise."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import ggnn_b200
+from ggnn_b200 import Propagator, synth, weights as W
+from oracle import ggnn_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-3
+
+
+def _h0(b, v, h, seed=1):
+    return np.random.default_rng(seed).uniform(-0.1, 0.1, (b, v, h)).astype(np.float32)
+
+
+def _trees(b, v, E, seed, lengths=None):
+    tri = synth.random_trees(b, v - 1, E, seed=seed, lengths=lengths)
+    return tri, synth.dense_adjacency(tri, v, E).numpy()
+
+
+def test_c1_small_dev(golden_dir):
+    adj = np.load(os.path.join(golden_dir, "c1_small_dev.npz"))["adj"]
+    w = O.make_weights(10, 100, 0)
+    h0 = _h0(3, 6, 100)
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=4, precision="f16")
+    assert out.shape == (3, 6, 100) and out.dtype == np.float32
+    assert O.normwise_err(out, O.propagate_dense(h0, adj, w, 4)) <= TOL
+
+
+@pytest.mark.parametrize("b,v,E,h,T", [(8, 32, 10, 128, 8), (3, 128, 46, 128, 8), (5, 16, 6, 100, 4),
+                                       (300, 128, 46, 128, 8), (7, 30, 12, 124, 1)])
+def test_random_trees(b, v, E, h, T):
+    _, adj = _trees(b, v, E, seed=b + v)
+    w = O.make_weights(2 * E, h, 0)
+    h0 = _h0(b, v, h)
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=T, precision="f16")
+    err = O.normwise_err(out, O.propagate_dense(h0, adj, w, T))
+    assert err <= TOL, err
+
+
+def test_matches_tf32_mode_closely_and_is_reproducible():
+    """Same 11-bit operand significand as TF32: the two modes agree far inside the tolerance."""
+    _, adj = _trees(16, 64, 20, seed=3)
+    w = O.make_weights(40, 128, 1)
+    h0 = _h0(16, 64, 128)
+    f = lambda p: ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=8, precision=p)
+    a, b_, t = f("f16"), f("f16"), f("tf32")
+    assert np.array_equal(a, b_)                       # fixed summation order, no atomics
+    assert O.normwise_err(a, t) <= 1e-3
+
+
+def test_ragged_general_graphs_fixed_ts_no_bias_and_paths_agree():
+    lengths = torch.tensor([31, 2, 1, 17, 9, 30])
+    tri, adj = _trees(6, 32, 8, seed=4, lengths=lengths)
+    w = O.make_weights(16, 128, 2)
+    w2 = O.make_weights(16, 128, 102)
+    w["edge_weights_fixed"], w["edge_biases_fixed"] = w2["edge_weights"], w2["edge_biases"]
+    h0 = _h0(6, 32, 128)
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=4, precision="f16")
+    assert O.normwise_err(out, O.propagate_dense(h0, adj, w, 4)) <= TOL
+    out1 = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, fixed_ts=1, precision="f16")
+    assert O.normwise_err(out1, O.propagate_dense(h0, adj, w, 1, fixed_ts=1)) <= TOL
+    # dense / csr / edge-list paths give bit-identical results
+    prop = Propagator(W.from_dict(w), "cuda:0")
+    d_h0, d_adj = torch.from_numpy(h0).cuda(), torch.from_numpy(adj).cuda()
+    dense = prop.propagate_dense(d_h0, d_adj, num_timesteps=4, precision="f16")
+    rowptr, col, _ = prop.compact_adjacency(d_adj)
+    assert torch.equal(dense, prop.propagate_csr(d_h0, rowptr, col, num_timesteps=4, precision="f16"))
+    edges = synth.global_edge_list(tri, 32, 8).cuda()
+    sp = prop.propagate_edges(d_h0.view(-1, 128), edges, num_timesteps=4, precision="f16").view(6, 32, 128)
+    assert torch.equal(dense, sp)
+    # any 0/1 adjacency, no bias, no edges, T = 0
+    rng = np.random.default_rng(5)
+    adjg = (rng.random((3, 6, 20, 20)) < 0.15).astype(np.float32)
+    wn = O.make_weights(6, 128, 1)
+    wn.pop("edge_biases")
+    hg = _h0(3, 20, 128)
+    og = ggnn_b200.compute_final_node_representations(hg, adjg, weights=wn, num_timesteps=3, precision="f16")
+    assert O.normwise_err(og, O.propagate_dense(hg, adjg, wn, 3, use_bias=False)) <= TOL
+    z = np.zeros((3, 6, 20, 20), np.float32)
+    oz = ggnn_b200.compute_final_node_representations(hg, z, weights=wn, num_timesteps=2, precision="f16")
+    assert O.normwise_err(oz, O.propagate_dense(hg, z, wn, 2, use_bias=False)) <= TOL
+    o0 = ggnn_b200.compute_final_node_representations(hg, z, weights=wn, num_timesteps=0, precision="f16")
+    assert np.array_equal(o0, hg)
+
+
+def test_range_guard_and_unsupported_hidden_size():
+    w = O.make_weights(6, 128, 0)
+    _, adj = _trees(2, 8, 3, seed=0)
+    big = _h0(2, 8, 128) * 1e4                         # |h0| ~ 1e3 -> products could leave the FP16 range
+    with pytest.raises(RuntimeError, match="FP16 range"):
+        ggnn_b200.compute_final_node_representations(big, adj, weights=w, num_timesteps=2, precision="f16")
+    out = ggnn_b200.compute_final_node_representations(big, adj, weights=w, num_timesteps=2, precision="tf32")
+    assert np.isfinite(out).all()
+    w64 = O.make_weights(6, 64, 0)
+    with pytest.raises(RuntimeError, match="hidden size"):
+        ggnn_b200.compute_final_node_representations(_h0(2, 8, 64), adj, weights=w64, num_timesteps=2, precision="f16")
