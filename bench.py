@@ -286,16 +286,18 @@ def run_gpu(args):
                  "note": "compute_final_node_representations_sparse on pinned host tensors: edge list "
                          "(6 KB/graph) + states H2D, result D2H"}
 
-    # strict-FP32 mode of the same workload (one pass over this rank's graphs), for the record
-    fp32_strict = None
-    if precision != "fp32" and not args.no_fp32:
-        prop.propagate_dense(h0[:pool], adj[:pool], num_timesteps=T, precision="fp32", out=out[:pool])
+    # the other arithmetic modes on the same workload (one pass over this rank's graphs each), for the record
+    other_modes = {}
+    notes = {"fp32": "GGNN_PREC_FP32, strict (<= 1e-5 norm-wise vs the FP64 oracle)",
+             "tf32": "GGNN_PREC_TF32, tcgen05 kind::tf32 (<= 2e-3)", "f16": "GGNN_PREC_F16, tcgen05 kind::f16 (<= 2e-3)"}
+    for mode in ([] if args.no_fp32 else [m for m in ("tf32", "fp32") if m != precision]):
+        prop.propagate_dense(h0[:pool], adj[:pool], num_timesteps=T, precision=mode, out=out[:pool])
         barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record()
         for c in range(0, graphs_rank, pool):
             n = min(pool, graphs_rank - c)
-            prop.propagate_dense(h0[c:c + n], adj[:n], num_timesteps=T, precision="fp32", out=out[c:c + n])
+            prop.propagate_dense(h0[c:c + n], adj[:n], num_timesteps=T, precision=mode, out=out[c:c + n])
         f1.record()
         barrier()
         fms = f0.elapsed_time(f1)
@@ -303,14 +305,14 @@ def run_gpu(args):
             tf_ = torch.tensor([fms], device=dev, dtype=torch.float64)
             dist.all_reduce(tf_, op=dist.ReduceOp.MAX)
             fms = float(tf_.item())
-        fp32_strict = {"value": args.graphs / (fms * 1e-3), "unit": "graphs/s", "ms_per_step": fms, "steps": 1,
-                       "note": "GGNN_PREC_FP32 (<= 1e-5 norm-wise vs the FP64 oracle), same inputs"}
+        other_modes[mode] = {"value": args.graphs / (fms * 1e-3), "unit": "graphs/s", "ms_per_step": fms,
+                             "steps": 1, "note": notes[mode] + ", same inputs"}
 
     if rank == 0:
         steps_g = args.steps * graphs_rank                 # graph passes timed on this rank
         st_ms = {k: v[0] for k, v in stages.items()}
         st_ln = {k: v[1] for k, v in stages.items()}
-        tf32_peak = peaks["bf16_tflops_sustained"] / 2.0
+        tf32_peak = peaks["bf16_tflops_sustained"] / (1.0 if precision == "f16" else 2.0)   # kind::f16 runs at the BF16 rate
         cand = {
             "compact_mask": ("hbm", steps_g * BYTES_COMPACT_PER_GRAPH / 1e9, "GB/s", peaks["hbm_gbs"]),
             "agg": ("hbm", steps_g * T * BYTES_AGG_PER_GRAPH_STEP / 1e9, "GB/s", peaks["hbm_gbs"]),
@@ -338,12 +340,13 @@ def run_gpu(args):
                     "unit": d["unit"], "frac": d["frac"], "traffic": None,
                     "avg_launch_ms": st_ms[dom] / max(st_ln[dom], 1),
                     "peak_source": peaks["source"] + ("" if d["bound"] == "hbm" else
-                                                      "; TF32 peak taken as half the sustained BF16 figure")}
+                                                      ("; kind::f16 peak = the measured sustained BF16 figure" if precision == "f16" else
+                                                       "; TF32 peak taken as half the sustained BF16 figure"))}
         line = {
             "metric": "GGNN propagation graphs/sec (T=8 steps)", "value": value, "unit": "graphs/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32" if precision == "fp32" else "tf32-in/f32-acc", "data": "synthetic",
+            "dtype": {"fp32": "f32", "tf32": "tf32-in/f32-acc", "f16": "f16-in/f32-acc"}[precision], "data": "synthetic",
             "config": {"workload": "C3 synthetic dependency trees v=128 2E=92 h=128 T=8, dense FP32 "
                                    "adjacency -> compaction -> propagation",
                        "global_graphs": args.graphs, "graphs_per_gpu": graphs_rank,
@@ -351,7 +354,7 @@ def run_gpu(args):
                        "parallelism": f"graph-sharded x{world}, no forward collective",
                        "cache": "inputs (>=24 GB per pass) far exceed the 126 MB L2; no flush needed"},
             "node_updates_per_s": value * V * T,
-            "clocks": clocks, "e2e": e2e, "e2e_edges": e2e_edges, "fp32_strict": fp32_strict,
+            "clocks": clocks, "e2e": e2e, "e2e_edges": e2e_edges, "other_modes": other_modes,
             "gpu_launches": int(launches),
             "roofline": roofline, "stages": per_stage,
         }
@@ -474,6 +477,8 @@ def run_c4(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    if args.precision == "f16":
+        args.precision = "tf32"          # the kind::f16 kernels are built for hidden size <= 128
     Vn, CH, BASE, Hc, Tc = 4096, 8, 32768, 256, 8
     per_gpu = args.c4_graphs
     wd = O.make_weights(CH, Hc, 0)
@@ -551,13 +556,13 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32"])
+    ap.add_argument("--precision", default="f16", choices=["fp32", "tf32", "f16"])
     ap.add_argument("--graphs", type=int, default=TOTAL_GRAPHS, help="global batch (all GPUs)")
     ap.add_argument("--pool", type=int, default=4096, help="distinct dense adjacency graphs resident per GPU")
     ap.add_argument("--e2e-graphs", type=int, default=256)
     ap.add_argument("--ref-graphs", type=int, default=64, help="graphs per step of the CPU reference arm")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-fp32", action="store_true", help="skip the strict-FP32 pass of the c3 workload")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the passes in the other arithmetic modes (c3 workload)")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c3 = the headline forward benchmark; c5 = training step (secondary line)")
     ap.add_argument("--c4-graphs", type=int, default=64, help="graphs per GPU of the c4 workload")

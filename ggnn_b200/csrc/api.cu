@@ -4,6 +4,7 @@
 #include "train.cuh"
 #include "heads.cuh"
 #include "f16.cuh"
+#include "plan_bits.cuh"
 
 #include <new>
 #include <stdlib.h>
@@ -84,6 +85,7 @@ extern "C" int ggnn_create(ggnn_ctx** out, int device) {
   }
   c->sm_count = prop.multiProcessorCount;
   c->no_fused = getenv("GGNN_NO_FUSED") != nullptr;
+  c->no_bits_plan = getenv("GGNN_NO_BITS_PLAN") != nullptr;
   c->ws = reinterpret_cast<char*>(new (std::nothrow) ctx_ext());
   if (cudaMallocHost(&c->h_mail, 8 * sizeof(int64_t)) != cudaSuccess ||
       cudaMalloc(&c->d_mail, 8 * sizeof(int64_t)) != cudaSuccess) {
@@ -369,6 +371,38 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
     const int64_t bc = (b - g0 < chunk) ? b - g0 : chunk;
     const int64_t rows = bc * rows_per_graph;
     const char* adj_c = reinterpret_cast<const char*>(adj) + (size_t)g0 * rows_per_graph * v * esz;
+    float* h_chunk = h_out + (size_t)g0 * v * h;
+    if (ggnn_plan_bits_supported(two_e, v) && !ctx->no_bits_plan) {
+      // fast route: bitmask -> plan, the 2E*v-rows-per-graph CSR is never materialised (plan_bits.cu)
+      ggnn_plan_bits_pre pre;
+      {
+        ws_alloc dry(nullptr);
+        ggnn_plan_bits_take_pre(dry, bc, two_e, v, &pre);
+        GGNN_TRY(arena_reserve(ctx, 0, dry.off + 256, st));
+      }
+      ws_alloc a0(ext_of(ctx)->ar[0].p);
+      ggnn_plan_bits_take_pre(a0, bc, two_e, v, &pre);
+      if (precision == GGNN_PREC_F16) GGNN_TRY(f16_prologue(ctx, slot, h_chunk, bc * v, st));
+      GGNN_TRY(ggnn_compact_bitmask(ctx, adj_c, adj_dtype, rows * v, pre.bits, st));
+      GGNN_TRY(ggnn_plan_bits_count(ctx, pre, bc, two_e, v, ctx->d_mail, st));
+      int64_t nnz = 0;
+      GGNN_TRY(read_i64(ctx, ctx->d_mail, &nnz, st));     // the one planning sync
+      if (precision == GGNN_PREC_F16) GGNN_TRY(f16_check(ctx, slot));
+      if (nnz >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "chunk has %lld edges", (long long)nnz);
+      ggnn_plan plan;
+      ggnn_step_bufs sb;
+      {
+        ws_alloc dry(nullptr);
+        GGNN_TRY(ggnn_plan_bits_place(ctx, pre, bc, two_e, v, nnz, &plan, dry, true, st));
+        take_step_bufs(dry, plan, h, &sb);
+        GGNN_TRY(arena_reserve(ctx, 1, dry.off + 256, st));
+      }
+      ws_alloc a1(ext_of(ctx)->ar[1].p);
+      GGNN_TRY(ggnn_plan_bits_place(ctx, pre, bc, two_e, v, nnz, &plan, a1, false, st));
+      take_step_bufs(a1, plan, h, &sb);
+      GGNN_TRY(run_steps(ctx, slot, plan, sb, h_chunk, T, precision, flags, st));
+      continue;
+    }
     // arena 0: [rowptr][compaction tmp]
     const size_t rp_bytes = align_up((size_t)(rows + 1) * 4, 256);
     GGNN_TRY(arena_reserve(ctx, 0, rp_bytes + ggnn_compact_tmp_bytes(rows * v, rows), st));

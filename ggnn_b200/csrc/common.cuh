@@ -46,6 +46,7 @@ struct ggnn_ctx {
   CUtensorMap tm_Wg, tm_Wc, tm_Wg256;  // TMA views of the packed GRU kernels (256-row box: fused kernel)
   unsigned long long* dbg_trace = nullptr;   // device buffer for kernel phase traces (ggnn_debug_trace)
   bool   no_fused = false;   // debugging / A-B switch (GGNN_NO_FUSED=1)
+  bool   no_bits_plan = false; // A-B switch (GGNN_NO_BITS_PLAN=1): dense path goes through the canonical CSR
   int    tm_rows_g = 0, tm_rows_c = 0;
   float* bg_pad = nullptr;   // [2hp]
   float* bc_pad = nullptr;   // [hp]
@@ -140,6 +141,8 @@ size_t ggnn_scan_tmp_elems(int64_t n);
 
 // ---- compact.cu
 size_t ggnn_compact_tmp_bytes(int64_t total_elems, int64_t rows);
+int ggnn_compact_bitmask(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t total, uint32_t* bits,
+                         cudaStream_t st);
 int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t rows, int v,
                        int32_t* rowptr, int64_t* nnz_out_dev, char* tmp, cudaStream_t st);
 int ggnn_compact_fill(ggnn_ctx* ctx, int64_t rows, int v, const int32_t* rowptr, int32_t* col,

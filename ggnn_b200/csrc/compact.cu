@@ -166,15 +166,10 @@ size_t ggnn_compact_tmp_bytes(int64_t total_elems, int64_t rows) {
   return align_up(words * 4 + 16, 256) + ggnn_scan_tmp_elems(rows + 1) * 4 + 256;
 }
 
-// P1..P3: bitmask, row counts, scan.  rowptr is final afterwards, *nnz_out_dev holds nnz.
-int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t rows, int v,
-                       int32_t* rowptr, int64_t* nnz_out_dev, char* tmp, cudaStream_t st) {
-  const int64_t total = rows * (int64_t)v;
+// P1: dense adjacency -> bitmask (the HBM-bound pass)
+int ggnn_compact_bitmask(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t total, uint32_t* bits,
+                         cudaStream_t st) {
   const int64_t words = ceil_div64(total, 32);
-  uint32_t* bits = reinterpret_cast<uint32_t*>(tmp);
-  int32_t* scan_tmp = reinterpret_cast<int32_t*>(tmp + align_up((size_t)words * 4 + 16, 256));
-  const size_t scan_elems = ggnn_scan_tmp_elems(rows + 1);
-
   if (total > 0) {
     prof_scope ps(ctx, GGNN_STAGE_COMPACT_MASK, st);
     const bool aligned = (reinterpret_cast<uintptr_t>(adj) & 15u) == 0;
@@ -217,6 +212,18 @@ int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t ro
       }
     }
   }
+  return GGNN_OK;
+}
+
+// P1..P3: bitmask, row counts, scan.  rowptr is final afterwards, *nnz_out_dev holds nnz.
+int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t rows, int v,
+                       int32_t* rowptr, int64_t* nnz_out_dev, char* tmp, cudaStream_t st) {
+  const int64_t total = rows * (int64_t)v;
+  const int64_t words = ceil_div64(total, 32);
+  uint32_t* bits = reinterpret_cast<uint32_t*>(tmp);
+  int32_t* scan_tmp = reinterpret_cast<int32_t*>(tmp + align_up((size_t)words * 4 + 16, 256));
+  const size_t scan_elems = ggnn_scan_tmp_elems(rows + 1);
+  GGNN_TRY(ggnn_compact_bitmask(ctx, adj, adj_dtype, total, bits, st));
   prof_scope ps(ctx, GGNN_STAGE_COMPACT_REST, st);
   rowcount_kernel<<<(unsigned)ceil_div64(rows + 1, 256), 256, 0, st>>>(bits, rows, v, rowptr);
   GGNN_LAUNCHED(ctx);

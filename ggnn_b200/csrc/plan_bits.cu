@@ -1,0 +1,209 @@
+// plan_bits.cu -- dense path, fast route: build the propagation plan STRAIGHT from the bitmask of
+// the adjacency, without materialising the canonical CSR.
+//
+// The canonical CSR has one row per (graph, channel, target): 48 M rows for 2 M edges at C3
+// (4 096 graphs), and every kernel that walks it moves ~200 MB.  Here one CTA per graph (one thread
+// per target node) walks its graph's 2E x v rows of the bitmask once, so the only per-row array is
+// a 16-bit count:
+//   count  (before the planning sync)  per-row popcounts -> rowcnt16; per-(channel, graph) segment
+//          lengths -> segposT; per-node in-degree -> tptr;  two scans; nnz = last(tptr)
+//   place  (after it)                  per channel, rank of every row inside its segment (warp
+//          scans over rowcnt16 in shared memory); thread t then emits, channel by channel, the
+//          message rows of its node: msg_src[row] = source, tmsg[cursor++] = row
+// The message-row numbering and the per-node (channel, source) order of tmsg are exactly those of
+// plan.cu (same tile table, same segment offsets), so results are bit-identical to the CSR route.
+#include "plan.cuh"
+#include "plan_bits.cuh"
+
+namespace {
+
+constexpr int MAX_THREADS = 1024;
+
+// bits [lo, hi) of the flat bitmask -> popcount
+__device__ __forceinline__ int row_popc(const uint32_t* __restrict__ bits, int64_t lo, int v) {
+  if ((v & 127) == 0 && (lo & 127) == 0) {          // aligned fast path: 128-bit loads
+    int c = 0;
+    const uint4* p = reinterpret_cast<const uint4*>(bits + (lo >> 5));
+    for (int q = 0; q < (v >> 7); ++q) {
+      const uint4 m = __ldg(p + q);
+      c += __popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w);
+    }
+    return c;
+  }
+  const int64_t hi = lo + v;
+  int c = 0;
+  for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
+    uint32_t m = __ldg(bits + w);
+    const int64_t wb = w << 5;
+    if (lo > wb) m &= 0xffffffffu << (int)(lo - wb);
+    if (hi < wb + 32) m &= 0xffffffffu >> (int)(wb + 32 - hi);
+    c += __popc(m);
+  }
+  return c;
+}
+
+// one CTA per graph, thread t = target node.  smem: int part[nwarps][two_e]
+__global__ void __launch_bounds__(MAX_THREADS)
+graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int v,
+                   uint16_t* __restrict__ rowcnt, int32_t* __restrict__ seglenT,
+                   int32_t* __restrict__ tcnt) {
+  extern __shared__ int part[];
+  const int64_t g = blockIdx.x;
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
+  int deg = 0;
+#pragma unroll 4
+  for (int e = 0; e < two_e; ++e) {
+    const int64_t r = (g * two_e + e) * v + t;
+    int c = 0;
+    if (t < v) {
+      c = row_popc(bits, r * v, v);
+      rowcnt[r] = (uint16_t)c;
+    }
+    deg += c;
+    int s = c;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) part[wid * two_e + e] = s;
+  }
+  if (t < v) tcnt[g * v + t] = deg;
+  if (g == b - 1 && t == 0) { tcnt[b * v] = 0; seglenT[b * two_e] = 0; }
+  __syncthreads();
+  for (int e = t; e < two_e; e += blockDim.x) {
+    int s = 0;
+    for (int w = 0; w < nw; ++w) s += part[w * two_e + e];
+    seglenT[(int64_t)e * b + g] = s;
+  }
+}
+
+// one CTA per graph, thread t = target node.  smem: uint16 rank[two_e][vt]
+__global__ void __launch_bounds__(MAX_THREADS)
+graph_place_kernel(const uint32_t* __restrict__ bits, const uint16_t* __restrict__ rowcnt, int64_t b,
+                   int two_e, int v, const int32_t* __restrict__ segposT,
+                   const int32_t* __restrict__ tile_base, const int32_t* __restrict__ tptr,
+                   int32_t* __restrict__ msg_src, int32_t* __restrict__ tmsg) {
+  extern __shared__ uint16_t rank[];
+  const int64_t g = blockIdx.x;
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5, vt = blockDim.x;
+  for (int e = 0; e < two_e; ++e)
+    rank[e * vt + t] = t < v ? rowcnt[(g * two_e + e) * v + t] : (uint16_t)0;
+  __syncthreads();
+  // exclusive scan of every channel's row counts over the target index (warp per channel)
+  for (int e = wid; e < two_e; e += nw) {
+    int carry = 0;
+    for (int t0 = 0; t0 < vt; t0 += 32) {
+      const int c = rank[e * vt + t0 + lane];
+      int incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += y;
+      }
+      rank[e * vt + t0 + lane] = (uint16_t)(carry + incl - c);
+      carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+  }
+  __syncthreads();
+  if (t >= v) return;
+  int cursor = tptr[g * v + t];
+  const int end = tptr[g * v + t + 1];
+  for (int e = 0; e < two_e && cursor < end; ++e) {
+    const int64_t r = (g * two_e + e) * v + t;
+    const int c = rowcnt[r];                              // L1/L2 hit: read a moment ago
+    if (c == 0) continue;
+    int mrow = tile_base[e] * GGNN_TILE_M + (segposT[(int64_t)e * b + g] - segposT[(int64_t)e * b]) +
+               rank[e * vt + t];
+    const int64_t lo = r * v, hi = lo + v;
+    for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
+      uint32_t m = __ldg(bits + w);
+      const int64_t wb = w << 5;
+      if (lo > wb) m &= 0xffffffffu << (int)(lo - wb);
+      if (hi < wb + 32) m &= 0xffffffffu >> (int)(wb + 32 - hi);
+      while (m) {
+        const int bpos = __ffs(m) - 1;
+        m &= m - 1;
+        msg_src[mrow] = (int32_t)(g * v + (wb + bpos - lo));
+        tmsg[cursor++] = mrow++;
+      }
+    }
+  }
+}
+
+// same tile table as plan.cu's tiles_kernel (kept separate: that one is file-local)
+__global__ void bits_tiles_kernel(const int32_t* __restrict__ segposT, int64_t b, int two_e,
+                                  int32_t* __restrict__ tile_base, int32_t* __restrict__ tile_type,
+                                  int32_t* __restrict__ n_tiles, int64_t max_tiles) {
+  extern __shared__ int32_t sh[];   // [two_e + 1]
+  if (threadIdx.x == 0) {
+    int32_t run = 0;
+    for (int e = 0; e < two_e; ++e) {
+      const int32_t cnt = segposT[(int64_t)(e + 1) * b] - segposT[(int64_t)e * b];
+      sh[e] = run;
+      run += (cnt + GGNN_TILE_M - 1) / GGNN_TILE_M;
+    }
+    sh[two_e] = run;
+    *n_tiles = run;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e <= two_e; e += blockDim.x) tile_base[e] = sh[e];
+  for (int e = 0; e < two_e; ++e)
+    for (int t = sh[e] + threadIdx.x; t < sh[e + 1]; t += blockDim.x)
+      if (t < max_tiles) tile_type[t] = e;
+}
+
+inline int threads_for(int v) { return (int)align_up((size_t)v, 32); }
+
+}  // namespace
+
+bool ggnn_plan_bits_supported(int two_e, int v) {
+  const int vt = threads_for(v);
+  return v >= 1 && v <= 255 /* ranks inside a segment fit 16 bits */ && vt <= MAX_THREADS &&
+         (size_t)two_e * vt * 2 <= 48 * 1024 &&
+         (size_t)(vt / 32) * two_e * 4 <= 48 * 1024;
+}
+
+void ggnn_plan_bits_take_pre(ws_alloc& a, int64_t b, int two_e, int v, ggnn_plan_bits_pre* pre) {
+  const int64_t rows = b * two_e * v, N = b * v, nseg = b * two_e;
+  pre->bits = a.take<uint32_t>((size_t)ceil_div64(rows * v, 32) + 4);
+  pre->rowcnt = a.take<uint16_t>((size_t)rows + 2);
+  pre->segposT = a.take<int32_t>((size_t)nseg + 1);
+  pre->tptr = a.take<int32_t>((size_t)N + 1);
+  pre->scan_elems = ggnn_scan_tmp_elems((nseg > N ? nseg : N) + 1);
+  pre->scan_tmp = a.take<int32_t>(pre->scan_elems);
+}
+
+int ggnn_plan_bits_count(ggnn_ctx* ctx, const ggnn_plan_bits_pre& pre, int64_t b, int two_e, int v,
+                         int64_t* nnz_out_dev, cudaStream_t st) {
+  prof_scope ps(ctx, GGNN_STAGE_COMPACT_REST, st);
+  const int vt = threads_for(v);
+  graph_count_kernel<<<(unsigned)b, vt, (size_t)(vt / 32) * two_e * 4, st>>>(pre.bits, b, two_e, v, pre.rowcnt,
+                                                                            pre.segposT, pre.tptr);
+  GGNN_LAUNCHED(ctx);
+  GGNN_TRY(ggnn_exclusive_scan_i32(ctx, pre.segposT, pre.segposT, b * two_e + 1, nullptr, pre.scan_tmp, pre.scan_elems, st));
+  GGNN_TRY(ggnn_exclusive_scan_i32(ctx, pre.tptr, pre.tptr, b * v + 1, nnz_out_dev, pre.scan_tmp, pre.scan_elems, st));
+  return GGNN_OK;
+}
+
+int ggnn_plan_bits_place(ggnn_ctx* ctx, const ggnn_plan_bits_pre& pre, int64_t b, int two_e, int v,
+                         int64_t nnz, ggnn_plan* plan, ws_alloc& a, bool dry, cudaStream_t st) {
+  plan->N = b * v;
+  plan->nnz = nnz;
+  plan->dense_rows = false;
+  plan->max_tiles = nnz / GGNN_TILE_M + two_e + 1;
+  plan->n_tiles = a.take<int32_t>(4);
+  plan->msg_src = a.take<int32_t>((size_t)plan->max_tiles * GGNN_TILE_M);
+  plan->tile_type = a.take<int32_t>((size_t)plan->max_tiles);
+  plan->tmsg = a.take<int32_t>((size_t)nnz + 1);
+  int32_t* tile_base = a.take<int32_t>((size_t)two_e + 1);
+  plan->tptr = pre.tptr;
+  if (dry) return GGNN_OK;
+  prof_scope ps(ctx, GGNN_STAGE_PLAN, st);
+  bits_tiles_kernel<<<1, 256, (two_e + 1) * sizeof(int32_t), st>>>(pre.segposT, b, two_e, tile_base, plan->tile_type,
+                                                                  plan->n_tiles, plan->max_tiles);
+  GGNN_LAUNCHED(ctx);
+  GGNN_CUDA(ctx, cudaMemsetAsync(plan->msg_src, 0xFF, (size_t)plan->max_tiles * GGNN_TILE_M * sizeof(int32_t), st));
+  const int vt = threads_for(v);
+  graph_place_kernel<<<(unsigned)b, vt, (size_t)two_e * vt * 2, st>>>(pre.bits, pre.rowcnt, b, two_e, v, pre.segposT,
+                                                                     tile_base, pre.tptr, plan->msg_src, plan->tmsg);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
