@@ -41,6 +41,9 @@ FLOP_MSG_PER_GRAPH_STEP = NNZ_PER_GRAPH * 2 * H * H           # 16.6 MFLOP
 FLOP_GATES_PER_GRAPH_STEP = V * 2 * (2 * H) * (2 * H)         # 16.8 MFLOP
 FLOP_CAND_PER_GRAPH_STEP = V * 2 * (2 * H) * H                #  8.4 MFLOP
 BYTES_COMPACT_PER_GRAPH = TWO_E * V * V * 4 + NNZ_PER_GRAPH * 4 + (TWO_E * V) * 4   # 6.08 MB
+# DRAM traffic of the compaction bitmask pass per graph from the ncu --set full capture
+# (profiles/r1_f16_ncu.md: 12.356 GB read + 0.342 GB written over 2 048 graphs)
+TRAFFIC_COMPACT_PER_GRAPH = (12.356429e9 + 342.248448e6) / 2048
 BYTES_AGG_PER_GRAPH_STEP = NNZ_PER_GRAPH * H * 4 + NNZ_PER_GRAPH * 4 + (V + 1) * 4 + V * H * 4
 
 
@@ -337,7 +340,11 @@ def run_gpu(args):
         dom = max(cand, key=lambda k: st_ms.get(k, 0))
         d = per_stage[dom]
         roofline = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"], "peak": d["peak"],
-                    "unit": d["unit"], "frac": d["frac"], "traffic": None,
+                    "unit": d["unit"], "frac": d["frac"],
+                    "traffic": (TRAFFIC_COMPACT_PER_GRAPH * steps_g / max(st_ln[dom], 1)) if dom == "compact_mask" else None,
+                    "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per graph of one ncu --set full "
+                                      "capture (profiles/r1_f16_ncu.md) x graphs per launch" if dom == "compact_mask" else None,
+                    "algorithmic_bytes_per_launch": (BYTES_COMPACT_PER_GRAPH * steps_g / max(st_ln[dom], 1)) if dom == "compact_mask" else None,
                     "avg_launch_ms": st_ms[dom] / max(st_ln[dom], 1),
                     "peak_source": peaks["source"] + ("" if d["bound"] == "hbm" else
                                                       ("; kind::f16 peak = the measured sustained BF16 figure" if precision == "f16" else

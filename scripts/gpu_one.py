@@ -12,6 +12,7 @@ prop = ggnn_b200.Propagator(ggnn_b200.from_dict(O.make_weights(2 * E, h, 0)), "c
 tri = synth.random_trees(b, v - 1, E, seed=1).cuda()
 adj = synth.dense_adjacency(tri, v, E)
 h0 = (torch.rand(b, v, h, device="cuda") - 0.5) * 0.2
-out = prop.propagate_dense(h0, adj, num_timesteps=T, precision="tf32")
+prec = sys.argv[3] if len(sys.argv) > 3 else "tf32"
+out = prop.propagate_dense(h0, adj, num_timesteps=T, precision=prec)
 torch.cuda.synchronize()
 print("ok", float(out.abs().max()))
