@@ -19,10 +19,16 @@ struct arena {
 // Two grow-only arenas per ctx: [0] compaction (bitmask, rowptr, scan), [1] col + plan + step
 // buffers.  They are separate because [1] is sized only after the edge count is known and
 // must not move [0].
-// [2] training tape (per-step activations), [3] backward scratch, [4] FP16 node states.
+// [2] training tape (per-step activations), [3] backward scratch, [4] FP16 node states,
+// [5] effective edge weights of the dropout path.
 struct ctx_ext {
-  arena ar[5];
+  arena ar[6];
   ggnn_tape tape;
+  // A8: masks for the next SAVE_TAPE forward (ggnn_set_dropout)
+  const float* drop_w = nullptr;
+  const float* drop_s = nullptr;
+  float drop_keep = 1.f;
+  int drop_T = -1;
 };
 
 ctx_ext* ext_of(ggnn_ctx* c) { return reinterpret_cast<ctx_ext*>(c->ws); }
@@ -284,12 +290,32 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
     GGNN_TRY(arena_reserve(ctx, 2, (size_t)T * TAPE_ARRAYS * nh * 4 + 256, st));
     tape.plan = plan; tape.T = T; tape.slot = slot; tape.h = ctx->h;
     tape.acts = reinterpret_cast<float*>(ext_of(ctx)->ar[2].p);
+    ctx_ext* ex = ext_of(ctx);
+    tape.w_mask = tape.state_mask = nullptr; tape.keep = 1.f; tape.w_eff = nullptr;
+    if (ex->drop_T >= 0) {                 // masks registered by ggnn_set_dropout apply to this call only
+      if (ex->drop_T != T) GGNN_FAIL(ctx, GGNN_E_SHAPE, "dropout masks were set for T=%d, propagate has T=%d", ex->drop_T, T);
+      tape.w_mask = ex->drop_w; tape.state_mask = ex->drop_s; tape.keep = ex->drop_keep;
+      ex->drop_T = -1;
+    }
+    const size_t wn = (size_t)ctx->two_e * ctx->h * ctx->h;
+    if (tape.w_mask) {
+      GGNN_TRY(arena_reserve(ctx, 5, wn * 4 + 256, st));
+      tape.w_eff = reinterpret_cast<float*>(ex->ar[5].p);
+    }
     for (int t = 0; t < T; ++t) {
       GGNN_CUDA(ctx, cudaMemcpyAsync(tape.at(t, TAPE_H), h_state, nh * 4, cudaMemcpyDeviceToDevice, st));
       ggnn_step_bufs tb = sb;
       tb.acts = tape.at(t, TAPE_X); tb.u = tape.at(t, TAPE_U);
       tb.tape_r = tape.at(t, TAPE_R); tb.tape_c = tape.at(t, TAPE_C);
+      if (tape.w_mask) {                   // tf.nn.dropout(W): W * m_t / keep, a fresh mask per unrolled step
+        GGNN_TRY(ggnn_mask_scale(ctx, ctx->edge[slot].W, tape.w_mask + (size_t)t * wn, 1.0f / tape.keep, tape.w_eff,
+                                 (int64_t)wn, false, st));
+        tb.W_override = tape.w_eff;
+      }
       GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, tb, h_state, st));
+      if (tape.state_mask)                 // DropoutWrapper(state_keep_prob): the new state is dropped
+        GGNN_TRY(ggnn_mask_scale(ctx, h_state, tape.state_mask + (size_t)t * nh, 1.0f / tape.keep, h_state,
+                                 (int64_t)nh, false, st));
     }
     tape.valid = true;
     return GGNN_OK;
@@ -493,6 +519,15 @@ extern "C" int64_t ggnn_grad_floats(const ggnn_ctx* ctx) {
   return (int64_t)ggnn_grad_count(ctx->two_e, ctx->h);
 }
 
+extern "C" int ggnn_set_dropout(ggnn_ctx* ctx, const float* w_mask, const float* state_mask, float keep, int T) {
+  if (!ctx) return GGNN_E_ARG;
+  if (!(keep > 0.f && keep <= 1.f) || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "set_dropout: keep must be in (0, 1], T >= 0");
+  ctx_ext* ex = ext_of(ctx);
+  ex->drop_w = w_mask; ex->drop_s = state_mask; ex->drop_keep = keep;
+  ex->drop_T = (w_mask || state_mask) ? T : -1;
+  return GGNN_OK;
+}
+
 extern "C" int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* d_h0, float* grads,
                                        void* stream) {
   if (!ctx) return GGNN_E_ARG;
@@ -504,11 +539,11 @@ extern "C" int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* 
   ggnn_bwd_scratch sc;
   {
     ws_alloc dry(nullptr);
-    ggnn_bwd_take_scratch(dry, tape.plan, ctx->h, &sc);
+    ggnn_bwd_take_scratch(dry, tape.plan, ctx->h, ctx->two_e, tape.w_mask != nullptr, &sc);
     GGNN_TRY(arena_reserve(ctx, 3, dry.off + 256, st));
   }
   ws_alloc a(ext_of(ctx)->ar[3].p);
-  ggnn_bwd_take_scratch(a, tape.plan, ctx->h, &sc);
+  ggnn_bwd_take_scratch(a, tape.plan, ctx->h, ctx->two_e, tape.w_mask != nullptr, &sc);
   return ggnn_backward_fp32(ctx, tape, sc, d_hT, d_h0, grads, st);
 }
 

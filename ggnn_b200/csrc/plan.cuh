@@ -35,6 +35,7 @@ struct ggnn_step_bufs {
   float* u = nullptr;     // [N, h]
   float* tape_r = nullptr;  // training tape (FP32 path only): reset gate r of this step, or null
   float* tape_c = nullptr;  // training tape: candidate c of this step, or null
+  const float* W_override = nullptr;  // training with edge-weight dropout: W * mask / keep of this step
 };
 int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs,
                    float* h_state, cudaStream_t st);

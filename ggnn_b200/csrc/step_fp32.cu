@@ -259,7 +259,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     sgemm_params p{};
     p.A1 = h_state; p.A2 = nullptr; p.gather = plan.msg_src;
     p.K1 = h; p.K2 = 0; p.lda = h;
-    p.Bmat = ew.W; p.bias = ew.B; p.N = h;
+    p.Bmat = bufs.W_override ? bufs.W_override : ew.W; p.bias = ew.B; p.N = h;
     p.M = plan.max_tiles * GGNN_TILE_M;
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg; p.h = h;

@@ -12,14 +12,23 @@ struct ggnn_tape {
   float* acts = nullptr;       // [T][TAPE_ARRAYS][N*h]
   float* at(int t, int which) const { return acts + ((size_t)t * TAPE_ARRAYS + which) * (size_t)plan.N * h; }
   int h = 0;
+  // A8: training-time dropout with caller-supplied 0/1 masks (null = keep everything)
+  const float* w_mask = nullptr;      // [T, 2E, h, h]  tf.nn.dropout on edge_weights, fresh per step (:397-403)
+  const float* state_mask = nullptr;  // [T, N, h]      DropoutWrapper(state_keep_prob) on the new state (:239-240)
+  float keep = 1.f;
+  float* w_eff = nullptr;             // [2E, h, h] scratch: W * mask_t / keep
 };
 
 // scratch the backward needs, in floats / int32s (for the bump allocator)
 struct ggnn_bwd_scratch {
   float *dh_a, *dh_b, *dx, *dzc, *rh, *dzg, *dxr;
   int32_t* msg_tgt;
+  float* gw_tmp;      // [2E, h, h] per-step dW before the mask is applied (only with w_mask)
 };
-void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_bwd_scratch* s);
+void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, int two_e, bool with_w_mask, ggnn_bwd_scratch* s);
+
+// elementwise helpers of the dropout path
+int ggnn_mask_scale(ggnn_ctx* ctx, const float* x, const float* mask, float scale, float* out, int64_t n, bool accumulate, cudaStream_t st);
 
 // flat gradient layout: [dW 2E*h*h | dB 2E*h | dWg 2h*2h | dbg 2h | dWc 2h*h | dbc h]
 size_t ggnn_grad_count(int two_e, int h);

@@ -293,6 +293,15 @@ __global__ void gru_bwd_pw3_kernel(const float* __restrict__ dxh, float* __restr
   }
 }
 
+// out = (accumulate ? out : 0) + x * mask * scale
+__global__ void mask_scale_kernel(const float* x, const float* __restrict__ mask, float scale,
+                                  float* out, int64_t n, int accumulate) {   // x may alias out
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = x[i] * mask[i] * scale;
+    out[i] = accumulate ? out[i] + v : v;
+  }
+}
+
 // msg_tgt[message row] = target node (from the target CSR); padding rows keep -1
 __global__ void msg_tgt_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg,
                                int64_t N, int32_t* __restrict__ msg_tgt) {
@@ -308,7 +317,15 @@ size_t ggnn_grad_count(int two_e, int h) {
   return (size_t)two_e * h * h + (size_t)two_e * h + (size_t)4 * h * h + 2 * h + (size_t)2 * h * h + h;
 }
 
-void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_bwd_scratch* s) {
+int ggnn_mask_scale(ggnn_ctx* ctx, const float* x, const float* mask, float scale, float* out, int64_t n,
+                    bool accumulate, cudaStream_t st) {
+  if (n <= 0) return GGNN_OK;
+  mask_scale_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(x, mask, scale, out, n, accumulate ? 1 : 0);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, int two_e, bool with_w_mask, ggnn_bwd_scratch* s) {
   const size_t nh = (size_t)plan.N * h;
   s->dh_a = a.take<float>(nh);
   s->dh_b = a.take<float>(nh);
@@ -318,6 +335,7 @@ void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, ggnn_bwd_s
   s->dzg = a.take<float>(2 * nh);
   s->dxr = a.take<float>(2 * nh);
   s->msg_tgt = a.take<int32_t>((size_t)plan.max_tiles * GGNN_TILE_M);
+  s->gw_tmp = with_w_mask ? a.take<float>((size_t)two_e * h * h) : nullptr;
 }
 
 namespace {
@@ -384,6 +402,17 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
   for (int t = tape.T - 1; t >= 0; --t) {
     const float *ht = tape.at(t, TAPE_H), *xt = tape.at(t, TAPE_X), *rt = tape.at(t, TAPE_R),
                 *ut = tape.at(t, TAPE_U), *ct = tape.at(t, TAPE_C);
+    const float inv_keep = 1.0f / tape.keep;
+    if (tape.state_mask) {   // dhn is w.r.t. the dropped state h' * s_t / keep
+      GGNN_TRY(ggnn_mask_scale(ctx, dhn, tape.state_mask + (size_t)t * nh, inv_keep, s.dx, (int64_t)nh, false, st));
+      dhn = s.dx;            // dx is free until the second pointwise kernel of this step
+    }
+    const float* Wt = ew.W;
+    if (tape.w_mask) {       // this step's effective weights W * m_t / keep
+      GGNN_TRY(ggnn_mask_scale(ctx, ew.W, tape.w_mask + (size_t)t * two_e * h * h, inv_keep, tape.w_eff,
+                               (int64_t)two_e * h * h, false, st));
+      Wt = tape.w_eff;
+    }
     gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h);
     GGNN_LAUNCHED(ctx);
     {  // [dx | drh] = dzc @ Wc^T
@@ -420,7 +449,7 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
       {  // dh[src_j] += dx[tgt_j] @ W_e^T
         nt_params p{};
         p.A1 = s.dx; p.K1 = h; p.lda = h; p.a_rowmap = s.msg_tgt;
-        p.B = ew.W; p.ldb = h; p.b_type_stride = (int64_t)h * h; p.N = h; p.M = mrows;
+        p.B = Wt; p.ldb = h; p.b_type_stride = (int64_t)h * h; p.N = h; p.M = mrows;
         p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
         p.C = dh; p.ldc = h; p.c_rowmap = plan.msg_src;
         GGNN_TRY(launch_nt(ctx, p, (unsigned)plan.max_tiles, st));
@@ -429,9 +458,13 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
         tn_params p{};
         p.X = ht; p.ldx = h; p.x_rowmap = plan.msg_src; p.D = s.dx; p.ldd = h; p.d_rowmap = s.msg_tgt;
         p.K1 = h; p.N = h; p.R = mrows; p.rows_per_cta = 8 * GGNN_TILE_M;
-        p.C = gW; p.ldc = h; p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
+        p.C = tape.w_mask ? s.gw_tmp : gW; p.ldc = h; p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
         p.c_type_stride = (int64_t)h * h;
+        if (tape.w_mask) GGNN_CUDA(ctx, cudaMemsetAsync(s.gw_tmp, 0, (size_t)two_e * h * h * 4, st));
         GGNN_TRY(launch_tn(ctx, p, mrows, st));
+        if (tape.w_mask)     // dW += dW_t * m_t / keep
+          GGNN_TRY(ggnn_mask_scale(ctx, s.gw_tmp, tape.w_mask + (size_t)t * two_e * h * h, inv_keep, gW,
+                                   (int64_t)two_e * h * h, true, st));
       }
       GGNN_TRY(launch_colsum(ctx, s.dx, h, s.msg_tgt, h, mrows, gB, plan.tile_type, plan.n_tiles, h, st));
     }

@@ -242,6 +242,23 @@ class Propagator:
     def grad_floats(self) -> int:
         return int(self._l.ggnn_grad_floats(self._ctx))
 
+    def set_dropout(self, w_mask: Optional[torch.Tensor], state_mask: Optional[torch.Tensor], keep: float,
+                    num_timesteps: int):
+        """Supplied-mask dropout for the next ``save_tape=True`` propagate call and its backward
+        (reference: tf.nn.dropout on the edge weights per unrolled step, DropoutWrapper on the new
+        state).  w_mask float32 [T, 2E, h, h], state_mask float32 [T, N, h] (or [T, b, v, h]), 0/1."""
+        for m in (w_mask, state_mask):
+            if m is not None and (m.dtype != torch.float32 or m.device != self.device or not m.is_contiguous()):
+                raise ValueError("dropout masks must be contiguous float32 tensors on the ctx device")
+        w = self.weights
+        if w_mask is not None and tuple(w_mask.shape) != (num_timesteps, w.two_e, w.hidden_size, w.hidden_size):
+            raise ValueError(f"w_mask must be [T, 2E, h, h], got {tuple(w_mask.shape)}")
+        if state_mask is not None and (state_mask.shape[0] != num_timesteps or state_mask.shape[-1] != w.hidden_size):
+            raise ValueError(f"state_mask must be [T, N, h], got {tuple(state_mask.shape)}")
+        self._drop_keep = (w_mask, state_mask)          # keep the tensors alive until the backward
+        rc = self._l.ggnn_set_dropout(self._ctx, _ptr(w_mask), _ptr(state_mask), float(keep), int(num_timesteps))
+        self._check(rc, "ggnn_set_dropout")
+
     def backward(self, d_hT: torch.Tensor, grads: Optional[torch.Tensor] = None
                  ) -> Tuple[torch.Tensor, torch.Tensor]:
         """Backward of the last ``save_tape=True`` propagate call.  ``d_hT``: gradient w.r.t. the

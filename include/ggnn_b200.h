@@ -137,6 +137,15 @@ int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0,
  * This buffer is what the data-parallel trainer all-reduces with NCCL.  Weight gradients are
  * summed with float atomics (order not fixed).  No synchronisation. */
 int64_t ggnn_grad_floats(const ggnn_ctx* ctx);
+/* A8: training-time dropout of the path with CALLER-SUPPLIED 0/1 masks (TF's RNG stream cannot be
+ * reproduced, so the masks are inputs).  Applies to the NEXT propagate call with GGNN_FLAG_SAVE_TAPE
+ * (and to its backward), then is cleared.
+ *   w_mask     [T, two_e, h, h] or NULL: tf.nn.dropout on edge_weights, a fresh mask per unrolled
+ *              step -- the step uses W * w_mask[t] / keep (chem_tensorflow_dense.py:397-403)
+ *   state_mask [T, N, h] or NULL: DropoutWrapper(state_keep_prob) -- the new state of step t becomes
+ *              h' * state_mask[t] / keep (:239-240, 333)
+ * Both pointers must stay valid until the backward has run.  keep in (0, 1]. */
+int ggnn_set_dropout(ggnn_ctx* ctx, const float* w_mask, const float* state_mask, float keep, int T);
 int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* d_h0, float* grads, void* stream);
 
 /* "Next" rows either side of the path, evaluation mode --------------------

@@ -20,17 +20,21 @@ import torch
 KEYS = ("edge_weights", "edge_biases", "gru_gate_kernel", "gru_gate_bias", "gru_cand_kernel", "gru_cand_bias")
 
 
-def forward_torch(h0, edges, wt, T, use_bias=True):
-    """h0 [N,H] tensor, edges int64 tensor [nnz,3] (src, ch, dst), wt dict of tensors."""
+def forward_torch(h0, edges, wt, T, use_bias=True, w_mask=None, state_mask=None, keep=1.0):
+    """h0 [N,H] tensor, edges int64 tensor [nnz,3] (src, ch, dst), wt dict of tensors.
+    Training-time dropout with supplied masks: tf.nn.dropout(W, rate=1-keep) draws a fresh mask per
+    unrolled step -> W * w_mask[t] / keep (chem_tensorflow_dense.py:397-403); DropoutWrapper(
+    state_keep_prob=keep) drops the NEW state -> h' * state_mask[t] / keep (:239-240, :333 takes [1])."""
     H = h0.shape[1]
     src, ch, dst = edges[:, 0], edges[:, 1], edges[:, 2]
     h = h0
     Wg, bg, Wc, bc = wt["gru_gate_kernel"], wt["gru_gate_bias"], wt["gru_cand_kernel"], wt["gru_cand_bias"]
-    for _ in range(T):
+    for t in range(T):
         x = torch.zeros_like(h)
+        W = wt["edge_weights"] if w_mask is None else wt["edge_weights"] * w_mask[t] / keep
         if len(edges):
             # m_j = h[src_j] @ W[ch_j] + b[ch_j]   (bias per edge, SURVEY F9)
-            m = torch.bmm(h[src].unsqueeze(1), wt["edge_weights"][ch]).squeeze(1)
+            m = torch.bmm(h[src].unsqueeze(1), W[ch]).squeeze(1)
             if use_bias:
                 m = m + wt["edge_biases"].reshape(-1, H)[ch]
             x = x.index_add(0, dst, m)
@@ -38,17 +42,20 @@ def forward_torch(h0, edges, wt, T, use_bias=True):
         r, u = g[:, :H], g[:, H:]
         c = torch.tanh(torch.cat([x, r * h], 1) @ Wc + bc)
         h = u * h + (1 - u) * c
+        if state_mask is not None:
+            h = h * state_mask[t] / keep
     return h
 
 
-def grads(h0, edges, w, T, d_hT, use_bias=True, dtype=torch.float64):
+def grads(h0, edges, w, T, d_hT, use_bias=True, dtype=torch.float64, w_mask=None, state_mask=None, keep=1.0):
     """Returns (h_T, d_h0, {key: gradient}) as numpy, for L = sum(h_T * d_hT)."""
     wt = {k: torch.tensor(np.asarray(w[k]), dtype=dtype, requires_grad=True) for k in KEYS if k in w}
     if "edge_biases" not in wt:
         use_bias = False
     h0t = torch.tensor(np.asarray(h0), dtype=dtype, requires_grad=True)
     e = torch.tensor(np.asarray(edges), dtype=torch.int64).reshape(-1, 3)
-    hT = forward_torch(h0t, e, wt, T, use_bias)
+    tm = lambda a: None if a is None else torch.tensor(np.asarray(a), dtype=dtype)
+    hT = forward_torch(h0t, e, wt, T, use_bias, tm(w_mask), tm(state_mask), keep)
     loss = (hT * torch.tensor(np.asarray(d_hT), dtype=dtype)).sum()
     loss.backward()
     out = {}

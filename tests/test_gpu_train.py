@@ -99,3 +99,29 @@ def test_train_step_helper_single_process():
     dt = torch.from_numpy(d).cuda()
     hT, dh0, flat = gdist.train_step(prop, torch.from_numpy(h0).cuda(), edges.cuda(), lambda hT: dt, 3)
     _check(prop, w, hT, dh0, flat, G.grads(h0, edges.numpy(), w, 3, d))
+
+
+@pytest.mark.parametrize("use_w,use_s", [(True, True), (True, False), (False, True)])
+def test_training_dropout_with_supplied_masks(use_w, use_s):
+    """A8: tf.nn.dropout on the edge weights (fresh mask per unrolled step) and DropoutWrapper on the new
+    state, keep = 0.9 as the reference feeds in training (chem_tensorflow_dense.py:800, 860-861), with
+    the masks supplied by the caller; forward and gradients against the autograd oracle."""
+    b, v, E, h, T, keep = 4, 16, 5, 64, 3, 0.9
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=21)
+    rng = np.random.default_rng(3)
+    wm = (rng.random((T, 2 * E, h, h)) < keep).astype(np.float32) if use_w else None
+    sm = (rng.random((T, b * v, h)) < keep).astype(np.float32) if use_s else None
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    dev = lambda a: None if a is None else torch.from_numpy(a).cuda()
+    prop.set_dropout(dev(wm), dev(sm), keep, T)
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    ref = G.grads(h0, edges.numpy(), w, T, d, w_mask=wm, state_mask=sm, keep=keep)
+    _check(prop, w, hT, dh0, flat, ref)
+    nodrop = G.grads(h0, edges.numpy(), w, T, d)
+    assert O.normwise_err(hT.cpu().numpy(), nodrop[0]) > 1e-3         # the masks really did something
+    # the masks apply to ONE forward only: the next tape forward is dropout-free again
+    hT2 = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, save_tape=True)
+    assert O.normwise_err(hT2.cpu().numpy(), nodrop[0]) <= 1e-5
+    with pytest.raises(ValueError):
+        prop.set_dropout(dev(wm), dev(sm), keep, T + 1)
