@@ -20,9 +20,11 @@ struct arena {
 // buffers.  They are separate because [1] is sized only after the edge count is known and
 // must not move [0].
 // [2] training tape (per-step activations), [3] backward scratch, [4] FP16 node states,
-// [5] effective edge weights of the dropout path.
+// [5] effective edge weights of the dropout path, [6] Adam moments + norm slots.
 struct ctx_ext {
-  arena ar[6];
+  arena ar[7];
+  int64_t adam_n = 0;       // floats the moment buffers were sized (and zeroed) for
+  int64_t adam_t = 0;       // steps taken
   ggnn_tape tape;
   // A8: masks for the next SAVE_TAPE forward (ggnn_set_dropout)
   const float* drop_w = nullptr;
@@ -517,6 +519,70 @@ extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, co
 extern "C" int64_t ggnn_grad_floats(const ggnn_ctx* ctx) {
   if (!ctx || !ctx->gru_set) return 0;
   return (int64_t)ggnn_grad_count(ctx->two_e, ctx->h);
+}
+
+// N4 ------------------------------------------------------------------------------------
+extern "C" int ggnn_optimizer_step(ggnn_ctx* ctx, int slot, const float* grads, float lr, float beta1,
+                                   float beta2, float eps, float clip_norm, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (slot < 0 || slot >= GGNN_MAX_SLOTS || !grads) GGNN_FAIL(ctx, GGNN_E_ARG, "optimizer_step: bad slot or null grads");
+  if (!ctx->gru_set || !ctx->edge[slot].set) GGNN_FAIL(ctx, GGNN_E_STATE, "optimizer_step: weights for slot %d not set", slot);
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  ctx_ext* ex = ext_of(ctx);
+  const int h = ctx->h, two_e = ctx->two_e;
+  const int64_t n = (int64_t)ggnn_grad_count(two_e, h);
+  if (ex->adam_n != n) {                      // (re)create zeroed moments
+    GGNN_TRY(arena_reserve(ctx, 6, (size_t)(2 * n + 64) * 4, st));
+    GGNN_CUDA(ctx, cudaMemsetAsync(ex->ar[6].p, 0, (size_t)(2 * n + 64) * 4, st));
+    ex->adam_n = n;
+    ex->adam_t = 0;
+  }
+  float* m = reinterpret_cast<float*>(ex->ar[6].p);
+  float* v = m + n;
+  float* norms = v + n;                       // 6 slots
+  GGNN_CUDA(ctx, cudaMemsetAsync(norms, 0, 8 * sizeof(float), st));
+  const int64_t t = ++ex->adam_t;
+  const float lr_t = lr * sqrtf(1.f - powf(beta2, (float)t)) / (1.f - powf(beta1, (float)t));
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  float* params[6] = {ew.W, ew.B, ctx->Wg, ctx->bg, ctx->Wc, ctx->bc};
+  const int64_t sizes[6] = {(int64_t)two_e * h * h, (int64_t)two_e * h, (int64_t)4 * h * h, 2 * h, (int64_t)2 * h * h, h};
+  int64_t off = 0;
+  for (int i = 0; i < 6; ++i) {
+    GGNN_TRY(ggnn_adam_segment(ctx, params[i], grads + off, m + off, v + off, sizes[i], norms + i, clip_norm, lr_t,
+                               beta1, beta2, eps, st));
+    off += sizes[i];
+  }
+  // the tensor-core copies follow the FP32 master weights
+  ctx->repack_in_place = true;
+  int rc = ggnn_tf32_pack_weights(ctx, slot, true, st);
+  if (rc == GGNN_OK) rc = ggnn_f16_pack_weights(ctx, slot, true, st);
+  ctx->repack_in_place = false;
+  if (rc != GGNN_OK) return rc;
+  ext_of(ctx)->tape.valid = false;
+  return GGNN_OK;
+}
+
+extern "C" int ggnn_get_weights(ggnn_ctx* ctx, int slot, float* W, float* B, float* Wg, float* bg, float* Wc,
+                                float* bc, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (slot < 0 || slot >= GGNN_MAX_SLOTS) GGNN_FAIL(ctx, GGNN_E_ARG, "get_weights: bad slot");
+  if (!ctx->gru_set || !ctx->edge[slot].set) GGNN_FAIL(ctx, GGNN_E_STATE, "get_weights: weights for slot %d not set", slot);
+  device_guard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int h = ctx->h, two_e = ctx->two_e;
+  const ggnn_edge_weights& ew = ctx->edge[slot];
+  auto cp = [&](float* dst, const float* src, size_t n) -> int {
+    if (dst && src) GGNN_CUDA(ctx, cudaMemcpyAsync(dst, src, n * 4, cudaMemcpyDeviceToDevice, st));
+    return GGNN_OK;
+  };
+  GGNN_TRY(cp(W, ew.W, (size_t)two_e * h * h));
+  GGNN_TRY(cp(B, ew.B, (size_t)two_e * h));
+  GGNN_TRY(cp(Wg, ctx->Wg, (size_t)4 * h * h));
+  GGNN_TRY(cp(bg, ctx->bg, (size_t)2 * h));
+  GGNN_TRY(cp(Wc, ctx->Wc, (size_t)2 * h * h));
+  GGNN_TRY(cp(bc, ctx->bc, (size_t)h));
+  return GGNN_OK;
 }
 
 extern "C" int ggnn_set_dropout(ggnn_ctx* ctx, const float* w_mask, const float* state_mask, float keep, int T) {

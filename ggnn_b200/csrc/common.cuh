@@ -46,6 +46,7 @@ struct ggnn_ctx {
   CUtensorMap tm_Wg, tm_Wc, tm_Wg256;  // TMA views of the packed GRU kernels (256-row box: fused kernel)
   unsigned long long* dbg_trace = nullptr;   // device buffer for kernel phase traces (ggnn_debug_trace)
   bool   no_fused = false;   // debugging / A-B switch (GGNN_NO_FUSED=1)
+  bool   repack_in_place = false; // optimizer step: shapes unchanged, packed weight buffers are reused
   bool   no_bits_plan = false; // A-B switch (GGNN_NO_BITS_PLAN=1): dense path goes through the canonical CSR
   int    tm_rows_g = 0, tm_rows_c = 0;
   float* bg_pad = nullptr;   // [2hp]

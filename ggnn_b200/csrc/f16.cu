@@ -679,6 +679,7 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
 bool ggnn_f16_supported(const ggnn_ctx* ctx) { return ctx->hp == HP && ctx->h % 4 == 0; }
 
 static int realloc_h(ggnn_ctx* ctx, void*& p, size_t n_halves) {
+  if (p && ctx->repack_in_place) return GGNN_OK;
   if (p) { cudaFree(p); p = nullptr; }
   GGNN_CUDA(ctx, cudaMalloc(&p, n_halves * 2));
   return GGNN_OK;

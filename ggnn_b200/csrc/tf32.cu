@@ -285,6 +285,7 @@ __global__ void pack_bias_kernel(const float* __restrict__ src, float* __restric
 }
 
 int realloc_f(ggnn_ctx* ctx, float*& p, size_t n) {
+  if (p && ctx->repack_in_place) return GGNN_OK;
   if (p) { cudaFree(p); p = nullptr; }
   GGNN_CUDA(ctx, cudaMalloc(&p, n * sizeof(float)));
   return GGNN_OK;

@@ -474,3 +474,53 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
   GGNN_CUDA(ctx, cudaMemcpyAsync(d_h0, dhn, nh * 4, cudaMemcpyDeviceToDevice, st));
   return GGNN_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// N4: per-tensor clip_by_norm + Adam over the flat gradient buffer (make_train_step,
+// chem_tensorflow.py:483-506: AdamOptimizer(lr, beta1=0.9, beta2=0.999), tf.clip_by_norm per variable)
+namespace {
+
+__global__ void __launch_bounds__(256)
+sumsq_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ out) {
+  float s = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    s = fmaf(g[i], g[i], s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ float ws[8];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += ws[w];
+    atomicAdd(out, t);
+  }
+}
+
+// g_c = g * clip / max(||g||, clip);  m, v, p updated in place (TF1 AdamOptimizer: eps outside the sqrt)
+__global__ void __launch_bounds__(256)
+adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+            int64_t n, const float* __restrict__ sumsq, float clip, float lr_t, float b1, float b2, float eps) {
+  const float norm = sqrtf(*sumsq);
+  const float scale = clip > 0.f ? clip / fmaxf(norm, clip) : 1.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float gc = g[i] * scale;
+    const float mi = b1 * m[i] + (1.f - b1) * gc;
+    const float vi = b2 * v[i] + (1.f - b2) * gc * gc;
+    m[i] = mi; v[i] = vi;
+    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+}  // namespace
+
+int ggnn_adam_segment(ggnn_ctx* ctx, float* param, const float* grad, float* m, float* v, int64_t n,
+                      float* sumsq_slot, float clip, float lr_t, float b1, float b2, float eps, cudaStream_t st) {
+  if (n <= 0 || !param) return GGNN_OK;
+  const int grid = (int)(ceil_div64(n, 256) < (int64_t)ctx->sm_count * 8 ? ceil_div64(n, 256) : (int64_t)ctx->sm_count * 8);
+  sumsq_kernel<<<grid, 256, 0, st>>>(grad, n, sumsq_slot);
+  GGNN_LAUNCHED(ctx);
+  adam_kernel<<<grid, 256, 0, st>>>(param, grad, m, v, n, sumsq_slot, clip, lr_t, b1, b2, eps);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}

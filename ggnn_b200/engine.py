@@ -278,6 +278,32 @@ class Propagator:
         self._check(rc, "ggnn_propagate_backward")
         return d_h0, grads
 
+    def optimizer_step(self, grads: torch.Tensor, lr: float = 0.003, beta1: float = 0.9, beta2: float = 0.999,
+                       eps: float = 1e-8, clip_norm: float = 1.0):
+        """Per-variable clip_by_norm + Adam on the ctx-owned weights (reference make_train_step,
+        chem_tensorflow.py:483-506; defaults: learning_rate .003 `:91`, clamp_gradient_norm 1.0)."""
+        if grads.dtype != torch.float32 or grads.numel() != self.grad_floats or not grads.is_contiguous():
+            raise ValueError(f"grads must be contiguous float32 [{self.grad_floats}]")
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_optimizer_step(self._ctx, _lib.SLOT_MAIN, _ptr(grads), lr, beta1, beta2, eps,
+                                             clip_norm, _stream_ptr(self.device))
+        self._check(rc, "ggnn_optimizer_step")
+
+    def get_weights(self) -> dict:
+        """Current FP32 master weights of slot 0 as device tensors keyed like GGNNWeights fields."""
+        w = self.weights
+        e2, h = w.two_e, w.hidden_size
+        f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.device)
+        out = {"edge_weights": f(e2, h, h), "edge_biases": f(e2, 1, h) if w.edge_biases is not None else None,
+               "gru_gate_kernel": f(2 * h, 2 * h), "gru_gate_bias": f(2 * h), "gru_cand_kernel": f(2 * h, h),
+               "gru_cand_bias": f(h)}
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_get_weights(self._ctx, _lib.SLOT_MAIN, *[_ptr(out[k]) for k in
+                                          ("edge_weights", "edge_biases", "gru_gate_kernel", "gru_gate_bias",
+                                           "gru_cand_kernel", "gru_cand_bias")], _stream_ptr(self.device))
+        self._check(rc, "ggnn_get_weights")
+        return out
+
     def split_grads(self, flat: torch.Tensor) -> dict:
         """Views of the flat gradient buffer, keyed like GGNNWeights fields."""
         w = self.weights

@@ -137,6 +137,18 @@ int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0,
  * This buffer is what the data-parallel trainer all-reduces with NCCL.  Weight gradients are
  * summed with float atomics (order not fixed).  No synchronisation. */
 int64_t ggnn_grad_floats(const ggnn_ctx* ctx);
+/* N4: the optimiser step of make_train_step (chem_tensorflow.py:483-506) on the ctx-owned FP32
+ * master weights of `slot` (and the shared GRU cell): per VARIABLE tf.clip_by_norm(grad, clip_norm)
+ * (the six segments of the flat buffer are the six variables), then TF1 AdamOptimizer
+ *   lr_t = lr*sqrt(1-beta2^t)/(1-beta1^t); m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr_t m/(sqrt(v)+eps)
+ * with ctx-owned moments (zero-initialised, t counted per ctx).  clip_norm <= 0 disables clipping.  The
+ * TF32 / FP16 packed copies are refreshed.  `grads` is the (all-reduced) buffer of
+ * ggnn_propagate_backward.  ggnn_get_weights copies the current master weights out (NULL = skip). */
+int ggnn_optimizer_step(ggnn_ctx* ctx, int slot, const float* grads, float lr, float beta1, float beta2,
+                        float eps, float clip_norm, void* stream);
+int ggnn_get_weights(ggnn_ctx* ctx, int slot, float* W, float* B, float* Wg, float* bg, float* Wc,
+                     float* bc, void* stream);
+
 /* A8: training-time dropout of the path with CALLER-SUPPLIED 0/1 masks (TF's RNG stream cannot be
  * reproduced, so the masks are inputs).  Applies to the NEXT propagate call with GGNN_FLAG_SAVE_TAPE
  * (and to its backward), then is cleared.

@@ -63,3 +63,18 @@ def grads(h0, edges, w, T, d_hT, use_bias=True, dtype=torch.float64, w_mask=None
         g = t.grad if t.grad is not None else torch.zeros_like(t)
         out[k] = g.detach().numpy()
     return hT.detach().numpy(), h0t.grad.detach().numpy(), out
+
+
+def adam_step(params, grads, m, v, t, lr=0.003, beta1=0.9, beta2=0.999, eps=1e-8, clip=1.0):
+    """make_train_step (chem_tensorflow.py:483-506) in NumPy FP64: per-variable tf.clip_by_norm
+    (g * clip / max(||g||_2, clip)) then TF1 AdamOptimizer's update (epsilon outside the square root,
+    bias correction folded into the step size).  Dicts keyed by variable; updates in place; t is 1-based."""
+    lr_t = lr * np.sqrt(1.0 - beta2 ** t) / (1.0 - beta1 ** t)
+    for k in params:
+        g = np.asarray(grads[k], dtype=np.float64)
+        if clip and clip > 0:
+            g = g * clip / max(np.sqrt((g * g).sum()), clip)
+        m[k] = beta1 * m[k] + (1 - beta1) * g
+        v[k] = beta2 * v[k] + (1 - beta2) * g * g
+        params[k] = params[k] - lr_t * m[k] / (np.sqrt(v[k]) + eps)
+    return params

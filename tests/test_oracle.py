@@ -241,3 +241,29 @@ def test_host_scorer_and_batch_builder_match_the_oracle(golden_dir):
             assert list(idx[g, :n, 1]) == r["node_features"] and list(idx[g, :n, 2]) == r["words_index"]
             assert list(idx[g, :n, 3]) == [0] + [e[0] for e in r["graph"]]
             assert np.array_equal(targets[g, 1:n], np.array(r["targets"]))
+
+
+def test_adam_oracle_matches_torch_adam_with_per_tensor_clip():
+    """The NumPy restatement of make_train_step (chem_tensorflow.py:483-506) against torch.optim.Adam (FP64).
+    TF1 puts epsilon outside the UNcorrected root ("epsilon hat"): lr_t m / (sqrt(v) + eps) equals torch's
+    update with eps_torch = eps / sqrt(1 - beta2^t), set per step here, so the two agree to rounding.
+    tf.clip_by_norm is g * clip / max(||g||, clip), applied per variable."""
+    import torch
+    from oracle import grad_oracle as G
+    rng = np.random.default_rng(0)
+    shapes = {"a": (7, 5), "b": (11,)}
+    P = {k: rng.standard_normal(s) for k, s in shapes.items()}
+    M = {k: np.zeros(s) for k, s in shapes.items()}
+    V = {k: np.zeros(s) for k, s in shapes.items()}
+    tp = {k: torch.tensor(P[k].copy(), requires_grad=True) for k in shapes}
+    opt = torch.optim.Adam(list(tp.values()), lr=0.003, betas=(0.9, 0.999), eps=1e-8)
+    for t in range(1, 6):
+        g = {"a": rng.standard_normal(shapes["a"]) * 2.0, "b": rng.standard_normal(shapes["b"]) * 0.01}
+        assert np.linalg.norm(g["a"]) > 1.0 > np.linalg.norm(g["b"])      # one clipped, one not
+        for k in shapes:
+            tp[k].grad = torch.tensor(g[k] * 1.0 / max(np.linalg.norm(g[k]), 1.0))
+        opt.param_groups[0]["eps"] = 1e-8 / np.sqrt(1.0 - 0.999 ** t)
+        opt.step()
+        G.adam_step(P, g, M, V, t)
+        for k in shapes:
+            np.testing.assert_allclose(P[k], tp[k].detach().numpy(), rtol=0, atol=1e-12)
