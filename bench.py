@@ -408,9 +408,10 @@ def run_c5(args):
     prop = ggnn_b200.Propagator(ggnn_b200.from_dict(wd), dev)
     h0, edges, d, N = c5_inputs(per_gpu, 1000 + rank, dev)
     grads = torch.zeros(prop.grad_floats, device=dev)
+    prec = "fp32" if args.precision == "fp32" else "tf32"      # the kind::f16 kernels have no training path
 
-    def step():
-        return gdist.train_step(prop, h0, edges, lambda hT: d, Tc, grads=grads, optimizer={})
+    def step(mode=None):
+        return gdist.train_step(prop, h0, edges, lambda hT: d, Tc, grads=grads, optimizer={}, precision=mode or prec)
 
     def barrier():
         if world > 1:
@@ -439,13 +440,27 @@ def run_c5(args):
         ms = float(tms.item())
     ms_per_step = ms / args.steps
     nnz = int(edges.shape[0])
+    other = None
+    if prec != "fp32" and not args.no_fp32:            # the strict-FP32 training step, same inputs
+        step("fp32"); barrier()
+        e0.record()
+        for _ in range(max(1, args.steps // 2)):
+            step("fp32")
+        e1.record(); barrier()
+        oms = e0.elapsed_time(e1) / max(1, args.steps // 2)
+        if world > 1:
+            t2 = torch.tensor([oms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+            oms = float(t2.item())
+        other = {"fp32": {"value": per_gpu * world / (oms * 1e-3), "unit": "graphs/s", "ms_per_step": oms}}
     if rank == 0:
         flop = 3 * Tc * (nnz * 2 * Hc * Hc + N * 12 * Hc * Hc)       # bwd counted as 2x fwd
         line = {"metric": "GGNN propagation training step graphs/sec (fwd+bwd+clip+Adam, T=4)",
                 "value": per_gpu * world / (ms_per_step * 1e-3), "unit": "graphs/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic",
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32" if prec == "fp32" else "tf32 operands, f32 accumulate / pointwise / optimiser",
+                "data": "synthetic", "other_modes": other,
                 "config": {"workload": "C5 synthetic WSJ-shaped trees, h=400 2E=92 T=4, fwd+bwd of the path + "
                                        "one all-reduce of the 62.9 MB flat weight gradient + per-variable clip_by_norm(1.0) + "
                                        "Adam(0.003) on the ctx-owned weights",

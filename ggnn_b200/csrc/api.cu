@@ -286,11 +286,13 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
   ggnn_tape& tape = ext_of(ctx)->tape;
   tape.valid = false;
   if (flags & GGNN_FLAG_SAVE_TAPE) {      // training forward: keep h, x, r, u, c of every step
-    if (precision != GGNN_PREC_FP32) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE needs GGNN_PREC_FP32");
+    if (precision != GGNN_PREC_FP32 && precision != GGNN_PREC_TF32)
+      GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE needs GGNN_PREC_FP32 or GGNN_PREC_TF32");
+    const bool tf = precision == GGNN_PREC_TF32;
     if (plan.dense_rows) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE: edge list is in dense-row mode (nnz >= N*2E)");
     const size_t nh = (size_t)plan.N * ctx->h;
     GGNN_TRY(arena_reserve(ctx, 2, (size_t)T * TAPE_ARRAYS * nh * 4 + 256, st));
-    tape.plan = plan; tape.T = T; tape.slot = slot; tape.h = ctx->h;
+    tape.plan = plan; tape.T = T; tape.slot = slot; tape.h = ctx->h; tape.tf32 = tf;
     tape.acts = reinterpret_cast<float*>(ext_of(ctx)->ar[2].p);
     ctx_ext* ex = ext_of(ctx);
     tape.w_mask = tape.state_mask = nullptr; tape.keep = 1.f; tape.w_eff = nullptr;
@@ -304,6 +306,7 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
       GGNN_TRY(arena_reserve(ctx, 5, wn * 4 + 256, st));
       tape.w_eff = reinterpret_cast<float*>(ex->ar[5].p);
     }
+    if (tf && T > 0) GGNN_TRY(ggnn_tf32_round_copy(ctx, h_state, h_state, (int64_t)nh, st));
     for (int t = 0; t < T; ++t) {
       GGNN_CUDA(ctx, cudaMemcpyAsync(tape.at(t, TAPE_H), h_state, nh * 4, cudaMemcpyDeviceToDevice, st));
       ggnn_step_bufs tb = sb;
@@ -313,12 +316,17 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
         GGNN_TRY(ggnn_mask_scale(ctx, ctx->edge[slot].W, tape.w_mask + (size_t)t * wn, 1.0f / tape.keep, tape.w_eff,
                                  (int64_t)wn, false, st));
         tb.W_override = tape.w_eff;
+        if (tf) GGNN_TRY(ggnn_tf32_repack_edge(ctx, slot, tape.w_eff, st));   // this step's packed operand
       }
-      GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, tb, h_state, st));
-      if (tape.state_mask)                 // DropoutWrapper(state_keep_prob): the new state is dropped
+      if (tf) GGNN_TRY(ggnn_step_tf32(ctx, slot, plan, tb, h_state, t == T - 1, st));
+      else GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, tb, h_state, st));
+      if (tape.state_mask) {               // DropoutWrapper(state_keep_prob): the new state is dropped
         GGNN_TRY(ggnn_mask_scale(ctx, h_state, tape.state_mask + (size_t)t * nh, 1.0f / tape.keep, h_state,
                                  (int64_t)nh, false, st));
+        if (tf && t < T - 1) GGNN_TRY(ggnn_tf32_round_copy(ctx, h_state, h_state, (int64_t)nh, st));
+      }
     }
+    if (tf && tape.w_mask) GGNN_TRY(ggnn_tf32_repack_edge(ctx, slot, nullptr, st));   // back to the undropped weights
     tape.valid = true;
     return GGNN_OK;
   }
@@ -606,10 +614,12 @@ extern "C" int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* 
   {
     ws_alloc dry(nullptr);
     ggnn_bwd_take_scratch(dry, tape.plan, ctx->h, ctx->two_e, tape.w_mask != nullptr, &sc);
+    if (tape.tf32) ggnn_bwd_take_nt_weights(dry, ctx, &sc);
     GGNN_TRY(arena_reserve(ctx, 3, dry.off + 256, st));
   }
   ws_alloc a(ext_of(ctx)->ar[3].p);
   ggnn_bwd_take_scratch(a, tape.plan, ctx->h, ctx->two_e, tape.w_mask != nullptr, &sc);
+  if (tape.tf32) ggnn_bwd_take_nt_weights(a, ctx, &sc);
   return ggnn_backward_fp32(ctx, tape, sc, d_hT, d_h0, grads, st);
 }
 

@@ -162,11 +162,30 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                            // SWIZZLE_128B
   return d;
 }
+// MN-major TF32 operand tile (the reduction runs over the ROWS of a row-major matrix).  The only layout the
+// tensor core accepts for 32-bit MN-major operands is SWIZZLE_128B with a 32-byte base (layout type 1):
+// the tile is stored as [K rows][128-byte row = 32 floats along M/N], rows 128 B apart, and inside every
+// 4-row group the 32-BYTE chunk index of a row is XORed with (row % 4).  Successive 4-row K groups are
+// `sbo_bytes` apart, successive 32-float M/N groups `lbo_bytes` apart.  One kind::tf32 instruction (K = 8)
+// reads two K groups; the next K step is taken by adding 8 rows to the start address.
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;                            // SWIZZLE_128B_BASE32B
+  return d;
+}
 // instruction descriptor, kind::tf32 / kind::f16: FP32 accumulate, both operands K-major
 //   fmt: 0 = F16, 1 = BF16, 2 = TF32
 __host__ __device__ constexpr uint32_t umma_idesc(int fmt, int M, int N) {
   return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(N >> 3) << 17) |
          ((uint32_t)(M >> 4) << 24);
+}
+// same with both operands MN-major (bits 15 / 16)
+__host__ __device__ constexpr uint32_t umma_idesc_mn(int fmt, int M, int N) {
+  return umma_idesc(fmt, M, N) | (1u << 15) | (1u << 16);
 }
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
                                           uint32_t idesc, uint32_t accumulate) {

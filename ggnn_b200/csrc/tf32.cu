@@ -28,7 +28,7 @@ constexpr int NPROD = 128;                // producer / epilogue threads (warps 
 constexpr int NTHREADS = NPROD + 32;      // + MMA warp
 constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
 
-enum { MODE_MSG = 0, MODE_GATES = 1, MODE_CAND = 2 };
+enum { MODE_MSG = 0, MODE_GATES = 1, MODE_CAND = 2, MODE_NT = 3 };
 
 struct tparams {
   const float* A1;          // [*, h]  K segment 1 source rows
@@ -49,6 +49,13 @@ struct tparams {
   int b_bytes;              // bytes one TMA box of the weight map delivers per K chunk
   __half* out_half;         // MSG: when set, messages are stored as FP16 [M, h] instead of out0
   int round_out;            // GATES: always rounds rh; CAND: round h' to TF32 (not on the last step)
+  int lda1, lda2;           // row strides of A1 / A2 in floats (0 = h)
+  float* tape_r;            // GATES: also store r (training tape) or null
+  float* tape_c;            // CAND: also store the candidate c (training tape) or null
+  // NT (backward, C = A @ B^T with B in its own row-major layout): padded output column n maps to
+  // out0[crow * ldc + (n / hp) * h + n % hp]; crow = row, or c_rowmap[row] with atomic accumulation
+  int ldc;
+  const int32_t* c_rowmap;
 };
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
@@ -69,7 +76,8 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
 
   const float* Bt = p.Bt;
   const float* bias = p.bias;
-  if (MODE == MODE_MSG) {
+  const bool grouped = MODE == MODE_MSG || (MODE == MODE_NT && p.tile_type != nullptr);
+  if (grouped) {
     if ((int)blockIdx.y >= *p.n_tiles) return;        // uniform across the CTA
     const int type = p.tile_type[blockIdx.y];
     Bt += (size_t)type * p.Np * p.Kp;
@@ -114,12 +122,12 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
       const int64_t grow = row0 + rbase + 16 * j;
       src1[j] = -1; src2[j] = -1;
       if (grow < p.M) {
-        if (MODE == MODE_MSG) src1[j] = p.gather[grow];
+        if (MODE == MODE_MSG || (MODE == MODE_NT && p.gather)) { src1[j] = p.gather[grow]; src2[j] = src1[j]; }
         else { src1[j] = grow; src2[j] = grow; }
       }
     }
     int b_row = n0;
-    if (MODE == MODE_MSG) b_row += p.tile_type[blockIdx.y] * p.Np;
+    if (grouped) b_row += p.tile_type[blockIdx.y] * p.Np;
     uint32_t a_off[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -137,6 +145,7 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
       // TF32-rounded where they were produced, so no register staging is needed)
       const bool seg2 = kc >= KC1;
       const float* Asrc = seg2 ? p.A2 : p.A1;
+      const int lda = seg2 ? p.lda2 : p.lda1;
       const int kloc = (seg2 ? kc - KC1 : kc) * BKF + c16 * 4;     // column within the segment
       const bool kin = kloc < p.h;                                 // h % 4 == 0
       const uint32_t a_st = sA + s * A_BYTES;
@@ -144,7 +153,7 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
       for (int j = 0; j < 8; ++j) {
         const int64_t r = seg2 ? src2[j] : src1[j];
         const bool ok = kin && r >= 0;
-        tc::cp_async16(a_st + a_off[j], ok ? (const void*)(Asrc + r * p.h + kloc) : (const void*)Asrc,
+        tc::cp_async16(a_st + a_off[j], ok ? (const void*)(Asrc + r * lda + kloc) : (const void*)Asrc,
                        ok ? 16u : 0u);
       }
       tc::cp_async_arrive(full_bar(s));
@@ -156,6 +165,8 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
     const int64_t row = row0 + warp * 32 + lane;
     bool row_ok = row < p.M;
     if (MODE == MODE_MSG && row_ok) row_ok = p.gather[row] >= 0;
+    int64_t crow = row;
+    if (MODE == MODE_NT && row_ok && p.c_rowmap) { crow = p.c_rowmap[row]; row_ok = crow >= 0; }
     for (int cc = 0; cc < n_tile / 32; ++cc) {
       uint32_t acc[32];
       tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cc * 32), acc);
@@ -163,6 +174,17 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
       const int n = n0 + cc * 32;                      // padded column index of acc[0]
       if (!row_ok) {
         // nothing to store for this row (keep the warp converged for the next tcgen05.ld)
+      } else if (MODE == MODE_NT) {
+        const int nb = n / p.hp, cbase = n - nb * p.hp;
+        float* dst = p.out0 + crow * p.ldc + nb * p.h + cbase;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (cbase + q * 4 >= p.h) break;
+          const float4 v = make_float4(__uint_as_float(acc[q * 4 + 0]), __uint_as_float(acc[q * 4 + 1]),
+                                       __uint_as_float(acc[q * 4 + 2]), __uint_as_float(acc[q * 4 + 3]));
+          if (p.c_rowmap) atomicAdd(reinterpret_cast<float4*>(dst + q * 4), v);
+          else *reinterpret_cast<float4*>(dst + q * 4) = v;
+        }
       } else if (MODE == MODE_MSG || MODE == MODE_CAND) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
@@ -188,11 +210,13 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
           } else {
             const float4 hv = *reinterpret_cast<const float4*>(p.out0 + row * p.h + col);
             const float4 uv = *reinterpret_cast<const float4*>(p.ubuf + row * p.h + col);
+            const float4 cv = make_float4(tanh_f(v[0]), tanh_f(v[1]), tanh_f(v[2]), tanh_f(v[3]));
+            if (p.tape_c) *reinterpret_cast<float4*>(p.tape_c + row * p.h + col) = cv;
             float4 o;
-            o.x = uv.x * hv.x + (1.0f - uv.x) * tanh_f(v[0]);
-            o.y = uv.y * hv.y + (1.0f - uv.y) * tanh_f(v[1]);
-            o.z = uv.z * hv.z + (1.0f - uv.z) * tanh_f(v[2]);
-            o.w = uv.w * hv.w + (1.0f - uv.w) * tanh_f(v[3]);
+            o.x = uv.x * hv.x + (1.0f - uv.x) * cv.x;
+            o.y = uv.y * hv.y + (1.0f - uv.y) * cv.y;
+            o.z = uv.z * hv.z + (1.0f - uv.z) * cv.z;
+            o.w = uv.w * hv.w + (1.0f - uv.w) * cv.w;
             if (p.round_out) {
               o.x = tc::to_tf32(o.x); o.y = tc::to_tf32(o.y); o.z = tc::to_tf32(o.z); o.w = tc::to_tf32(o.w);
             }
@@ -217,6 +241,7 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
             *reinterpret_cast<float4*>(p.out0 + row * p.h + col) =
                 make_float4(tc::to_tf32(g[0] * hv.x), tc::to_tf32(g[1] * hv.y),
                             tc::to_tf32(g[2] * hv.z), tc::to_tf32(g[3] * hv.w));
+            if (p.tape_r) *reinterpret_cast<float4*>(p.tape_r + row * p.h + col) = make_float4(g[0], g[1], g[2], g[3]);
           } else {
             *reinterpret_cast<float4*>(p.out1 + row * p.h + col) = make_float4(g[0], g[1], g[2], g[3]);
           }
@@ -317,8 +342,25 @@ __global__ void round_copy_kernel(const float4* __restrict__ src, float4* __rest
   }
 }
 
+// backward operands: dst[b][rb*hp + r][cb*hp + c] = tf32(src[b][(rb*h + r) * src_ld + cb*h + c]), zero padding
+__global__ void pack_blocks_kernel(const float* __restrict__ src, int src_ld, float* __restrict__ dst, int nbatch,
+                                   int rblocks, int cblocks, int h, int hp) {
+  const int64_t rows = (int64_t)rblocks * hp, cols = (int64_t)cblocks * hp;
+  const int64_t total = (int64_t)nbatch * rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cc = (int)(i % cols);
+    const int rr = (int)((i / cols) % rows);
+    const int64_t b = i / (rows * cols);
+    const int rb = rr / hp, r = rr % hp, cb = cc / hp, c = cc % hp;
+    dst[i] = (r < h && c < h) ? tc::to_tf32(src[(b * rblocks * h + rb * h + r) * src_ld + cb * h + c]) : 0.f;
+  }
+}
+
 template <int MODE>
-int launch(ggnn_ctx* ctx, const tparams& p, const CUtensorMap& tm, unsigned mtiles, cudaStream_t st) {
+int launch(ggnn_ctx* ctx, const tparams& p_in, const CUtensorMap& tm, unsigned mtiles, cudaStream_t st) {
+  tparams p = p_in;
+  if (p.lda1 == 0) p.lda1 = p.h;
+  if (p.lda2 == 0) p.lda2 = p.h;
   static bool attr_set = false;
   if (!attr_set) {
     GGNN_CUDA(ctx, cudaFuncSetAttribute(gemm_tf32_kernel<MODE>,
@@ -369,6 +411,58 @@ static int make_weight_map(ggnn_ctx* ctx, CUtensorMap* tm, float* base, int64_t 
   return ggnn_make_tmap_2d(ctx, tm, base, rows, cols, *box_rows);
 }
 
+// ---- backward (train_tf32.cu): NT contractions on the forward kernel ----------------------
+size_t ggnn_tf32_nt_weight_floats(const ggnn_ctx* ctx) {
+  const size_t hp = ctx->hp;
+  return (size_t)ctx->two_e * hp * hp + 4 * hp * hp + 2 * hp * hp + 64;
+}
+
+void ggnn_tf32_nt_take(ws_alloc& a, const ggnn_ctx* ctx, ggnn_nt_weights* w) {
+  const size_t hp = ctx->hp;
+  w->We = a.take<float>((size_t)ctx->two_e * hp * hp);
+  w->Wg = a.take<float>(4 * hp * hp);
+  w->Wc = a.take<float>(2 * hp * hp);
+}
+
+int ggnn_tf32_pack_nt_edge(ggnn_ctx* ctx, const float* W_src, ggnn_nt_weights* w, cudaStream_t st) {
+  const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
+  pack_blocks_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src, h, w->We, two_e, 1, 1, h, hp);
+  GGNN_LAUNCHED(ctx);
+  return make_weight_map(ctx, &w->tmE, w->We, (int64_t)two_e * hp, hp, &w->rowsE);
+}
+
+int ggnn_tf32_pack_nt_gru(ggnn_ctx* ctx, ggnn_nt_weights* w, cudaStream_t st) {
+  const int h = ctx->h, hp = ctx->hp;
+  pack_blocks_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, 2 * h, w->Wg, 1, 2, 2, h, hp);
+  GGNN_LAUNCHED(ctx);
+  pack_blocks_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, h, w->Wc, 1, 2, 1, h, hp);
+  GGNN_LAUNCHED(ctx);
+  GGNN_TRY(make_weight_map(ctx, &w->tmG, w->Wg, 2 * hp, 2 * hp, &w->rowsG));
+  return make_weight_map(ctx, &w->tmC, w->Wc, 2 * hp, hp, &w->rowsC);
+}
+
+int ggnn_tf32_nt(ggnn_ctx* ctx, const float* A1, const float* A2, int lda, const int32_t* gather, int64_t M,
+                 unsigned mtiles, const float* Bt, const CUtensorMap& tm, int tm_rows, int Kp, int Np,
+                 const int32_t* tile_type, const int32_t* n_tiles, float* out, int ldc,
+                 const int32_t* c_rowmap, cudaStream_t st) {
+  if (mtiles == 0) return GGNN_OK;
+  tparams p{};
+  p.A1 = A1; p.A2 = A2; p.lda1 = lda; p.lda2 = lda; p.gather = gather;
+  p.Bt = Bt; p.h = ctx->h; p.hp = ctx->hp; p.Kp = Kp; p.Np = Np; p.M = M;
+  p.tile_type = tile_type; p.n_tiles = n_tiles;
+  p.out0 = out; p.ldc = ldc; p.c_rowmap = c_rowmap;
+  p.b_bytes = tm_rows * BKF * 4;
+  return launch<MODE_NT>(ctx, p, tm, mtiles, st);
+}
+
+// edge weights of `slot` re-packed from W_src (dropout: this step's effective weights; null = the slot's own)
+int ggnn_tf32_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st) {
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src ? W_src : ew.W, ew.Wt_tf32, ctx->two_e, ctx->h, ctx->hp);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
 bool ggnn_tf32_supported(const ggnn_ctx* ctx) { return ctx->h % 4 == 0 && ctx->hp >= 32; }
 
 // h (any FP32) -> TF32-rounded copy; n = number of floats (multiple of 4). src may equal dst.
@@ -415,7 +509,7 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
   const int h = ctx->h, hp = ctx->hp;
   const ggnn_edge_weights& ew = ctx->edge[slot];
   if (plan.N == 0) return GGNN_OK;
-  const bool fused = ggnn_gru_fused_supported(ctx) && !ctx->no_fused;
+  const bool fused = ggnn_gru_fused_supported(ctx) && !ctx->no_fused && !bufs.tape_r;   // the tape needs x, r, u, c
   if (fused) {
     GGNN_TRY(ggnn_msg_tc_step(ctx, slot, plan, h_state, bufs.msg, st));
   } else if (plan.max_tiles > 0 && plan.nnz > 0) {
@@ -439,7 +533,7 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.A1 = bufs.acts; p.A2 = h_state;
     p.Bt = ctx->Wgt_tf32; p.bias = ctx->bg_pad;
     p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = 2 * hp; p.M = plan.N;
-    p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state;
+    p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state; p.tape_r = bufs.tape_r;
     p.b_bytes = ctx->tm_rows_g * BKF * 4;
     GGNN_TRY(launch<MODE_GATES>(ctx, p, ctx->tm_Wg, mt, st));
   }
@@ -449,7 +543,7 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.A1 = bufs.acts; p.A2 = bufs.rh;
     p.Bt = ctx->Wct_tf32; p.bias = ctx->bc;
     p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = hp; p.M = plan.N;
-    p.out0 = h_state; p.ubuf = bufs.u;
+    p.out0 = h_state; p.ubuf = bufs.u; p.tape_c = bufs.tape_c;
     p.b_bytes = ctx->tm_rows_c * BKF * 4;
     p.round_out = last_step ? 0 : 1;
     GGNN_TRY(launch<MODE_CAND>(ctx, p, ctx->tm_Wc, mt, st));

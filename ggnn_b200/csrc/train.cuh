@@ -1,6 +1,7 @@
 // train.cuh -- training tape + backward of the propagation path (strict FP32), declarations.
 #pragma once
 #include "plan.cuh"
+#include "tf32.cuh"
 
 // per-step saved activations, each [N, h]: state before the step, aggregated messages, gates, candidate
 enum { TAPE_H = 0, TAPE_X = 1, TAPE_R = 2, TAPE_U = 3, TAPE_C = 4, TAPE_ARRAYS = 5 };
@@ -8,6 +9,7 @@ enum { TAPE_H = 0, TAPE_X = 1, TAPE_R = 2, TAPE_U = 3, TAPE_C = 4, TAPE_ARRAYS =
 struct ggnn_tape {
   bool valid = false;
   int T = 0, slot = 0;
+  bool tf32 = false;           // forward ran in GGNN_PREC_TF32: tape holds TF32-rounded operands, backward uses the tensor cores
   ggnn_plan plan;              // lives in the step arena of the forward call
   float* acts = nullptr;       // [T][TAPE_ARRAYS][N*h]
   float* at(int t, int which) const { return acts + ((size_t)t * TAPE_ARRAYS + which) * (size_t)plan.N * h; }
@@ -24,7 +26,9 @@ struct ggnn_bwd_scratch {
   float *dh_a, *dh_b, *dx, *dzc, *rh, *dzg, *dxr;
   int32_t* msg_tgt;
   float* gw_tmp;      // [2E, h, h] per-step dW before the mask is applied (only with w_mask)
+  ggnn_nt_weights ntw; // TF32 backward: weights in their own layout, rounded + padded (only when tape.tf32)
 };
+void ggnn_bwd_take_nt_weights(ws_alloc& a, const ggnn_ctx* ctx, ggnn_bwd_scratch* s);
 void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, int two_e, bool with_w_mask, ggnn_bwd_scratch* s);
 
 // elementwise helpers of the dropout path

@@ -17,6 +17,8 @@
 //                                               message tile type; split over row blocks, atomics)
 #include "plan.cuh"
 #include "train.cuh"
+#include "tf32.cuh"
+#include "tc.cuh"
 
 namespace {
 
@@ -258,37 +260,41 @@ __global__ void gru_bwd_pw1_kernel(const float* __restrict__ dhn, const float* _
                                    const float* __restrict__ r, const float* __restrict__ u,
                                    const float* __restrict__ c, float* __restrict__ dzc,
                                    float* __restrict__ dzg, float* __restrict__ dh, float* __restrict__ rh,
-                                   int64_t N, int h) {
+                                   int64_t N, int h, int rnd) {   // rnd: GEMM operands rounded to TF32
   const int64_t total = N * h;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / h; const int k = (int)(i % h);
     const float g = dhn[i], uu = u[i], cc = c[i], hh = hs[i];
-    dzc[i] = g * (1.f - uu) * (1.f - cc * cc);
-    dzg[n * 2 * h + h + k] = g * (hh - cc) * uu * (1.f - uu);
+    float a = g * (1.f - uu) * (1.f - cc * cc), b = g * (hh - cc) * uu * (1.f - uu), q = r[i] * hh;
+    if (rnd) { a = tc::to_tf32(a); b = tc::to_tf32(b); q = tc::to_tf32(q); }
+    dzc[i] = a;
+    dzg[n * 2 * h + h + k] = b;
     dh[i] = g * uu;
-    rh[i] = r[i] * hh;
+    rh[i] = q;
   }
 }
 // dxr = [dx | drh]:  dzr -> dzg[:, :h];  dh += drh r;  dx = dxr[:, :h]
 __global__ void gru_bwd_pw2_kernel(const float* __restrict__ dxr, const float* __restrict__ hs,
                                    const float* __restrict__ r, float* __restrict__ dzg,
-                                   float* __restrict__ dh, float* __restrict__ dx, int64_t N, int h) {
+                                   float* __restrict__ dh, float* __restrict__ dx, int64_t N, int h, int rnd) {
   const int64_t total = N * h;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / h; const int k = (int)(i % h);
     const float drh = dxr[n * 2 * h + h + k], rr = r[i];
-    dzg[n * 2 * h + k] = drh * hs[i] * rr * (1.f - rr);
+    const float dzr = drh * hs[i] * rr * (1.f - rr);
+    dzg[n * 2 * h + k] = rnd ? tc::to_tf32(dzr) : dzr;
     dh[i] += drh * rr;
     dx[i] = dxr[n * 2 * h + k];
   }
 }
 // dxh = [dx2 | dh2]:  dx += dx2;  dh += dh2
 __global__ void gru_bwd_pw3_kernel(const float* __restrict__ dxh, float* __restrict__ dx,
-                                   float* __restrict__ dh, int64_t N, int h) {
+                                   float* __restrict__ dh, int64_t N, int h, int rnd) {
   const int64_t total = N * h;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / h; const int k = (int)(i % h);
-    dx[i] += dxh[n * 2 * h + k];
+    const float v = dx[i] + dxh[n * 2 * h + k];
+    dx[i] = rnd ? tc::to_tf32(v) : v;
     dh[i] += dxh[n * 2 * h + h + k];
   }
 }
@@ -337,6 +343,7 @@ void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, int two_e,
   s->msg_tgt = a.take<int32_t>((size_t)plan.max_tiles * GGNN_TILE_M);
   s->gw_tmp = with_w_mask ? a.take<float>((size_t)two_e * h * h) : nullptr;
 }
+void ggnn_bwd_take_nt_weights(ws_alloc& a, const ggnn_ctx* ctx, ggnn_bwd_scratch* s) { ggnn_tf32_nt_take(a, ctx, &s->ntw); }
 
 namespace {
 
@@ -359,7 +366,7 @@ int launch_tn(ggnn_ctx* ctx, const tn_params& p, int64_t rows_bound, cudaStream_
 int launch_colsum(ggnn_ctx* ctx, const float* D, int ldd, const int32_t* map, int N, int64_t R,
                   float* out, const int32_t* tile_type, const int32_t* n_tiles, int stride, cudaStream_t st) {
   if (R <= 0) return GGNN_OK;
-  const int rows_per_cta = 1024;
+  const int rows_per_cta = 128;
   dim3 grid((N + 255) / 256, (unsigned)ceil_div64(R, rows_per_cta));
   colsum_kernel<<<grid, 256, 0, st>>>(D, ldd, map, N, R, rows_per_cta, out, tile_type, n_tiles, stride);
   GGNN_LAUNCHED(ctx);
@@ -396,6 +403,13 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
   }
   const unsigned mt = (unsigned)ceil_div64(N, BM);
   const int pw_grid = ctx->sm_count * 8;
+  const bool tf = tape.tf32;                 // contractions on the tensor cores (train_tf32.cu)
+  const int rnd = tf ? 1 : 0, hp = ctx->hp;
+  ggnn_nt_weights ntw = s.ntw;
+  if (tf) {
+    GGNN_TRY(ggnn_tf32_pack_nt_gru(ctx, &ntw, st));
+    if (have_msgs && !tape.w_mask) GGNN_TRY(ggnn_tf32_pack_nt_edge(ctx, ew.W, &ntw, st));
+  }
   const int tn_rows = 2048;
   const float* dhn = d_hT;
   float* dh = s.dh_a;
@@ -413,8 +427,16 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
                                (int64_t)two_e * h * h, false, st));
       Wt = tape.w_eff;
     }
-    gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h);
+    gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h, rnd);
     GGNN_LAUNCHED(ctx);
+    if (tf) {
+      if (tape.w_mask && have_msgs) GGNN_TRY(ggnn_tf32_pack_nt_edge(ctx, Wt, &ntw, st));
+      GGNN_TRY(ggnn_tf32_nt(ctx, s.dzc, nullptr, h, nullptr, N, mt, ntw.Wc, ntw.tmC, ntw.rowsC, hp, 2 * hp, nullptr,
+                            nullptr, s.dxr, 2 * h, nullptr, st));
+      for (int part = 0; part < 2; ++part)
+        GGNN_TRY(ggnn_tf32_tn(ctx, part ? s.rh : xt, h, nullptr, h, s.dzc, h, nullptr, h, N, tn_rows,
+                              gWc + (size_t)part * h * h, h, nullptr, nullptr, 0, st));
+    } else {
     {  // [dx | drh] = dzc @ Wc^T
       nt_params p{};
       p.A1 = s.dzc; p.K1 = h; p.lda = h; p.B = ctx->Wc; p.ldb = h; p.N = 2 * h; p.M = N;
@@ -427,9 +449,17 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
       p.rows_per_cta = tn_rows; p.C = gWc + (size_t)part * h * h; p.ldc = h;
       GGNN_TRY(launch_tn(ctx, p, N, st));
     }
+    }
     GGNN_TRY(launch_colsum(ctx, s.dzc, h, nullptr, h, N, gbc, nullptr, nullptr, 0, st));
-    gru_bwd_pw2_kernel<<<pw_grid, 256, 0, st>>>(s.dxr, ht, rt, s.dzg, dh, s.dx, N, h);
+    gru_bwd_pw2_kernel<<<pw_grid, 256, 0, st>>>(s.dxr, ht, rt, s.dzg, dh, s.dx, N, h, rnd);
     GGNN_LAUNCHED(ctx);
+    if (tf) {
+      GGNN_TRY(ggnn_tf32_nt(ctx, s.dzg, s.dzg + h, 2 * h, nullptr, N, mt, ntw.Wg, ntw.tmG, ntw.rowsG, 2 * hp, 2 * hp,
+                            nullptr, nullptr, s.dxr, 2 * h, nullptr, st));
+      for (int part = 0; part < 2; ++part)
+        GGNN_TRY(ggnn_tf32_tn(ctx, part ? ht : xt, h, nullptr, h, s.dzg, 2 * h, nullptr, 2 * h, N, tn_rows,
+                              gWg + (size_t)part * h * 2 * h, 2 * h, nullptr, nullptr, 0, st));
+    } else {
     {  // [dx2 | dh2] = [dzr, dzu] @ Wg^T
       nt_params p{};
       p.A1 = s.dzg; p.K1 = 2 * h; p.lda = 2 * h; p.B = ctx->Wg; p.ldb = 2 * h; p.N = 2 * h; p.M = N;
@@ -442,10 +472,22 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
       p.rows_per_cta = tn_rows; p.C = gWg + (size_t)part * h * 2 * h; p.ldc = 2 * h;
       GGNN_TRY(launch_tn(ctx, p, N, st));
     }
+    }
     GGNN_TRY(launch_colsum(ctx, s.dzg, 2 * h, nullptr, 2 * h, N, gbg, nullptr, nullptr, 0, st));
-    gru_bwd_pw3_kernel<<<pw_grid, 256, 0, st>>>(s.dxr, s.dx, dh, N, h);
+    gru_bwd_pw3_kernel<<<pw_grid, 256, 0, st>>>(s.dxr, s.dx, dh, N, h, rnd);
     GGNN_LAUNCHED(ctx);
-    if (have_msgs) {
+    if (have_msgs && tf) {
+      float* gw = tape.w_mask ? s.gw_tmp : gW;
+      GGNN_TRY(ggnn_tf32_nt(ctx, s.dx, nullptr, h, s.msg_tgt, mrows, (unsigned)plan.max_tiles, ntw.We, ntw.tmE, ntw.rowsE,
+                            hp, hp, plan.tile_type, plan.n_tiles, dh, h, plan.msg_src, st));
+      if (tape.w_mask) GGNN_CUDA(ctx, cudaMemsetAsync(s.gw_tmp, 0, (size_t)two_e * h * h * 4, st));
+      GGNN_TRY(ggnn_tf32_tn(ctx, ht, h, plan.msg_src, h, s.dx, h, s.msg_tgt, h, mrows, 8 * GGNN_TILE_M, gw, h,
+                            plan.tile_type, plan.n_tiles, (int64_t)h * h, st));
+      if (tape.w_mask)
+        GGNN_TRY(ggnn_mask_scale(ctx, s.gw_tmp, tape.w_mask + (size_t)t * two_e * h * h, inv_keep, gW,
+                                 (int64_t)two_e * h * h, true, st));
+      GGNN_TRY(launch_colsum(ctx, s.dx, h, s.msg_tgt, h, mrows, gB, plan.tile_type, plan.n_tiles, h, st));
+    } else if (have_msgs) {
       {  // dh[src_j] += dx[tgt_j] @ W_e^T
         nt_params p{};
         p.A1 = s.dx; p.K1 = h; p.lda = h; p.a_rowmap = s.msg_tgt;

@@ -84,12 +84,12 @@ def test_backward_edge_cases():
     prop.propagate_edges(h0, e0, num_timesteps=0, save_tape=True)
     dh0, flat = prop.backward(d)
     assert torch.equal(dh0, d) and float(flat.abs().max()) == 0.0
-    # the tape is dropped by a non-tape call; TF32 cannot tape
+    # the tape is dropped by a non-tape call; the FP16 mode cannot tape
     prop.propagate_edges(h0, e0, num_timesteps=1)
     with pytest.raises(RuntimeError):
         prop.backward(d)
     with pytest.raises(RuntimeError):
-        prop.propagate_edges(h0, e0, num_timesteps=1, precision="tf32", save_tape=True)
+        prop.propagate_edges(h0, e0, num_timesteps=1, precision="f16", save_tape=True)
 
 
 def test_train_step_helper_single_process():
@@ -180,3 +180,92 @@ def test_training_loop_reduces_loss():
         prop.optimizer_step(flat)
     assert losses[-1] < 0.8 * losses[0], losses[::5]
     assert all(np.isfinite(losses))
+
+
+# ---------------------------------------------------------------------------------------------------
+# tensor-core training path: forward with the tape in GGNN_PREC_TF32, backward on tcgen05 kind::tf32
+# (NT contractions on the forward kernel, TN contractions with MN-major operands).  Tolerance: the
+# north_star bound for TF32-input / FP32-accumulate arithmetic, 2e-3 norm-wise per tensor against the
+# FP64 autograd oracle (measured 3e-4 .. 9e-4).
+TOL_TF32 = 2e-3
+
+
+def _check_tf32(prop, hT, dh0, flat, ref):
+    rT, rh0, rg = ref
+    assert O.normwise_err(hT.cpu().numpy(), rT) <= TOL_TF32
+    assert O.normwise_err(dh0.cpu().numpy(), rh0) <= TOL_TF32
+    g = prop.split_grads(flat)
+    for k, r in rg.items():
+        got = g[k].cpu().numpy().reshape(r.shape)
+        if np.abs(r).max() == 0:
+            assert np.abs(got).max() == 0, k
+            continue
+        e = O.normwise_err(got, r)
+        assert e <= TOL_TF32, (k, e)
+        assert e > 1e-6, (k, "suspiciously exact: did the FP32 path run?")
+
+
+@pytest.mark.parametrize("b,v,E,h,T", [(4, 16, 5, 64, 3), (3, 32, 10, 100, 4), (2, 128, 46, 128, 2),
+                                       (6, 24, 8, 400, 2), (40, 40, 46, 400, 4), (5, 20, 3, 36, 1)])
+def test_backward_tf32_edges(b, v, E, h, T):
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=b + T)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision="tf32",
+                              save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    _check_tf32(prop, hT, dh0, flat, G.grads(h0, edges.numpy(), w, T, d))
+
+
+def test_backward_tf32_dense_ragged_no_bias_and_no_edges():
+    b, v, E, h, T = 5, 20, 6, 96, 3
+    lengths = torch.tensor([19, 3, 11, 1, 7])
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=9, lengths=lengths, bias=False)
+    adj = synth.dense_adjacency(tri, v, E).cuda()
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    hT = prop.propagate_dense(torch.from_numpy(h0).cuda().view(b, v, h), adj, num_timesteps=T, precision="tf32",
+                              save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda().view(b, v, h))
+    ref = G.grads(h0, O.dense_to_edges(adj.cpu().numpy()), w, T, d)
+    _check_tf32(prop, hT.view(b * v, h), dh0.view(b * v, h), flat, ref)
+    # no edges at all: GRU-only gradients, edge gradients exactly zero
+    e0 = torch.zeros(0, 3, dtype=torch.int32, device="cuda")
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), e0, num_timesteps=2, precision="tf32", save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    _check_tf32(prop, hT, dh0, flat, G.grads(h0, np.zeros((0, 3), np.int64), w, 2, d))
+
+
+def test_training_dropout_tf32():
+    b, v, E, h, T, keep = 4, 16, 5, 64, 3, 0.9
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=21)
+    rng = np.random.default_rng(3)
+    wm = (rng.random((T, 2 * E, h, h)) < keep).astype(np.float32)
+    sm = (rng.random((T, b * v, h)) < keep).astype(np.float32)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    prop.set_dropout(torch.from_numpy(wm).cuda(), torch.from_numpy(sm).cuda(), keep, T)
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision="tf32",
+                              save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    _check_tf32(prop, hT, dh0, flat, G.grads(h0, edges.numpy(), w, T, d, w_mask=wm, state_mask=sm, keep=keep))
+    # the packed weights are restored after the dropped forward: a plain TF32 call matches the oracle again
+    out = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision="tf32")
+    assert O.normwise_err(out.cpu().numpy(), O.propagate_edges(h0, edges.numpy(), w, T)) <= TOL_TF32
+
+
+def test_training_loop_tf32_tracks_fp32():
+    """20 optimiser steps on one batch in both modes from the same start: the TF32 loss curve follows the
+    FP32 one (relative difference of the final loss below 2 %), and both fall."""
+    b, v, E, h, T = 8, 16, 4, 64, 3
+    tri, edges, w, h0, _ = _case(b, v, E, h, seed=21)
+    y = torch.from_numpy(np.random.default_rng(2).uniform(-0.5, 0.5, (b * v, h)).astype(np.float32)).cuda()
+    h0d, ed = torch.from_numpy(h0).cuda(), edges.cuda()
+    final = {}
+    for prec in ("fp32", "tf32"):
+        prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+        for _ in range(20):
+            hT = prop.propagate_edges(h0d, ed, num_timesteps=T, precision=prec, save_tape=True)
+            diff = hT - y
+            loss = float(0.5 * (diff * diff).sum())
+            _, flat = prop.backward(diff.contiguous())
+            prop.optimizer_step(flat)
+        final[prec] = loss
+    assert abs(final["tf32"] - final["fp32"]) <= 0.02 * final["fp32"], final
