@@ -434,7 +434,7 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
       GGNN_TRY(ggnn_tf32_nt(ctx, s.dzc, nullptr, h, nullptr, N, mt, ntw.Wc, ntw.tmC, ntw.rowsC, hp, 2 * hp, nullptr,
                             nullptr, s.dxr, 2 * h, nullptr, st));
       for (int part = 0; part < 2; ++part)
-        GGNN_TRY(ggnn_tf32_tn(ctx, part ? s.rh : xt, h, nullptr, h, s.dzc, h, nullptr, h, N, tn_rows,
+        GGNN_TRY(ggnn_tf32_tn(ctx, part ? s.rh : xt, h, nullptr, h, s.dzc, h, nullptr, h, N, 0,
                               gWc + (size_t)part * h * h, h, nullptr, nullptr, 0, st));
     } else {
     {  // [dx | drh] = dzc @ Wc^T
@@ -457,7 +457,7 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
       GGNN_TRY(ggnn_tf32_nt(ctx, s.dzg, s.dzg + h, 2 * h, nullptr, N, mt, ntw.Wg, ntw.tmG, ntw.rowsG, 2 * hp, 2 * hp,
                             nullptr, nullptr, s.dxr, 2 * h, nullptr, st));
       for (int part = 0; part < 2; ++part)
-        GGNN_TRY(ggnn_tf32_tn(ctx, part ? ht : xt, h, nullptr, h, s.dzg, 2 * h, nullptr, 2 * h, N, tn_rows,
+        GGNN_TRY(ggnn_tf32_tn(ctx, part ? ht : xt, h, nullptr, h, s.dzg, 2 * h, nullptr, 2 * h, N, 0,
                               gWg + (size_t)part * h * 2 * h, 2 * h, nullptr, nullptr, 0, st));
     } else {
     {  // [dx2 | dh2] = [dzr, dzu] @ Wg^T

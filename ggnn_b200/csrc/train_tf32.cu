@@ -15,20 +15,22 @@
 
 namespace tn {
 
-constexpr int BMo = 128;                  // output rows per CTA (columns of X) = UMMA M = TMEM lanes
-constexpr int BNo = 128;                  // output columns per CTA (columns of D) = UMMA N = TMEM columns
-constexpr int RK = 32;                    // reduction rows per stage (4 MMAs of K = 8)
+constexpr int BMo = 256;                  // output rows per CTA (columns of X): two UMMA M = 128 halves
+constexpr int BNo = 256;                  // max output columns per CTA (columns of D) = UMMA N
+constexpr int RK = 32;                    // reduction rows per stage (4 MMAs of K = 8 per half)
 constexpr int STAGES = 3;
 constexpr int GROUP_BYTES = RK * 128;     // one 32-float M/N group of a stage: 32 rows x 128 B
-constexpr int A_BYTES = (BMo / 32) * GROUP_BYTES;   // 16 KB
-constexpr int B_BYTES = (BNo / 32) * GROUP_BYTES;   // 16 KB
+constexpr int A_BYTES = (BMo / 32) * GROUP_BYTES;   // 32 KB
+constexpr int B_BYTES = (BNo / 32) * GROUP_BYTES;   // 32 KB
 constexpr int NPROD = 128;
 constexpr int NTHREADS = NPROD + 32;
-constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256;   // 2 CTAs / SM
+constexpr int TMEM_COLS = 512;            // two 128 x 256 FP32 accumulators: the whole tensor memory of the SM
+constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256;
 
 struct params {
   const float* X; int ldx; const int32_t* x_rowmap; int K1;   // X [R, K1], rows optionally gathered (-1 = zero)
   const float* D; int ldd; const int32_t* d_rowmap; int N;    // D [R, N]
+  int bn;                                                     // output columns per CTA (multiple of 32, <= 256)
   int64_t R; int rows_per_cta;                                // multiple of 128
   float* C; int ldc;                                          // [K1, N] (+ type * c_type_stride when grouped)
   const int32_t* tile_type; const int32_t* n_tiles; int64_t c_type_stride;
@@ -45,16 +47,19 @@ __device__ __forceinline__ int64_t segment_end(const params& p, int64_t seg_begi
   return e < r_end ? e : r_end;
 }
 
-__global__ void __launch_bounds__(NTHREADS)
+__global__ void __launch_bounds__(NTHREADS, 1)
 tn_tc_kernel(const params p) {
   extern __shared__ uint8_t smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n0 = blockIdx.x * BNo, k0 = blockIdx.y * BMo;
+  const int n0 = blockIdx.x * p.bn, k0 = blockIdx.y * BMo;
   int64_t r_begin = (int64_t)blockIdx.z * p.rows_per_cta, r_end = r_begin + p.rows_per_cta;
   int64_t R = p.R;
   if (p.tile_type) R = (int64_t)(*p.n_tiles) * GGNN_TILE_M;
   if (r_end > R) r_end = R;
   if (r_begin >= r_end) return;                         // uniform
+  const int n_valid = min(p.bn, ((p.N - n0) + 31) & ~31);          // UMMA N of this CTA (multiple of 32)
+  const int halves = (p.K1 - k0 > 128) ? 2 : 1;                     // active 128-row halves of the output tile
+  const int a_groups = halves * 4, b_groups = n_valid >> 5;
 
   const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sA = base, sB = base + STAGES * A_BYTES;
@@ -73,22 +78,21 @@ tn_tc_kernel(const params p) {
     tc::mbar_init(accum_bar, 1);
     tc::fence_barrier_init();
   }
-  if (warp == 0) tc::tmem_alloc(tmem_slot, BNo);
+  if (warp == 0) tc::tmem_alloc(tmem_slot, TMEM_COLS);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
 
   if (warp < 4) {
-    // ===== producers: warp w fills M/N group w (32 floats) of both operands; lane = (row%4, 16-byte chunk)
+    // ===== producers: warp w fills M/N groups w and w + 4 (32 floats each) of both operands;
+    //       lane = (row % 4, 16-byte chunk of the 128-byte row)
     const int c16 = lane & 7, rsub = lane >> 3;
-    const int xcol = k0 + warp * 32 + c16 * 4, dcol = n0 + warp * 32 + c16 * 4;
-    const bool x_in = xcol < p.K1, d_in = dcol < p.N;            // K1, N multiples of 4
     uint32_t off[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int rr = rsub + 4 * j;
-      off[j] = warp * GROUP_BYTES + rr * 128 + ((((c16 >> 1) ^ (rr & 3)) << 5) | ((c16 & 1) << 4));   // 32-byte-base swizzle
+      off[j] = rr * 128 + ((((c16 >> 1) ^ (rr & 3)) << 5) | ((c16 & 1) << 4));   // 32-byte-base swizzle
     }
     int it = 0, seg = 0;
     for (int64_t seg_begin = r_begin; seg_begin < r_end; ++seg) {
@@ -97,39 +101,63 @@ tn_tc_kernel(const params p) {
         const int s = it % STAGES;
         if (it >= STAGES) tc::mbar_wait(empty_bar(s), ((it / STAGES) - 1) & 1);
         const uint32_t a_st = sA + s * A_BYTES, b_st = sB + s * B_BYTES;
+        int64_t xs[8], ds[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int64_t r = r0 + rsub + 4 * j;
-          int64_t xs = -1, ds = -1;
+          xs[j] = -1; ds[j] = -1;
           if (r < seg_end) {
-            xs = p.x_rowmap ? (int64_t)p.x_rowmap[r] : r;
-            ds = p.d_rowmap ? (int64_t)p.d_rowmap[r] : r;
+            xs[j] = p.x_rowmap ? (int64_t)p.x_rowmap[r] : r;
+            ds[j] = p.d_rowmap ? (int64_t)p.d_rowmap[r] : r;
           }
-          const bool xok = x_in && xs >= 0, dok = d_in && ds >= 0;
-          tc::cp_async16(a_st + off[j], xok ? (const void*)(p.X + xs * p.ldx + xcol) : (const void*)p.X, xok ? 16u : 0u);
-          tc::cp_async16(b_st + off[j], dok ? (const void*)(p.D + ds * p.ldd + dcol) : (const void*)p.D, dok ? 16u : 0u);
+        }
+#pragma unroll
+        for (int gg = 0; gg < 2; ++gg) {
+          const int g = warp + 4 * gg;
+          if (g < a_groups) {
+            const int xcol = k0 + g * 32 + c16 * 4;
+            const bool in = xcol < p.K1;                           // K1 multiple of 4
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const bool ok = in && xs[j] >= 0;
+              tc::cp_async16(a_st + g * GROUP_BYTES + off[j],
+                             ok ? (const void*)(p.X + xs[j] * p.ldx + xcol) : (const void*)p.X, ok ? 16u : 0u);
+            }
+          }
+          if (g < b_groups) {
+            const int dcol = n0 + g * 32 + c16 * 4;
+            const bool in = dcol < p.N;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const bool ok = in && ds[j] >= 0;
+              tc::cp_async16(b_st + g * GROUP_BYTES + off[j],
+                             ok ? (const void*)(p.D + ds[j] * p.ldd + dcol) : (const void*)p.D, ok ? 16u : 0u);
+            }
+          }
         }
         tc::cp_async_arrive(full_bar(s));
       }
-      // ===== epilogue of this segment: C[type] += accumulator (lane = output row)
+      // ===== epilogue of this segment: C[type] += accumulators (TMEM lane = output row)
       tc::mbar_wait(accum_bar, seg & 1);
       tc::fence_after_sync();
       const int type = p.tile_type ? p.tile_type[seg_begin / GGNN_TILE_M] : 0;
-      const int krow = k0 + warp * 32 + lane;
-      float* crow = p.C + (size_t)type * p.c_type_stride + (size_t)krow * p.ldc;
+      for (int hf = 0; hf < halves; ++hf) {
+        const int krow = k0 + hf * 128 + warp * 32 + lane;
+        float* crow = p.C + (size_t)type * p.c_type_stride + (size_t)krow * p.ldc;
 #pragma unroll 1
-      for (int cc = 0; cc < BNo / 32; ++cc) {
-        uint32_t acc[32];
-        tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cc * 32), acc);
-        tc::tmem_ld_wait();
-        if (krow < p.K1) {
+        for (int cc = 0; cc < b_groups; ++cc) {
+          uint32_t acc[32];
+          tc::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(hf * BNo + cc * 32), acc);
+          tc::tmem_ld_wait();
+          if (krow < p.K1) {
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const int n = n0 + cc * 32 + q * 4;
-            if (n >= p.N) break;
-            atomicAdd(reinterpret_cast<float4*>(crow + n),
-                      make_float4(__uint_as_float(acc[q * 4 + 0]), __uint_as_float(acc[q * 4 + 1]),
-                                  __uint_as_float(acc[q * 4 + 2]), __uint_as_float(acc[q * 4 + 3])));
+            for (int q = 0; q < 8; ++q) {
+              const int n = n0 + cc * 32 + q * 4;
+              if (n >= p.N) break;
+              atomicAdd(reinterpret_cast<float4*>(crow + n),
+                        make_float4(__uint_as_float(acc[q * 4 + 0]), __uint_as_float(acc[q * 4 + 1]),
+                                    __uint_as_float(acc[q * 4 + 2]), __uint_as_float(acc[q * 4 + 3])));
+            }
           }
         }
       }
@@ -139,7 +167,7 @@ tn_tc_kernel(const params p) {
   } else {
     // ===== MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = tc::umma_idesc_mn(/*TF32*/ 2, BMo, BNo);
+      const uint32_t idesc = tc::umma_idesc_mn(/*TF32*/ 2, 128, n_valid);
       int it = 0;
       for (int64_t seg_begin = r_begin; seg_begin < r_end;) {
         const int64_t seg_end = segment_end(p, seg_begin, r_end);
@@ -150,10 +178,13 @@ tn_tc_kernel(const params p) {
           tc::fence_proxy_async();                      // cp.async (generic proxy) writes -> async-proxy reads
           tc::fence_after_sync();
           const uint32_t a0 = sA + s * A_BYTES, b0 = sB + s * B_BYTES;
+          for (int hf = 0; hf < halves; ++hf) {
 #pragma unroll
-          for (int k = 0; k < RK / 8; ++k) {
-            tc::umma_tf32(tmem_base, tc::umma_desc_mn_sw128_32b(a0 + k * 1024, GROUP_BYTES, 512),
-                          tc::umma_desc_mn_sw128_32b(b0 + k * 1024, GROUP_BYTES, 512), idesc, !(first && k == 0));
+            for (int k = 0; k < RK / 8; ++k) {
+              tc::umma_tf32(tmem_base + hf * BNo,
+                            tc::umma_desc_mn_sw128_32b(a0 + hf * 4 * GROUP_BYTES + k * 1024, GROUP_BYTES, 512),
+                            tc::umma_desc_mn_sw128_32b(b0 + k * 1024, GROUP_BYTES, 512), idesc, !(first && k == 0));
+            }
           }
           first = false;
           tc::umma_commit(empty_bar(s));
@@ -167,7 +198,7 @@ tn_tc_kernel(const params p) {
 
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem_base, BNo);
+  if (warp == 0) tc::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 }  // namespace tn
@@ -184,9 +215,18 @@ int ggnn_tf32_tn(ggnn_ctx* ctx, const float* X, int ldx, const int32_t* x_rowmap
   tn::params p{};
   p.X = X; p.ldx = ldx; p.x_rowmap = x_rowmap; p.K1 = K1;
   p.D = D; p.ldd = ldd; p.d_rowmap = d_rowmap; p.N = N;
+  // balanced column tiles: as few as 256 allows, equal width rounded up to 32
+  const int ntiles = (N + tn::BNo - 1) / tn::BNo;
+  p.bn = (int)align_up((size_t)((N + ntiles - 1) / ntiles), 32);
+  const int ktiles = (K1 + tn::BMo - 1) / tn::BMo;
+  const int gx = (N + p.bn - 1) / p.bn;
+  if (rows_per_cta <= 0) {          // ungrouped: about two waves of equal CTAs
+    const int64_t chunks = (2 * (int64_t)ctx->sm_count) / ((int64_t)gx * ktiles) > 0 ? (2 * (int64_t)ctx->sm_count) / ((int64_t)gx * ktiles) : 1;
+    rows_per_cta = (int)align_up((size_t)ceil_div64(R, chunks), 128);
+  }
   p.R = R; p.rows_per_cta = rows_per_cta; p.C = C; p.ldc = ldc;
   p.tile_type = tile_type; p.n_tiles = n_tiles; p.c_type_stride = c_type_stride;
-  dim3 grid((N + tn::BNo - 1) / tn::BNo, (K1 + tn::BMo - 1) / tn::BMo, (unsigned)ceil_div64(R, rows_per_cta));
+  dim3 grid(gx, ktiles, (unsigned)ceil_div64(R, rows_per_cta));
   tn::tn_tc_kernel<<<grid, tn::NTHREADS, tn::SMEM_BYTES, st>>>(p);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
