@@ -270,6 +270,20 @@ def run_gpu(args):
            "note": "ggnn_b200.compute_final_node_representations on pinned host tensors: dense "
                    "FP32 adjacency (6.03 MB/graph, the reference's feed format) + states H2D, result D2H"}
 
+    # context for the e2e figure: what a bare pinned-host -> device copy of the same adjacency reaches on this box
+    d_tmp = torch.empty_like(adj_host, device=dev)
+    d_tmp.copy_(adj_host, non_blocking=True)
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(3):
+        d_tmp.copy_(adj_host, non_blocking=True)
+    c1.record()
+    torch.cuda.synchronize()
+    e2e["h2d_copy_peak_gbps"] = 3 * adj_host.numel() * 4 / (c0.elapsed_time(c1) * 1e-3) / 1e9
+    e2e["achieved_bus_gbps"] = (e2e["h2d_bytes_per_step"] + e2e["d2h_bytes_per_step"]) / e2e_s / 1e9
+    del d_tmp
+
     # same graphs handed over as (src, channel, dst) triples: no dense adjacency on the bus
     edges_host = synth.global_edge_list(tri[:ne].cpu(), V, E).pin_memory()
     h0_flat = h0_host.view(ne * V, H)
@@ -410,8 +424,15 @@ def run_c5(args):
     grads = torch.zeros(prop.grad_floats, device=dev)
     prec = "fp32" if args.precision == "fp32" else "tf32"      # the kind::f16 kernels have no training path
 
+    drop = None
+    if args.c5_keep < 1.0:           # keep-prob 0.9 with supplied masks in the timed run
+        gm = torch.Generator(device=dev).manual_seed(77 + rank)
+        drop = ((torch.rand(Tc, TWO_E, Hc, Hc, device=dev, generator=gm) < args.c5_keep).float(),
+                (torch.rand(Tc, N, Hc, device=dev, generator=gm) < args.c5_keep).float(), args.c5_keep)
+
     def step(mode=None):
-        return gdist.train_step(prop, h0, edges, lambda hT: d, Tc, grads=grads, optimizer={}, precision=mode or prec)
+        return gdist.train_step(prop, h0, edges, lambda hT: d, Tc, grads=grads, optimizer={}, precision=mode or prec,
+                                dropout=drop)
 
     def barrier():
         if world > 1:
@@ -463,7 +484,8 @@ def run_c5(args):
                 "data": "synthetic", "other_modes": other,
                 "config": {"workload": "C5 synthetic WSJ-shaped trees, h=400 2E=92 T=4, fwd+bwd of the path + "
                                        "one all-reduce of the 62.9 MB flat weight gradient + per-variable clip_by_norm(1.0) + "
-                                       "Adam(0.003) on the ctx-owned weights",
+                                       "Adam(0.003) on the ctx-owned weights; edge-weight and state dropout with supplied masks, "
+                                       f"keep-prob {args.c5_keep}",
                            "graphs_per_gpu": per_gpu, "nodes_per_gpu": N, "edges_per_gpu": nnz,
                            "parallelism": f"data parallel x{world}, NCCL all-reduce (sum) of {prop.grad_floats} floats"},
                 "achieved_tflops_algorithmic_per_gpu": flop / (ms_per_step * 1e-3) / 1e12,
@@ -590,6 +612,7 @@ def main():
                     help="c3 = the headline forward benchmark; c5 = training step (secondary line)")
     ap.add_argument("--c4-graphs", type=int, default=64, help="graphs per GPU of the c4 workload")
     ap.add_argument("--c5-graphs", type=int, default=2048, help="graphs per GPU of the c5 workload")
+    ap.add_argument("--c5-keep", type=float, default=0.9, help="dropout keep-prob of the c5 timed run (1.0 = no masks)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -57,6 +57,78 @@ def _to_device(x, device, dtype=None, name="tensor"):
     raise ValueError(f"{name} must be a numpy array or torch tensor, got {type(x).__name__}")
 
 
+_streams = {}       # (thread id, device index) -> (copy-in, compute, copy-out) streams of the host pipeline
+_HOST_CHUNK_BYTES = 96 << 20
+
+
+def _as_host_tensor(x, dtype=None):
+    if isinstance(x, np.ndarray):
+        if dtype is not None and x.dtype != dtype:
+            x = x.astype(dtype)
+        x = torch.from_numpy(np.ascontiguousarray(x))
+    return x.contiguous()
+
+
+def _propagate_dense_from_host(prop: Propagator, h0, adj, num_timesteps, fixed_ts, precision):
+    """Host-resident inputs (the reference's feed_dict arrays): the batch is cut into chunks of ~96 MB of
+    adjacency and pipelined over three streams -- H2D of chunk k+1 (straight from the caller's memory when it
+    is pinned, else through a pinned double buffer) overlaps compaction + propagation of chunk k and the D2H
+    of chunk k-1 -- so the call runs at the speed of the bus.  Returns a pinned CPU tensor."""
+    dev = prop.device
+    b, v, h = h0.shape
+    per_graph = adj[0].numel() * adj.element_size()
+    cg = int(max(1, min(b, _HOST_CHUNK_BYTES // max(per_graph, 1))))
+    key = (threading.get_ident(), dev.index)
+    if key not in _streams:
+        _streams[key] = tuple(torch.cuda.Stream(dev) for _ in range(3))
+    s_in, s_run, s_out = _streams[key]
+    cur = torch.cuda.current_stream(dev)
+    d_adj = [torch.empty((cg,) + tuple(adj.shape[1:]), dtype=adj.dtype, device=dev) for _ in range(2)]
+    d_h = torch.empty((b, v, h), dtype=torch.float32, device=dev)
+    out_host = torch.empty((b, v, h), dtype=torch.float32, pin_memory=True)
+    stage = None
+    if not adj.is_pinned():
+        stage = [torch.empty((cg,) + tuple(adj.shape[1:]), dtype=adj.dtype, pin_memory=True) for _ in range(2)]
+    copied = [torch.cuda.Event() for _ in range(2)]
+    done = [torch.cuda.Event() for _ in range(2)]
+    for st in (s_in, s_run, s_out):
+        st.wait_stream(cur)
+    nchunks = (b + cg - 1) // cg
+
+    def enqueue_copy(k):
+        slot, lo, hi = k & 1, k * cg, min(b, (k + 1) * cg)
+        src = adj[lo:hi]
+        if stage is not None:
+            if k >= 2:
+                copied[slot].synchronize()            # the DMA out of this staging buffer has finished
+            stage[slot][:hi - lo].copy_(src)
+            src = stage[slot][:hi - lo]
+        with torch.cuda.stream(s_in):
+            if k >= 2:
+                s_in.wait_event(done[slot])           # chunk k-2 no longer reads this device buffer
+            d_adj[slot][:hi - lo].copy_(src, non_blocking=True)
+            d_h[lo:hi].copy_(h0[lo:hi], non_blocking=True)
+            copied[slot].record(s_in)
+
+    enqueue_copy(0)
+    for k in range(nchunks):
+        slot, lo, hi = k & 1, k * cg, min(b, (k + 1) * cg)
+        if k + 1 < nchunks:
+            enqueue_copy(k + 1)                        # in flight while this chunk is planned and propagated
+        with torch.cuda.stream(s_run):
+            s_run.wait_event(copied[slot])
+            prop.propagate_dense(d_h[lo:hi], d_adj[slot][:hi - lo], num_timesteps=num_timesteps, fixed_ts=fixed_ts,
+                                 precision=precision, out=d_h[lo:hi])
+            done[slot].record(s_run)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(done[slot])
+            out_host[lo:hi].copy_(d_h[lo:hi], non_blocking=True)
+    s_out.synchronize()
+    for t in d_adj + [d_h]:                            # the caching allocator must not hand these out too early
+        t.record_stream(s_in); t.record_stream(s_run); t.record_stream(s_out)
+    return out_host
+
+
 def _device_of(*xs):
     for x in xs:
         if isinstance(x, torch.Tensor) and x.device.type == "cuda":
@@ -96,9 +168,24 @@ def compute_final_node_representations(initial_node_representations, adjacency_m
         raise RuntimeError("ggnn_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     dev = weights.device if isinstance(weights, Propagator) else _device_of(initial_node_representations, adjacency_matrix)
     prop = get_propagator(weights, dev)
-    h0, kind = _to_device(initial_node_representations, dev, np.float32, "initial_node_representations")
     if isinstance(adjacency_matrix, np.ndarray) and adjacency_matrix.dtype not in (np.float32, np.uint8):
         adjacency_matrix = adjacency_matrix.astype(np.float32)     # the placeholder is tf.float32
+    host = lambda x: isinstance(x, np.ndarray) or (isinstance(x, torch.Tensor) and x.device.type == "cpu")
+    if host(initial_node_representations) and host(adjacency_matrix) and not skip_padded:
+        kind = "numpy" if isinstance(initial_node_representations, np.ndarray) else "cpu"
+        h0 = _as_host_tensor(initial_node_representations, np.float32)
+        adj = _as_host_tensor(adjacency_matrix)
+        if adj.dtype == torch.float64:
+            adj = adj.float()
+        if h0.dim() != 3 or adj.dim() != 4 or h0.dtype != torch.float32 or adj.dtype not in (torch.float32, torch.uint8) \
+                or adj.shape[0] != h0.shape[0] or adj.shape[2] != h0.shape[1] or adj.shape[3] != h0.shape[1] \
+                or h0.shape[2] != prop.weights.hidden_size or adj.shape[1] != prop.weights.two_e:
+            raise ValueError(f"states {tuple(h0.shape)} {h0.dtype} / adjacency {tuple(adj.shape)} {adj.dtype} do not "
+                             f"match [b, v, {prop.weights.hidden_size}] float32 / [b, {prop.weights.two_e}, v, v]")
+        if h0.shape[0] > 0:
+            out = _propagate_dense_from_host(prop, h0, adj, num_timesteps, fixed_ts, precision)
+            return out.numpy() if kind == "numpy" else out
+    h0, kind = _to_device(initial_node_representations, dev, np.float32, "initial_node_representations")
     adj, _ = _to_device(adjacency_matrix, dev, None, "adjacency_matrix")
     if adj.dtype == torch.float64:
         adj = adj.float()

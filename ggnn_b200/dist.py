@@ -34,13 +34,15 @@ def allreduce_grads(flat: torch.Tensor, average: bool = False, group=None) -> to
 
 def train_step(prop, h0: torch.Tensor, edges: torch.Tensor, d_hT_fn, num_timesteps: int,
                grads: torch.Tensor = None, average: bool = False, optimizer: dict = None,
-               precision: str = "fp32"):
+               precision: str = "fp32", dropout=None):
     """One data-parallel step of the path on this rank's shard: forward with the tape, the caller's
     upstream gradient d_hT_fn(h_T) -> dL/dh_T, backward, all-reduce of the weight gradients and -- when
     `optimizer` is a dict of Propagator.optimizer_step keywords ({} = the reference's defaults, lr .003 /
     clip 1.0, chem_tensorflow.py:483-506) -- the clip + Adam update, identical on every rank because the
     all-reduced gradient is.  `precision` "tf32" runs forward and
     backward on the tensor cores (gradients within 2e-3 of FP64).  Returns (h_T, d_h0, flat grads)."""
+    if dropout is not None:          # (w_mask [T,2E,h,h] | None, state_mask [T,N,h] | None, keep): A8, this step only
+        prop.set_dropout(dropout[0], dropout[1], dropout[2], num_timesteps)
     hT = prop.propagate_edges(h0, edges, num_timesteps=num_timesteps, precision=precision, save_tape=True)
     d_hT = d_hT_fn(hT)
     if grads is not None:

@@ -231,3 +231,29 @@ def test_dense_route_from_bitmask_equals_csr_route(b, c, v, density):
     # 128 equal-magnitude messages per node (density 1.0) sum to a few e-5 of FP32 rounding; realistic
     # in-degrees stay inside the 1e-5 bound
     assert O.normwise_err(dense.cpu().numpy(), ref) <= (1e-5 if density < 0.5 else 5e-5)
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_host_pipeline_chunks_equal_device_path(pinned, monkeypatch):
+    """Host-resident inputs go through the chunked three-stream pipeline (H2D of chunk k+1 overlapping the
+    propagation of chunk k); with 7 graphs per chunk over 30 graphs (ragged last chunk) the result must equal
+    the single device-resident call bit for bit (graphs are independent), for torch-CPU (pinned or pageable),
+    NumPy and uint8 adjacency inputs."""
+    from ggnn_b200 import api
+    b, v, E, h, T = 30, 16, 3, 32, 3
+    w = _weights(2 * E, h, 4)
+    _, adj = _trees(b, v, E, seed=11)
+    h0 = _h0(b, v, h)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    ref = prop.propagate_dense(torch.from_numpy(h0).cuda(), torch.from_numpy(adj).cuda(), num_timesteps=T).cpu()
+    monkeypatch.setattr(api, "_HOST_CHUNK_BYTES", 7 * adj[0].nbytes)
+    ht, at = torch.from_numpy(h0), torch.from_numpy(adj)
+    if pinned:
+        ht, at = ht.pin_memory(), at.pin_memory()
+    out = ggnn_b200.compute_final_node_representations(ht, at, weights=prop, num_timesteps=T)
+    assert isinstance(out, torch.Tensor) and out.device.type == "cpu" and torch.equal(out, ref)
+    out_np = ggnn_b200.compute_final_node_representations(h0, adj, weights=prop, num_timesteps=T)
+    assert isinstance(out_np, np.ndarray) and np.array_equal(out_np, ref.numpy())
+    out_u8 = ggnn_b200.compute_final_node_representations(h0, (adj != 0).astype(np.uint8), weights=prop, num_timesteps=T)
+    assert np.array_equal(out_u8, ref.numpy())
+    assert O.normwise_err(out_np, O.propagate_dense(h0, adj, w, T)) <= TOL["fp32"]
