@@ -231,27 +231,41 @@ tn_kernel(const tn_params p) {
   flush(cur_type);
 }
 
-// column sums of D rows (optionally gathered), grouped by tile type: out[type][n] += sum_r D[map(r)][n]
+// column sums of D rows (optionally gathered), grouped by tile type: out[type][n] += sum_r D[map(r)][n].
+// One CTA = 128 rows (one message tile in grouped mode, so one type) x 128 columns; thread (x, y) sums the
+// float4 column group x over rows y, y + 8, ..., then the 8 partial sums are combined in shared memory.
 __global__ void __launch_bounds__(256)
 colsum_kernel(const float* __restrict__ D, int ldd, const int32_t* __restrict__ d_rowmap, int N,
-              int64_t R, int rows_per_cta, float* __restrict__ out, const int32_t* __restrict__ tile_type,
+              int64_t R, float* __restrict__ out, const int32_t* __restrict__ tile_type,
               const int32_t* __restrict__ n_tiles, int out_type_stride) {
-  int64_t r_begin = (int64_t)blockIdx.y * rows_per_cta, r_end = r_begin + rows_per_cta;
+  __shared__ float4 part[8][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t r_begin = (int64_t)blockIdx.y * GGNN_TILE_M;
   if (tile_type) R = (int64_t)(*n_tiles) * GGNN_TILE_M;
+  int64_t r_end = r_begin + GGNN_TILE_M;
   if (r_end > R) r_end = R;
-  const int n = blockIdx.x * 256 + threadIdx.x;
-  if (r_begin >= r_end || n >= N) return;
-  int cur_type = tile_type ? tile_type[r_begin / GGNN_TILE_M] : 0;
-  float s = 0.f;
-  for (int64_t r = r_begin; r < r_end; ++r) {
-    if (tile_type && r > r_begin && (r % GGNN_TILE_M) == 0) {
-      const int t = tile_type[r / GGNN_TILE_M];
-      if (t != cur_type) { if (s != 0.f) atomicAdd(out + (size_t)cur_type * out_type_stride + n, s); s = 0.f; cur_type = t; }
+  if (r_begin >= r_end) return;
+  const int n = blockIdx.x * 128 + tx * 4;                     // N % 4 == 0
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (n < N) {
+#pragma unroll 4
+    for (int64_t r = r_begin + ty; r < r_end; r += 8) {
+      const int64_t src = d_rowmap ? (int64_t)d_rowmap[r] : r;
+      if (src >= 0) {
+        const float4 v = *reinterpret_cast<const float4*>(D + src * ldd + n);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
     }
-    const int64_t src = d_rowmap ? (int64_t)d_rowmap[r] : r;
-    if (src >= 0) s += D[src * ldd + n];
   }
-  if (s != 0.f) atomicAdd(out + (size_t)cur_type * out_type_stride + n, s);
+  part[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && n < N) {
+#pragma unroll
+    for (int y = 1; y < 8; ++y) { const float4 v = part[y][tx]; s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+    const int type = tile_type ? tile_type[r_begin / GGNN_TILE_M] : 0;
+    if (s.x != 0.f || s.y != 0.f || s.z != 0.f || s.w != 0.f)
+      atomicAdd(reinterpret_cast<float4*>(out + (size_t)type * out_type_stride + n), s);
+  }
 }
 
 // ---- pointwise pieces of the GRU backward -------------------------------------------------
@@ -366,9 +380,8 @@ int launch_tn(ggnn_ctx* ctx, const tn_params& p, int64_t rows_bound, cudaStream_
 int launch_colsum(ggnn_ctx* ctx, const float* D, int ldd, const int32_t* map, int N, int64_t R,
                   float* out, const int32_t* tile_type, const int32_t* n_tiles, int stride, cudaStream_t st) {
   if (R <= 0) return GGNN_OK;
-  const int rows_per_cta = 128;
-  dim3 grid((N + 255) / 256, (unsigned)ceil_div64(R, rows_per_cta));
-  colsum_kernel<<<grid, 256, 0, st>>>(D, ldd, map, N, R, rows_per_cta, out, tile_type, n_tiles, stride);
+  dim3 grid((N + 127) / 128, (unsigned)ceil_div64(R, GGNN_TILE_M));
+  colsum_kernel<<<grid, 256, 0, st>>>(D, ldd, map, N, R, out, tile_type, n_tiles, stride);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
