@@ -424,13 +424,14 @@ def run_c5(args):
     grads = torch.zeros(prop.grad_floats, device=dev)
     prec = "fp32" if args.precision == "fp32" else "tf32"      # the kind::f16 kernels have no training path
 
-    drop = None
-    if args.c5_keep < 1.0:           # keep-prob 0.9 with supplied masks in the timed run
-        gm = torch.Generator(device=dev).manual_seed(77 + rank)
-        drop = ((torch.rand(Tc, TWO_E, Hc, Hc, device=dev, generator=gm) < args.c5_keep).float(),
-                (torch.rand(Tc, N, Hc, device=dev, generator=gm) < args.c5_keep).float(), args.c5_keep)
+    step_no = [0]
 
     def step(mode=None):
+        # keep-prob 0.9 in the timed run; fresh Philox masks every step, drawn on the device
+        drop = None
+        if args.c5_keep < 1.0:
+            step_no[0] += 1
+            drop = {"keep": args.c5_keep, "seed": 1000003 * (rank + 1) + step_no[0]}
         return gdist.train_step(prop, h0, edges, lambda hT: d, Tc, grads=grads, optimizer={}, precision=mode or prec,
                                 dropout=drop)
 
@@ -484,7 +485,7 @@ def run_c5(args):
                 "data": "synthetic", "other_modes": other,
                 "config": {"workload": "C5 synthetic WSJ-shaped trees, h=400 2E=92 T=4, fwd+bwd of the path + "
                                        "one all-reduce of the 62.9 MB flat weight gradient + per-variable clip_by_norm(1.0) + "
-                                       "Adam(0.003) on the ctx-owned weights; edge-weight and state dropout with supplied masks, "
+                                       "Adam(0.003) on the ctx-owned weights; edge-weight and state dropout, fresh device-generated (Philox) masks per step, "
                                        f"keep-prob {args.c5_keep}",
                            "graphs_per_gpu": per_gpu, "nodes_per_gpu": N, "edges_per_gpu": nnz,
                            "parallelism": f"data parallel x{world}, NCCL all-reduce (sum) of {prop.grad_floats} floats"},

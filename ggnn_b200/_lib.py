@@ -36,6 +36,8 @@ SIGNATURES = {
     "ggnn_grad_floats": (_i64, [_vp]),
     "ggnn_optimizer_step": (_i, [_vp, _i, _vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _vp]),
     "ggnn_get_weights": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ggnn_set_dropout_seed": (_i, [_vp, C.c_float, C.c_uint64, _i, _i]),
+    "ggnn_dropout_mask": (_i, [_vp, _vp, C.c_int64, C.c_uint64, C.c_uint64, C.c_float, _vp]),
     "ggnn_set_dropout": (_i, [_vp, _vp, _vp, C.c_float, _i]),
     "ggnn_propagate_backward": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "ggnn_embed_nodes": (_i, [_vp, _vp, _i64, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _vp, _vp]),

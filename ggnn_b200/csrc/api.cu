@@ -31,6 +31,9 @@ struct ctx_ext {
   const float* drop_s = nullptr;
   float drop_keep = 1.f;
   int drop_T = -1;
+  // ... or generated on the device from a seed (ggnn_set_dropout_seed); stream ids: 2t = weights, 2t+1 = state of step t
+  bool drop_gen = false, drop_gen_w = false, drop_gen_s = false;
+  unsigned long long drop_seed = 0;
 };
 
 ctx_ext* ext_of(ggnn_ctx* c) { return reinterpret_cast<ctx_ext*>(c->ws); }
@@ -302,7 +305,26 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
       ex->drop_T = -1;
     }
     const size_t wn = (size_t)ctx->two_e * ctx->h * ctx->h;
-    if (tape.w_mask) {
+    if (ex->drop_gen) {                    // device-generated masks: materialise [T, 2E, h, h] and [T, N, h] once
+      ex->drop_gen = false;
+      const size_t wm = ex->drop_gen_w ? (size_t)T * wn : 0, sm = ex->drop_gen_s ? (size_t)T * nh : 0;
+      GGNN_TRY(arena_reserve(ctx, 5, (wn + wm + sm) * 4 + 1024, st));
+      float* base = reinterpret_cast<float*>(ex->ar[5].p);
+      tape.w_eff = base;
+      tape.keep = ex->drop_keep;
+      if (wm) {
+        float* m = base + wn;
+        for (int t = 0; t < T; ++t)
+          GGNN_TRY(ggnn_dropout_mask_fill(ctx, m + (size_t)t * wn, (int64_t)wn, ex->drop_seed, 2ull * t, tape.keep, st));
+        tape.w_mask = m;
+      }
+      if (sm) {
+        float* m = base + wn + wm;
+        for (int t = 0; t < T; ++t)
+          GGNN_TRY(ggnn_dropout_mask_fill(ctx, m + (size_t)t * nh, (int64_t)nh, ex->drop_seed, 2ull * t + 1, tape.keep, st));
+        tape.state_mask = m;
+      }
+    } else if (tape.w_mask) {
       GGNN_TRY(arena_reserve(ctx, 5, wn * 4 + 256, st));
       tape.w_eff = reinterpret_cast<float*>(ex->ar[5].p);
     }
@@ -593,10 +615,31 @@ extern "C" int ggnn_get_weights(ggnn_ctx* ctx, int slot, float* W, float* B, flo
   return GGNN_OK;
 }
 
+extern "C" int ggnn_set_dropout_seed(ggnn_ctx* ctx, float keep, unsigned long long seed, int drop_weights,
+                                     int drop_state) {
+  if (!ctx) return GGNN_E_ARG;
+  if (!(keep > 0.f && keep <= 1.f)) GGNN_FAIL(ctx, GGNN_E_ARG, "set_dropout_seed: keep must be in (0, 1]");
+  ctx_ext* ex = ext_of(ctx);
+  ex->drop_T = -1; ex->drop_w = ex->drop_s = nullptr;
+  ex->drop_gen = (drop_weights || drop_state) && keep < 1.f;
+  ex->drop_gen_w = drop_weights != 0; ex->drop_gen_s = drop_state != 0;
+  ex->drop_keep = keep; ex->drop_seed = seed;
+  return GGNN_OK;
+}
+
+extern "C" int ggnn_dropout_mask(ggnn_ctx* ctx, float* out, int64_t n, unsigned long long seed,
+                                 unsigned long long stream_id, float keep, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (!out && n > 0) GGNN_FAIL(ctx, GGNN_E_ARG, "dropout_mask: null output");
+  device_guard g(ctx->device);
+  return ggnn_dropout_mask_fill(ctx, out, n, seed, stream_id, keep, (cudaStream_t)stream);
+}
+
 extern "C" int ggnn_set_dropout(ggnn_ctx* ctx, const float* w_mask, const float* state_mask, float keep, int T) {
   if (!ctx) return GGNN_E_ARG;
   if (!(keep > 0.f && keep <= 1.f) || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "set_dropout: keep must be in (0, 1], T >= 0");
   ctx_ext* ex = ext_of(ctx);
+  ex->drop_gen = false;
   ex->drop_w = w_mask; ex->drop_s = state_mask; ex->drop_keep = keep;
   ex->drop_T = (w_mask || state_mask) ? T : -1;
   return GGNN_OK;

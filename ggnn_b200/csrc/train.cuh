@@ -34,6 +34,10 @@ void ggnn_bwd_take_scratch(ws_alloc& a, const ggnn_plan& plan, int h, int two_e,
 // elementwise helpers of the dropout path
 int ggnn_mask_scale(ggnn_ctx* ctx, const float* x, const float* mask, float scale, float* out, int64_t n, bool accumulate, cudaStream_t st);
 
+// Philox4x32-10 0/1 mask: out[i] = 1 where uniform(seed, stream, i) < keep
+int ggnn_dropout_mask_fill(ggnn_ctx* ctx, float* out, int64_t n, unsigned long long seed, unsigned long long stream,
+                           float keep, cudaStream_t st);
+
 // flat gradient layout: [dW 2E*h*h | dB 2E*h | dWg 2h*2h | dbg 2h | dWc 2h*h | dbc h]
 size_t ggnn_grad_count(int two_e, int h);
 

@@ -322,6 +322,34 @@ __global__ void mask_scale_kernel(const float* x, const float* __restrict__ mask
   }
 }
 
+// Philox4x32-10 (Salmon et al., SC'11): counter = (i / 4, stream), key = seed; element i of a mask is
+// word i % 4 of the block; mask = 1 where u32 * 2^-32 < keep.  Counter-based, so the backward regenerates
+// nothing -- the masks are materialised once per forward and read by both passes.
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+__global__ void __launch_bounds__(256)
+dropout_mask_kernel(float* __restrict__ out, int64_t n, unsigned long long seed, unsigned long long stream, float keep) {
+  const int64_t nblk = (n + 3) / 4;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += (int64_t)gridDim.x * blockDim.x) {
+    uint32_t c[4] = {(uint32_t)b, (uint32_t)((unsigned long long)b >> 32), (uint32_t)stream, (uint32_t)(stream >> 32)};
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      philox_round(c, k0, k1);
+      k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int64_t i = b * 4 + q;
+      if (i < n) out[i] = ((float)c[q] * 2.3283064365386963e-10f < keep) ? 1.f : 0.f;
+    }
+  }
+}
+
 // msg_tgt[message row] = target node (from the target CSR); padding rows keep -1
 __global__ void msg_tgt_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg,
                                int64_t N, int32_t* __restrict__ msg_tgt) {
@@ -341,6 +369,14 @@ int ggnn_mask_scale(ggnn_ctx* ctx, const float* x, const float* mask, float scal
                     bool accumulate, cudaStream_t st) {
   if (n <= 0) return GGNN_OK;
   mask_scale_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(x, mask, scale, out, n, accumulate ? 1 : 0);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+int ggnn_dropout_mask_fill(ggnn_ctx* ctx, float* out, int64_t n, unsigned long long seed, unsigned long long stream,
+                           float keep, cudaStream_t st) {
+  if (n <= 0) return GGNN_OK;
+  dropout_mask_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(out, n, seed, stream, keep);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

@@ -41,7 +41,10 @@ def train_step(prop, h0: torch.Tensor, edges: torch.Tensor, d_hT_fn, num_timeste
     clip 1.0, chem_tensorflow.py:483-506) -- the clip + Adam update, identical on every rank because the
     all-reduced gradient is.  `precision` "tf32" runs forward and
     backward on the tensor cores (gradients within 2e-3 of FP64).  Returns (h_T, d_h0, flat grads)."""
-    if dropout is not None:          # (w_mask [T,2E,h,h] | None, state_mask [T,N,h] | None, keep): A8, this step only
+    if isinstance(dropout, dict):    # {"keep": k, "seed": s}: masks drawn on the device (Philox), A8, this step only
+        prop.set_dropout_seed(dropout["keep"], dropout["seed"], dropout.get("drop_weights", True),
+                              dropout.get("drop_state", True))
+    elif dropout is not None:        # (w_mask [T,2E,h,h] | None, state_mask [T,N,h] | None, keep): supplied masks
         prop.set_dropout(dropout[0], dropout[1], dropout[2], num_timesteps)
     hT = prop.propagate_edges(h0, edges, num_timesteps=num_timesteps, precision=precision, save_tape=True)
     d_hT = d_hT_fn(hT)

@@ -259,6 +259,25 @@ class Propagator:
         rc = self._l.ggnn_set_dropout(self._ctx, _ptr(w_mask), _ptr(state_mask), float(keep), int(num_timesteps))
         self._check(rc, "ggnn_set_dropout")
 
+    def set_dropout_seed(self, keep: float, seed: int, drop_weights: bool = True, drop_state: bool = True):
+        """Device-generated dropout (Philox4x32-10) for the next ``save_tape=True`` propagate call and its
+        backward: fresh edge-weight mask per unrolled step and a mask on every new state, keep-prob ``keep``
+        (reference: chem_tensorflow_dense.py:397-403, 239-240; 0.9 in training, :800)."""
+        self._drop_keep = None
+        rc = self._l.ggnn_set_dropout_seed(self._ctx, float(keep), int(seed) & (2 ** 64 - 1), int(drop_weights),
+                                           int(drop_state))
+        self._check(rc, "ggnn_set_dropout_seed")
+
+    def dropout_mask(self, n: int, seed: int, stream_id: int, keep: float) -> torch.Tensor:
+        """The 0/1 mask (float32 [n]) the kernels use for (seed, stream_id): stream 2t = edge weights of step
+        t (flattened [2E, h, h]), 2t+1 = state of step t (flattened [N, h])."""
+        out = torch.empty(int(n), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_dropout_mask(self._ctx, _ptr(out), int(n), int(seed) & (2 ** 64 - 1), int(stream_id),
+                                           float(keep), _stream_ptr(self.device))
+        self._check(rc, "ggnn_dropout_mask")
+        return out
+
     def backward(self, d_hT: torch.Tensor, grads: Optional[torch.Tensor] = None
                  ) -> Tuple[torch.Tensor, torch.Tensor]:
         """Backward of the last ``save_tape=True`` propagate call.  ``d_hT``: gradient w.r.t. the

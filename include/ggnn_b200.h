@@ -158,6 +158,16 @@ int ggnn_get_weights(ggnn_ctx* ctx, int slot, float* W, float* B, float* Wg, flo
  *              h' * state_mask[t] / keep (:239-240, 333)
  * Both pointers must stay valid until the backward has run.  keep in (0, 1]. */
 int ggnn_set_dropout(ggnn_ctx* ctx, const float* w_mask, const float* state_mask, float keep, int T);
+
+/* Same, with the masks drawn on the device: Philox4x32-10, key = seed, counter = (element / 4, stream id),
+ * stream id 2t = edge-weight mask of unrolled step t, 2t+1 = state mask of step t; mask = 1 where
+ * u32 * 2^-32 < keep.  (TF's own generator cannot be reproduced bit for bit; parity of the dropped path is
+ * established with the SAME masks fed to the oracle: ggnn_dropout_mask materialises exactly the mask of
+ * (seed, stream id) the kernels use, n elements, into a device buffer.)  Applies to the next SAVE_TAPE
+ * propagate call and its backward only. */
+int ggnn_set_dropout_seed(ggnn_ctx* ctx, float keep, unsigned long long seed, int drop_weights, int drop_state);
+int ggnn_dropout_mask(ggnn_ctx* ctx, float* out, int64_t n, unsigned long long seed,
+                      unsigned long long stream_id, float keep, void* stream);
 int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* d_h0, float* grads, void* stream);
 
 /* "Next" rows either side of the path, evaluation mode --------------------

@@ -78,3 +78,35 @@ def adam_step(params, grads, m, v, t, lr=0.003, beta1=0.9, beta2=0.999, eps=1e-8
         v[k] = beta2 * v[k] + (1 - beta2) * g * g
         params[k] = params[k] - lr_t * m[k] / (np.sqrt(v[k]) + eps)
     return params
+
+
+def philox4x32_10(counter, key):
+    """Philox4x32-10 (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3", SC'11).
+    counter uint32 [n, 4], key uint32 [2] -> uint32 [n, 4].  Restated from the paper / Random123's
+    published round function; pinned by Random123's known-answer vectors in tests/test_oracle.py."""
+    c = np.asarray(counter, dtype=np.uint64).copy()
+    k0, k1 = int(key[0]), int(key[1])
+    M0, M1, MASK = 0xD2511F53, 0xCD9E8D57, 0xFFFFFFFF
+    for _ in range(10):
+        p0 = c[:, 0] * np.uint64(M0)
+        p1 = c[:, 2] * np.uint64(M1)
+        hi0, lo0 = p0 >> np.uint64(32), p0 & np.uint64(MASK)
+        hi1, lo1 = p1 >> np.uint64(32), p1 & np.uint64(MASK)
+        n0 = hi1 ^ c[:, 1] ^ np.uint64(k0)
+        n2 = hi0 ^ c[:, 3] ^ np.uint64(k1)
+        c = np.stack([n0, lo1, n2, lo0], axis=1)
+        k0 = (k0 + 0x9E3779B9) & MASK
+        k1 = (k1 + 0xBB67AE85) & MASK
+    return c.astype(np.uint32)
+
+
+def philox_mask(n, seed, stream, keep):
+    """0/1 float32 mask of ggnn_dropout_mask: element i = word i % 4 of the block with counter
+    (i // 4 as 64 bit, stream as 64 bit) and key = seed as 64 bit; 1 where float32(u32) * 2^-32 < keep."""
+    nb = (n + 3) // 4
+    b = np.arange(nb, dtype=np.uint64)
+    ctr = np.stack([b & np.uint64(0xFFFFFFFF), b >> np.uint64(32),
+                    np.full(nb, stream & 0xFFFFFFFF, np.uint64), np.full(nb, (stream >> 32) & 0xFFFFFFFF, np.uint64)], axis=1)
+    r = philox4x32_10(ctr, (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)).reshape(-1)[:n]
+    u = r.astype(np.float32) * np.float32(2.3283064365386963e-10)
+    return (u < np.float32(keep)).astype(np.float32)

@@ -269,3 +269,38 @@ def test_training_loop_tf32_tracks_fp32():
             prop.optimizer_step(flat)
         final[prec] = loss
     assert abs(final["tf32"] - final["fp32"]) <= 0.02 * final["fp32"], final
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_device_generated_dropout_matches_oracle_with_same_masks(precision):
+    """A8 with the masks drawn on the device (Philox4x32-10): the device masks equal the NumPy Philox restatement
+    bit for bit (itself pinned by Random123's known answers), and forward + gradients equal the autograd oracle
+    fed with exactly those masks.  A second call without re-arming is dropout-free."""
+    b, v, E, h, T, keep, seed = 4, 16, 5, 64, 3, 0.9, 12345678901234567
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=21)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    wn, nh = 2 * E * h * h, b * v * h
+    wm = np.stack([G.philox_mask(wn, seed, 2 * t, keep) for t in range(T)]).reshape(T, 2 * E, h, h)
+    sm = np.stack([G.philox_mask(nh, seed, 2 * t + 1, keep) for t in range(T)]).reshape(T, b * v, h)
+    for t in range(T):
+        assert np.array_equal(prop.dropout_mask(wn, seed, 2 * t, keep).cpu().numpy(), wm[t].ravel())
+        assert np.array_equal(prop.dropout_mask(nh, seed, 2 * t + 1, keep).cpu().numpy(), sm[t].ravel())
+    assert abs(float(wm.mean()) - keep) < 5e-3 and abs(float(sm.mean()) - keep) < 2e-2
+    prop.set_dropout_seed(keep, seed)
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision=precision,
+                              save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    ref = G.grads(h0, edges.numpy(), w, T, d, w_mask=wm, state_mask=sm, keep=keep)
+    if precision == "fp32":
+        _check(prop, w, hT, dh0, flat, ref)
+    else:
+        _check_tf32(prop, hT, dh0, flat, ref)
+    hT2 = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision=precision,
+                               save_tape=True)
+    assert O.normwise_err(hT2.cpu().numpy(), G.grads(h0, edges.numpy(), w, T, d)[0]) <= 2e-3
+    # only one of the two dropouts
+    prop.set_dropout_seed(keep, seed, drop_weights=False)
+    hT3 = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision=precision,
+                               save_tape=True)
+    ref3 = G.grads(h0, edges.numpy(), w, T, d, state_mask=sm, keep=keep)
+    assert O.normwise_err(hT3.cpu().numpy(), ref3[0]) <= (1e-5 if precision == "fp32" else 2e-3)

@@ -267,3 +267,17 @@ def test_adam_oracle_matches_torch_adam_with_per_tensor_clip():
         G.adam_step(P, g, M, V, t)
         for k in shapes:
             np.testing.assert_allclose(P[k], tp[k].detach().numpy(), rtol=0, atol=1e-12)
+
+
+def test_philox_known_answers():
+    """Random123's published known-answer vectors for philox4x32-10 (kat_vectors: counter, key -> output)."""
+    from oracle import grad_oracle as G
+    z = G.philox4x32_10(np.zeros((1, 4), np.uint32), (0, 0))[0]
+    assert [hex(int(x)) for x in z] == ["0x6627e8d5", "0xe169c58d", "0xbc57ac4c", "0x9b00dbd8"]
+    f = G.philox4x32_10(np.full((1, 4), 0xFFFFFFFF, np.uint32), (0xFFFFFFFF, 0xFFFFFFFF))[0]
+    assert [hex(int(x)) for x in f] == ["0x408f276d", "0x41c83b0e", "0xa20bc7c6", "0x6d5451fd"]
+    p = G.philox4x32_10(np.array([[0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344]], np.uint32), (0xa4093822, 0x299f31d0))[0]
+    assert [hex(int(x)) for x in p] == ["0xd16cfe09", "0x94fdcceb", "0x5001e420", "0x24126ea1"]
+    m = G.philox_mask(100003, seed=7, stream=3, keep=0.9)
+    assert m.shape == (100003,) and abs(float(m.mean()) - 0.9) < 5e-3
+    assert not np.array_equal(m, G.philox_mask(100003, seed=7, stream=4, keep=0.9))
