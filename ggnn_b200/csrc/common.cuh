@@ -29,6 +29,7 @@ struct ggnn_edge_weights {
 struct ggnn_ctx {
   int device = 0;
   int sm_count = 148;
+  unsigned attr_mask = 0;   // kernels whose dynamic-smem attribute has been set on THIS ctx's device (GGNN_ATTR_*)
   int two_e = 0;
   int h = 0;
   int hp = 0;              // h padded to the tensor-core tile granularity
@@ -68,6 +69,17 @@ struct ggnn_ctx {
   double prof_ms[GGNN_N_STAGES] = {0};
   int64_t prof_launches[GGNN_N_STAGES] = {0};
 };
+
+// cudaFuncSetAttribute is per device: remember per ctx (a process may own one ctx per GPU), not in a static
+enum { GGNN_ATTR_TF32_GEMM0 = 0 /* + mode 0..3 */, GGNN_ATTR_GRU_FUSED = 4, GGNN_ATTR_MSG_TC = 5, GGNN_ATTR_F16 = 6,
+       GGNN_ATTR_TN = 7 };
+#define GGNN_ENSURE_SMEM(ctx, bit, kernel, bytes)                                                          \
+  do {                                                                                                     \
+    if (!((ctx)->attr_mask & (1u << (bit)))) {                                                             \
+      GGNN_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (bytes))); \
+      (ctx)->attr_mask |= 1u << (bit);                                                                     \
+    }                                                                                                      \
+  } while (0)
 
 // RAII stage timer: records an event pair around the launches of one stage when profiling is on
 struct prof_scope {

@@ -726,11 +726,10 @@ int ggnn_absmax(ggnn_ctx* ctx, const float* x, int64_t n, unsigned* out_bits, cu
 int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16,
                   float* h_out, bool last_step, cudaStream_t st) {
   if (plan.N == 0) return GGNN_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!(ctx->attr_mask & (1u << GGNN_ATTR_F16))) {
     GGNN_CUDA(ctx, cudaFuncSetAttribute(msg16::msg_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, msg16::SMEM_BYTES));
     GGNN_CUDA(ctx, cudaFuncSetAttribute(gru16::gru_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gru16::SMEM_BYTES));
-    attr_set = true;
+    ctx->attr_mask |= 1u << GGNN_ATTR_F16;
   }
   const ggnn_edge_weights& ew = ctx->edge[slot];
   if (plan.max_tiles > 0 && plan.nnz > 0) {

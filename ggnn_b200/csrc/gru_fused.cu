@@ -456,12 +456,7 @@ bool ggnn_gru_fused_supported(const ggnn_ctx* ctx) { return ctx->hp == HP && ctx
 int ggnn_gru_fused_step(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* h_state,
                         bool last_step, cudaStream_t st) {
   if (plan.N == 0) return GGNN_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GGNN_CUDA(ctx, cudaFuncSetAttribute(gru_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        SMEM_BYTES));
-    attr_set = true;
-  }
+  GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_GRU_FUSED, gru_fused_kernel, SMEM_BYTES);
   CUtensorMap tmH;
   GGNN_TRY(ggnn_make_tmap_2d(ctx, &tmH, h_state, plan.N, ctx->h, BM));
   gparams p{};

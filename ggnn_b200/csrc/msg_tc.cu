@@ -248,11 +248,7 @@ bool ggnn_msg_tc_supported(const ggnn_ctx* ctx) { return ctx->hp == HP && ctx->h
 int ggnn_msg_tc_step(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const float* h_state,
                      void* msg_half, cudaStream_t st) {
   if (plan.max_tiles == 0 || plan.nnz == 0) return GGNN_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GGNN_CUDA(ctx, cudaFuncSetAttribute(msg_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set = true;
-  }
+  GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_MSG_TC, msg_tc_kernel, SMEM_BYTES);
   const ggnn_edge_weights& ew = ctx->edge[slot];
   CUtensorMap tmOut;
   GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmOut, msg_half, plan.max_tiles * (int64_t)BM, HP, 64, BM));

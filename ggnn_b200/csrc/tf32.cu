@@ -361,12 +361,7 @@ int launch(ggnn_ctx* ctx, const tparams& p_in, const CUtensorMap& tm, unsigned m
   tparams p = p_in;
   if (p.lda1 == 0) p.lda1 = p.h;
   if (p.lda2 == 0) p.lda2 = p.h;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GGNN_CUDA(ctx, cudaFuncSetAttribute(gemm_tf32_kernel<MODE>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set = true;
-  }
+  GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_TF32_GEMM0 + MODE, gemm_tf32_kernel<MODE>, SMEM_BYTES);
   dim3 grid((p.Np + BN - 1) / BN, mtiles);
   gemm_tf32_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(p, tm);
   GGNN_LAUNCHED(ctx);

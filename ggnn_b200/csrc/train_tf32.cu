@@ -207,11 +207,7 @@ int ggnn_tf32_tn(ggnn_ctx* ctx, const float* X, int ldx, const int32_t* x_rowmap
                  const int32_t* d_rowmap, int N, int64_t R, int rows_per_cta, float* C, int ldc,
                  const int32_t* tile_type, const int32_t* n_tiles, int64_t c_type_stride, cudaStream_t st) {
   if (R <= 0 || K1 <= 0 || N <= 0) return GGNN_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
-    GGNN_CUDA(ctx, cudaFuncSetAttribute(tn::tn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tn::SMEM_BYTES));
-    attr_set = true;
-  }
+  GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_TN, tn::tn_tc_kernel, tn::SMEM_BYTES);
   tn::params p{};
   p.X = X; p.ldx = ldx; p.x_rowmap = x_rowmap; p.K1 = K1;
   p.D = D; p.ldd = ldd; p.d_rowmap = d_rowmap; p.N = N;

@@ -257,3 +257,26 @@ def test_host_pipeline_chunks_equal_device_path(pinned, monkeypatch):
     out_u8 = ggnn_b200.compute_final_node_representations(h0, (adj != 0).astype(np.uint8), weights=prop, num_timesteps=T)
     assert np.array_equal(out_u8, ref.numpy())
     assert O.normwise_err(out_np, O.propagate_dense(h0, adj, w, T)) <= TOL["fp32"]
+
+
+def test_one_process_two_devices():
+    """One ctx per device inside ONE process (SURVEY 8b threading note): kernel attributes are per device, so the
+    second device must work like the first.  Skipped on single-GPU boxes."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    b, v, E, h, T = 6, 32, 4, 128, 3
+    w = _weights(2 * E, h, 2)
+    _, adj = _trees(b, v, E, seed=3)
+    h0 = _h0(b, v, h)
+    ref = O.propagate_dense(h0, adj, w, T)
+    outs = {}
+    for dev in ("cuda:0", "cuda:1"):
+        prop = Propagator(ggnn_b200.from_dict(w), dev)
+        for prec in ("fp32", "tf32", "f16"):
+            out = prop.propagate_dense(torch.from_numpy(h0).to(dev), torch.from_numpy(adj).to(dev),
+                                       num_timesteps=T, precision=prec)
+            assert out.device == torch.device(dev)
+            assert O.normwise_err(out.cpu().numpy(), ref) <= (1e-5 if prec == "fp32" else 2e-3), (dev, prec)
+            outs[(dev, prec)] = out.cpu()
+    for prec in ("fp32", "tf32", "f16"):
+        assert torch.equal(outs[("cuda:0", prec)], outs[("cuda:1", prec)])
