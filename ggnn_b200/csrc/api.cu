@@ -183,6 +183,7 @@ extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const
     GGNN_FAIL(ctx, GGNN_E_SHAPE, "set_weights: slot %d must match slot 0 (two_e=%d, h=%d)", slot, ctx->two_e, ctx->h);
   device_guard g(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
+  ext_of(ctx)->tape.valid = false;     // a tape belongs to the weights it was recorded with
   if (slot == GGNN_SLOT_MAIN) {
     if (ctx->two_e != two_e || ctx->h != h) ctx->edge[GGNN_SLOT_FIXED].set = false;
     ctx->two_e = two_e;
@@ -219,6 +220,7 @@ extern "C" int ggnn_compact_adjacency(ggnn_ctx* ctx, const void* adj, int adj_dt
   if (rows >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "compact: b*two_e*v = %lld rows needs int64 rowptr; split the batch", (long long)rows);
   device_guard g(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
+  ext_of(ctx)->tape.valid = false;     // a taped dense forward keeps its target CSR in the compaction arena
   GGNN_TRY(arena_reserve(ctx, 0, ggnn_compact_tmp_bytes(rows * v, rows), st));
   char* tmp = ext_of(ctx)->ar[0].p;
   GGNN_TRY(ggnn_compact_count(ctx, adj, adj_dtype, rows, v, rowptr, nnz_out_dev, tmp, st));
