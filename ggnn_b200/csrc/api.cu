@@ -38,6 +38,11 @@ struct ctx_ext {
 
 ctx_ext* ext_of(ggnn_ctx* c) { return reinterpret_cast<ctx_ext*>(c->ws); }
 
+// the kernels move 16-byte vectors (float4, cp.async, TMA): every state / gradient pointer of the ABI must be
+// 16-byte aligned (any cudaMalloc or framework allocation is); the adjacency may be element-aligned only (the
+// bitmask pass falls back to scalar loads)
+inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
+
 int arena_reserve(ggnn_ctx* ctx, int which, size_t bytes, cudaStream_t st) {
   arena& a = ext_of(ctx)->ar[which];
   if (a.bytes >= bytes) return GGNN_OK;
@@ -411,6 +416,7 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
   if (!ctx) return GGNN_E_ARG;
   if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: bad sizes b=%d v=%d T=%d", b, v, T);
   if (b > 0 && (!h0 || !adj || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: null pointer");
+  if (misaligned16(h0) || misaligned16(h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: state pointers must be 16-byte aligned");
   if (adj_dtype != GGNN_ADJ_F32 && adj_dtype != GGNN_ADJ_U8) GGNN_FAIL(ctx, GGNN_E_ARG, "bad adj_dtype %d", adj_dtype);
   GGNN_TRY(check_ready(ctx, slot, precision));
   if (b == 0) return GGNN_OK;
@@ -424,6 +430,7 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
   const int64_t rows_per_graph = (int64_t)two_e * v;
   int64_t chunk = ((int64_t)1 << 26) / rows_per_graph;
   if (chunk < 1) chunk = 1;
+  if (chunk >= 16) chunk &= ~(int64_t)15;     // chunk starts stay 16-byte aligned for any v, 2E and adjacency dtype
   if (chunk > b) chunk = b;
   if ((flags & GGNN_FLAG_SAVE_TAPE) && chunk < b)
     GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE: batch of %d graphs needs more than one chunk (%lld graphs)", b, (long long)chunk);
@@ -491,6 +498,7 @@ extern "C" int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0, cons
   if (!ctx) return GGNN_E_ARG;
   if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: bad sizes");
   if (b > 0 && (!h0 || !rowptr || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: null pointer");
+  if (misaligned16(h0) || misaligned16(h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_csr: state pointers must be 16-byte aligned");
   GGNN_TRY(check_ready(ctx, slot, precision));
   if (b == 0) return GGNN_OK;
   const int64_t rows = (int64_t)b * ctx->two_e * v;
@@ -520,6 +528,7 @@ extern "C" int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0, co
   if (!ctx) return GGNN_E_ARG;
   if (nnz < 0 || N < 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: bad sizes");
   if ((N > 0 && (!h0 || !h_out)) || (nnz > 0 && !edges)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: null pointer");
+  if (misaligned16(h0) || misaligned16(h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_edges: state pointers must be 16-byte aligned");
   GGNN_TRY(check_ready(ctx, slot, precision));
   if (N == 0) return GGNN_OK;
   if (N >= 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "propagate_edges: N too large for int32 node ids");
@@ -558,6 +567,7 @@ extern "C" int ggnn_optimizer_step(ggnn_ctx* ctx, int slot, const float* grads, 
                                    float beta2, float eps, float clip_norm, void* stream) {
   if (!ctx) return GGNN_E_ARG;
   if (slot < 0 || slot >= GGNN_MAX_SLOTS || !grads) GGNN_FAIL(ctx, GGNN_E_ARG, "optimizer_step: bad slot or null grads");
+  if (misaligned16(grads)) GGNN_FAIL(ctx, GGNN_E_ARG, "optimizer_step: grads must be 16-byte aligned");
   if (!ctx->gru_set || !ctx->edge[slot].set) GGNN_FAIL(ctx, GGNN_E_STATE, "optimizer_step: weights for slot %d not set", slot);
   device_guard g(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
@@ -653,6 +663,8 @@ extern "C" int ggnn_propagate_backward(ggnn_ctx* ctx, const float* d_hT, float* 
   ggnn_tape& tape = ext_of(ctx)->tape;
   if (!tape.valid) GGNN_FAIL(ctx, GGNN_E_STATE, "propagate_backward: no tape (run a propagate call with GGNN_FLAG_SAVE_TAPE first)");
   if (tape.plan.N > 0 && (!d_hT || !d_h0 || !grads)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_backward: null pointer");
+  if (misaligned16(d_hT) || misaligned16(d_h0) || misaligned16(grads))
+    GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_backward: pointers must be 16-byte aligned");
   device_guard g(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
   ggnn_bwd_scratch sc;

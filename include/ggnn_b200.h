@@ -15,6 +15,9 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer on the ctx's device unless it says "host";
+ *   - state and gradient buffers must be 16-byte aligned (the kernels move 16-byte vectors; any cudaMalloc /
+ *     framework allocation is); a misaligned pointer is GGNN_E_ARG.  The adjacency may be element-aligned only
+ *     (slower scalar path);
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
  *   - all work is enqueued on `stream`; the calls that must learn a device-side
  *     count to size their plan (propagate_dense / propagate_csr / propagate_edges)

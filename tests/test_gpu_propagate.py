@@ -280,3 +280,26 @@ def test_one_process_two_devices():
             outs[(dev, prec)] = out.cpu()
     for prec in ("fp32", "tf32", "f16"):
         assert torch.equal(outs[("cuda:0", prec)], outs[("cuda:1", prec)])
+
+
+def test_misaligned_pointers_are_rejected():
+    """The kernels move 16-byte vectors: a state / adjacency view that starts 4 bytes into an allocation must be
+    refused with ValueError (GGNN_E_ARG), not read misaligned.  (The adjacency has a scalar fallback.)"""
+    w = _weights(6, 16, 0)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    buf = torch.zeros(2 * 4 * 16 + 1, device="cuda")
+    h_bad = buf[1:].view(2, 4, 16)
+    adj = torch.zeros(2, 6, 4, 4, device="cuda")
+    assert h_bad.data_ptr() % 16 != 0
+    with pytest.raises(ValueError, match="aligned"):
+        prop.propagate_dense(h_bad, adj, num_timesteps=1)
+    # the adjacency may be element-aligned only (scalar bitmask path): same result as the aligned call
+    _, a_np = _trees(2, 4, 3, seed=1)
+    abuf = torch.zeros(2 * 6 * 4 * 4 + 1, device="cuda")
+    abuf[1:] = torch.from_numpy(a_np).cuda().reshape(-1)
+    h_ok = torch.rand(2, 4, 16, device="cuda") - 0.5
+    assert torch.equal(prop.propagate_dense(h_ok, abuf[1:].view(2, 6, 4, 4), num_timesteps=2),
+                       prop.propagate_dense(h_ok, torch.from_numpy(a_np).cuda(), num_timesteps=2))
+    e = torch.zeros(0, 3, dtype=torch.int32, device="cuda")
+    with pytest.raises(ValueError, match="aligned"):
+        prop.propagate_edges(buf[1:].view(8, 16), e, num_timesteps=1)
