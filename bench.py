@@ -42,8 +42,8 @@ FLOP_GATES_PER_GRAPH_STEP = V * 2 * (2 * H) * (2 * H)         # 16.8 MFLOP
 FLOP_CAND_PER_GRAPH_STEP = V * 2 * (2 * H) * H                #  8.4 MFLOP
 BYTES_COMPACT_PER_GRAPH = TWO_E * V * V * 4 + NNZ_PER_GRAPH * 4 + (TWO_E * V) * 4   # 6.08 MB
 # DRAM traffic of the compaction bitmask pass per graph from the ncu --set full capture
-# (profiles/r1_f16_ncu.md: 12.356 GB read + 0.342 GB written over 2 048 graphs)
-TRAFFIC_COMPACT_PER_GRAPH = (12.356429e9 + 342.248448e6) / 2048
+# (profiles/r1_compact_ncu.md, bitmask_f32_v8_kernel: 12.348 GB read + 0.342 GB written over 2 048 graphs)
+TRAFFIC_COMPACT_PER_GRAPH = (12.348041e9 + 341.879552e6) / 2048
 BYTES_AGG_PER_GRAPH_STEP = NNZ_PER_GRAPH * H * 4 + NNZ_PER_GRAPH * 4 + (V + 1) * 4 + V * H * 4
 
 
@@ -357,7 +357,10 @@ def run_gpu(args):
                     "unit": d["unit"], "frac": d["frac"],
                     "traffic": (TRAFFIC_COMPACT_PER_GRAPH * steps_g / max(st_ln[dom], 1)) if dom == "compact_mask" else None,
                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per graph of one ncu --set full "
-                                      "capture (profiles/r1_f16_ncu.md) x graphs per launch" if dom == "compact_mask" else None,
+                                      "capture (profiles/r1_compact_ncu.md) x graphs per launch" if dom == "compact_mask" else None,
+                    "note": ("read-dominated stream (1/32 written): it can exceed the measured COPY bandwidth used as "
+                             "peak, which moves read + write; ncu reports 83.8 % of the DRAM peak for this kernel")
+                            if dom == "compact_mask" else None,
                     "algorithmic_bytes_per_launch": (BYTES_COMPACT_PER_GRAPH * steps_g / max(st_ln[dom], 1)) if dom == "compact_mask" else None,
                     "avg_launch_ms": st_ms[dom] / max(st_ln[dom], 1),
                     "peak_source": peaks["source"] + ("" if d["bound"] == "hbm" else
