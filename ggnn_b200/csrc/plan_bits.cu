@@ -84,8 +84,18 @@ graph_place_kernel(const uint32_t* __restrict__ bits, const uint16_t* __restrict
   extern __shared__ uint16_t rank[];
   const int64_t g = blockIdx.x;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5, vt = blockDim.x;
-  for (int e = 0; e < two_e; ++e)
-    rank[e * vt + t] = t < v ? rowcnt[(g * two_e + e) * v + t] : (uint16_t)0;
+  // load this target's row counts (independent loads, several in flight) and remember which channels are
+  // non-empty: the emit loop below then visits ~4 rows per node instead of all 2E
+  unsigned long long nz[4] = {0ull, 0ull, 0ull, 0ull};          // two_e <= 256
+#pragma unroll 8
+  for (int e = 0; e < two_e; ++e) {
+    const uint16_t c = t < v ? rowcnt[(g * two_e + e) * v + t] : (uint16_t)0;
+    rank[e * vt + t] = c;
+    const unsigned long long bit = c ? 1ull << (e & 63) : 0ull;
+    const int q = e >> 6;                                       // selects keep nz[] in registers
+    nz[0] |= q == 0 ? bit : 0ull; nz[1] |= q == 1 ? bit : 0ull;
+    nz[2] |= q == 2 ? bit : 0ull; nz[3] |= q == 3 ? bit : 0ull;
+  }
   __syncthreads();
   // exclusive scan of every channel's row counts over the target index (warp per channel)
   for (int e = wid; e < two_e; e += nw) {
@@ -106,23 +116,27 @@ graph_place_kernel(const uint32_t* __restrict__ bits, const uint16_t* __restrict
   if (t >= v) return;
   int cursor = tptr[g * v + t];
   const int end = tptr[g * v + t + 1];
-  for (int e = 0; e < two_e && cursor < end; ++e) {
-    const int64_t r = (g * two_e + e) * v + t;
-    const int c = rowcnt[r];                              // L1/L2 hit: read a moment ago
-    if (c == 0) continue;
-    int mrow = tile_base[e] * GGNN_TILE_M + (segposT[(int64_t)e * b + g] - segposT[(int64_t)e * b]) +
-               rank[e * vt + t];
-    const int64_t lo = r * v, hi = lo + v;
-    for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
-      uint32_t m = __ldg(bits + w);
-      const int64_t wb = w << 5;
-      if (lo > wb) m &= 0xffffffffu << (int)(lo - wb);
-      if (hi < wb + 32) m &= 0xffffffffu >> (int)(wb + 32 - hi);
-      while (m) {
-        const int bpos = __ffs(m) - 1;
-        m &= m - 1;
-        msg_src[mrow] = (int32_t)(g * v + (wb + bpos - lo));
-        tmsg[cursor++] = mrow++;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    unsigned long long m64 = nz[q];
+    while (m64) {
+      const int e = q * 64 + __ffsll((long long)m64) - 1;
+      m64 &= m64 - 1;
+      const int64_t r = (g * two_e + e) * v + t;
+      int mrow = tile_base[e] * GGNN_TILE_M + (segposT[(int64_t)e * b + g] - segposT[(int64_t)e * b]) +
+                 rank[e * vt + t];
+      const int64_t lo = r * v, hi = lo + v;
+      for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
+        uint32_t m = __ldg(bits + w);
+        const int64_t wb = w << 5;
+        if (lo > wb) m &= 0xffffffffu << (int)(lo - wb);
+        if (hi < wb + 32) m &= 0xffffffffu >> (int)(wb + 32 - hi);
+        while (m) {
+          const int bpos = __ffs(m) - 1;
+          m &= m - 1;
+          msg_src[mrow] = (int32_t)(g * v + (wb + bpos - lo));
+          tmsg[cursor++] = mrow++;
+        }
       }
     }
   }
@@ -156,7 +170,7 @@ inline int threads_for(int v) { return (int)align_up((size_t)v, 32); }
 
 bool ggnn_plan_bits_supported(int two_e, int v) {
   const int vt = threads_for(v);
-  return v >= 1 && v <= 255 /* ranks inside a segment fit 16 bits */ && vt <= MAX_THREADS &&
+  return v >= 1 && v <= 255 /* ranks inside a segment fit 16 bits */ && vt <= MAX_THREADS && two_e <= 256 &&
          (size_t)two_e * vt * 2 <= 48 * 1024 &&
          (size_t)(vt / 32) * two_e * 4 <= 48 * 1024;
 }
