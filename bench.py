@@ -249,16 +249,22 @@ def run_gpu(args):
     ne = min(args.e2e_graphs, pool)
     h0_host = h0[:ne].cpu().pin_memory()
     adj_host = adj[:ne].cpu().pin_memory()
-    for _ in range(2):
-        ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,
-                                                     num_timesteps=T, precision=precision)
+    res = None
+    for _ in range(max(3, args.warmup)):   # results are held like in the timed loop, so the pinned-host allocator
+        res = ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,   # caches both blocks
+                                                           num_timesteps=T, precision=precision)
     barrier()
     t0 = time.perf_counter()
+    per_call = []
     for _ in range(args.steps):
+        tc0 = time.perf_counter()
         res = ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,
                                                            num_timesteps=T, precision=precision)
+        per_call.append(time.perf_counter() - tc0)     # the call returns host data: it has synchronised
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / args.steps
+    if os.environ.get("GGNN_BENCH_DEBUG"):
+        print("e2e per call ms:", [round(x * 1e3, 2) for x in per_call], file=sys.stderr)
     if world > 1:
         te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -287,9 +293,10 @@ def run_gpu(args):
     # same graphs handed over as (src, channel, dst) triples: no dense adjacency on the bus
     edges_host = synth.global_edge_list(tri[:ne].cpu(), V, E).pin_memory()
     h0_flat = h0_host.view(ne * V, H)
-    for _ in range(2):
-        ggnn_b200.compute_final_node_representations_sparse(h0_flat, edges_host, weights=prop,
-                                                            num_timesteps=T, precision=precision)
+    res2 = None
+    for _ in range(max(3, args.warmup)):
+        res2 = ggnn_b200.compute_final_node_representations_sparse(h0_flat, edges_host, weights=prop,
+                                                                   num_timesteps=T, precision=precision)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
