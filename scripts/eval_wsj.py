@@ -50,6 +50,7 @@ def main():
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])
     ap.add_argument("--feed", default="edges", choices=["edges", "dense"])
     ap.add_argument("--check", type=int, default=0, help="also run the CPU oracle on this many sentences")
+    ap.add_argument("--batch", type=int, default=20, help="sentences per batch within a bucket (reference: 20)")
     a = ap.parse_args()
     tmp = tempfile.mkdtemp()
     if a.data and a.restore and os.path.exists(a.data) and os.path.exists(a.restore):
@@ -62,10 +63,13 @@ def main():
     ev = PE.ParserEvaluator(ggnn_b200.load_checkpoint(path), PE.heads_from_checkpoint(data["weights"]), "cuda:0")
     ev.evaluate(recs[:64], precision=a.precision, feed=a.feed)          # warm-up
     torch.cuda.synchronize(); t0 = time.perf_counter()
-    res, per = ev.evaluate(recs, precision=a.precision, feed=a.feed)
+    res, per = ev.evaluate(recs, batch_size=a.batch, precision=a.precision, feed=a.feed)
     torch.cuda.synchronize(); dt = time.perf_counter() - t0
-    out = {"data": kind, "precision": a.precision, "feed": a.feed, **res, "seconds": dt,
+    out = {"data": kind, "precision": a.precision, "feed": a.feed, "batch": a.batch, **res, "seconds": dt,
            "instances_per_s": res["sentences"] / dt}
+    if a.batch != 20:      # batching must not change any sentence's scores
+        _, per20 = ev.evaluate(recs, batch_size=20, precision=a.precision, feed=a.feed)
+        out["per_sentence_scores_equal_to_batch_20"] = bool(np.array_equal(np.sort(per20, 0), np.sort(per, 0)))
     if a.check:
         sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
         from test_gpu_parser import _oracle_scores
