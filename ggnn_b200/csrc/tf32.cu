@@ -5,7 +5,7 @@
 //   GATES  g = sigmoid([tf32(acts), tf32(h)] @ tf32(Wg) + bg);  rh = g[:, :h]*h;  u = g[:, h:]
 //   CAND   c = tanh([tf32(acts), tf32(rh)] @ tf32(Wc) + bc);    h' = u*h + (1-u)*c
 //
-// One CTA = one 128-row x (<=128)-column output tile.  Warp roles:
+// One CTA = one 128-row x (<=256)-column output tile (two CTAs per SM: 2 x 48 KB stages, 256 TMEM columns each).  Warp roles:
 //   warps 0-3  operand producers: activations by 16-byte cp.async straight into the
 //              128B-swizzled tile (no register staging), weights by one TMA box per K chunk;
 //              then the epilogue (tcgen05.ld, fused bias / sigmoid / tanh / state update)
@@ -19,11 +19,11 @@
 namespace {
 
 constexpr int BM = 128;           // rows per tile  (UMMA M, one TMEM lane per row)
-constexpr int BN = 128;           // max columns per tile (UMMA N, TMEM columns)
+constexpr int BN = 256;           // max columns per tile (UMMA N, TMEM columns)
 constexpr int BKF = 32;           // floats per K chunk = one 128-byte swizzle row
-constexpr int STAGES = 3;
+constexpr int STAGES = 2;           // 2 x 48 KB: two CTAs per SM, so one CTA's epilogue overlaps the other's mainloop
 constexpr int A_BYTES = BM * BKF * 4;     // 16 KB
-constexpr int B_BYTES = BN * BKF * 4;     // 16 KB
+constexpr int B_BYTES = BN * BKF * 4;     // 32 KB
 constexpr int NPROD = 128;                // producer / epilogue threads (warps 0-3)
 constexpr int NTHREADS = NPROD + 32;      // + MMA warp
 constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
@@ -400,9 +400,11 @@ int ggnn_make_tmap_2d_f16(ggnn_ctx* ctx, CUtensorMap* tm, const void* base, int6
   return GGNN_OK;
 }
 
+// np = output columns one GEMM sees (per edge type for the message weights): the box never needs more rows
 static int make_weight_map(ggnn_ctx* ctx, CUtensorMap* tm, float* base, int64_t rows, int64_t cols,
-                           int* box_rows) {
+                           int* box_rows, int np) {
   *box_rows = (int)(rows < BN ? rows : BN);
+  if (*box_rows > np) *box_rows = np;
   return ggnn_make_tmap_2d(ctx, tm, base, rows, cols, *box_rows);
 }
 
@@ -423,7 +425,7 @@ int ggnn_tf32_pack_nt_edge(ggnn_ctx* ctx, const float* W_src, ggnn_nt_weights* w
   const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
   pack_blocks_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src, h, w->We, two_e, 1, 1, h, hp);
   GGNN_LAUNCHED(ctx);
-  return make_weight_map(ctx, &w->tmE, w->We, (int64_t)two_e * hp, hp, &w->rowsE);
+  return make_weight_map(ctx, &w->tmE, w->We, (int64_t)two_e * hp, hp, &w->rowsE, hp);
 }
 
 int ggnn_tf32_pack_nt_gru(ggnn_ctx* ctx, ggnn_nt_weights* w, cudaStream_t st) {
@@ -432,8 +434,8 @@ int ggnn_tf32_pack_nt_gru(ggnn_ctx* ctx, ggnn_nt_weights* w, cudaStream_t st) {
   GGNN_LAUNCHED(ctx);
   pack_blocks_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, h, w->Wc, 1, 2, 1, h, hp);
   GGNN_LAUNCHED(ctx);
-  GGNN_TRY(make_weight_map(ctx, &w->tmG, w->Wg, 2 * hp, 2 * hp, &w->rowsG));
-  return make_weight_map(ctx, &w->tmC, w->Wc, 2 * hp, hp, &w->rowsC);
+  GGNN_TRY(make_weight_map(ctx, &w->tmG, w->Wg, 2 * hp, 2 * hp, &w->rowsG, 2 * hp));
+  return make_weight_map(ctx, &w->tmC, w->Wc, 2 * hp, hp, &w->rowsC, 2 * hp);
 }
 
 int ggnn_tf32_nt(ggnn_ctx* ctx, const float* A1, const float* A2, int lda, const int32_t* gather, int64_t M,
@@ -476,7 +478,7 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
   GGNN_TRY(realloc_f(ctx, ew.Wt_tf32, (size_t)two_e * hp * hp));
   pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32, two_e, h, hp);
   GGNN_LAUNCHED(ctx);
-  GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt, ew.Wt_tf32, (int64_t)two_e * hp, hp, &ew.tm_rows));
+  GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt, ew.Wt_tf32, (int64_t)two_e * hp, hp, &ew.tm_rows, hp));
   if (with_gru) {
     GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32, (size_t)4 * hp * hp));
     GGNN_TRY(realloc_f(ctx, ctx->Wct_tf32, (size_t)2 * hp * hp));
@@ -490,8 +492,8 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
     GGNN_LAUNCHED(ctx);
     pack_bias_kernel<<<(hp + 255) / 256, 256, 0, st>>>(ctx->bc, ctx->bc_pad, 1, h, hp);
     GGNN_LAUNCHED(ctx);
-    GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wg, ctx->Wgt_tf32, 2 * hp, 2 * hp, &ctx->tm_rows_g));
-    GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wc, ctx->Wct_tf32, hp, 2 * hp, &ctx->tm_rows_c));
+    GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wg, ctx->Wgt_tf32, 2 * hp, 2 * hp, &ctx->tm_rows_g, 2 * hp));
+    GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wc, ctx->Wct_tf32, hp, 2 * hp, &ctx->tm_rows_c, hp));
     if (2 * hp <= 256) GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg256, ctx->Wgt_tf32, 2 * hp, 2 * hp, 2 * hp));
   }
   return GGNN_OK;
