@@ -41,3 +41,5 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
                    float* h_state, cudaStream_t st);
 int ggnn_aggregate(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float* acts, int h,
                    bool round_tf32, cudaStream_t st);
+int ggnn_aggregate_f16(ggnn_ctx* ctx, const ggnn_plan& plan, const void* msg_half, float* acts, int h,
+                       bool round_tf32, cudaStream_t st);

@@ -7,6 +7,7 @@
 //   GATES  g = sigmoid([acts, h] @ Wg + bg); rh = g[:, :h] * h; u = g[:, h:]     (TF GRUCell)
 //   CAND   c = tanh([acts, rh] @ Wc + bc);  h' = u*h + (1-u)*c
 #include "plan.cuh"
+#include <cuda_fp16.h>
 #include "tc.cuh"
 #include "heads.cuh"
 
@@ -187,9 +188,21 @@ sgemm_kernel(const sgemm_params p) {
 // Segmented gather-sum: one warp per target node, lanes across the feature dimension with
 // 128-bit loads; messages are added in tmsg order (ascending channel, source) -- no atomics,
 // so the result is bit-reproducible.
+// one message row chunk (4 columns) as FP32, from FP32 or FP16 storage
+__device__ __forceinline__ float4 ld_msg4(const float* msg, size_t row, int h, int c) {
+  return __ldg(reinterpret_cast<const float4*>(msg + row * h) + c);
+}
+__device__ __forceinline__ float4 ld_msg4(const __half* msg, size_t row, int h, int c) {
+  const uint2 v = __ldg(reinterpret_cast<const uint2*>(msg + row * h) + c);
+  const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+  const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+  return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+
+template <typename MT>
 __global__ void __launch_bounds__(256)
 aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg,
-                 const float* __restrict__ msg, float* __restrict__ acts, int64_t N, int h,
+                 const MT* __restrict__ msg, float* __restrict__ acts, int64_t N, int h,
                  int round_tf32) {
   const int lane = threadIdx.x & 31;
   const int64_t node = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -201,10 +214,10 @@ aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ t
     int j = j0;
     for (; j + 4 <= j1; j += 4) {
       int r0 = __ldg(tmsg + j), r1 = __ldg(tmsg + j + 1), r2 = __ldg(tmsg + j + 2), r3 = __ldg(tmsg + j + 3);
-      float4 m0 = __ldg(reinterpret_cast<const float4*>(msg + (size_t)r0 * h) + c);
-      float4 m1 = __ldg(reinterpret_cast<const float4*>(msg + (size_t)r1 * h) + c);
-      float4 m2 = __ldg(reinterpret_cast<const float4*>(msg + (size_t)r2 * h) + c);
-      float4 m3 = __ldg(reinterpret_cast<const float4*>(msg + (size_t)r3 * h) + c);
+      float4 m0 = ld_msg4(msg, (size_t)r0, h, c);
+      float4 m1 = ld_msg4(msg, (size_t)r1, h, c);
+      float4 m2 = ld_msg4(msg, (size_t)r2, h, c);
+      float4 m3 = ld_msg4(msg, (size_t)r3, h, c);
       acc.x += m0.x; acc.y += m0.y; acc.z += m0.z; acc.w += m0.w;
       acc.x += m1.x; acc.y += m1.y; acc.z += m1.z; acc.w += m1.w;
       acc.x += m2.x; acc.y += m2.y; acc.z += m2.z; acc.w += m2.w;
@@ -212,7 +225,7 @@ aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ t
     }
     for (; j < j1; ++j) {
       int r0 = __ldg(tmsg + j);
-      float4 m0 = __ldg(reinterpret_cast<const float4*>(msg + (size_t)r0 * h) + c);
+      float4 m0 = ld_msg4(msg, (size_t)r0, h, c);
       acc.x += m0.x; acc.y += m0.y; acc.z += m0.z; acc.w += m0.w;
     }
     if (round_tf32) {   // acts only feeds tensor-core operands in TF32 mode: round once, here
@@ -230,8 +243,20 @@ int ggnn_aggregate(ggnn_ctx* ctx, const ggnn_plan& plan, const float* msg, float
   if (plan.N == 0) return GGNN_OK;
   prof_scope ps(ctx, GGNN_STAGE_AGG, st);
   const int64_t threads = plan.N * 32;
-  aggregate_kernel<<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(plan.tptr, plan.tmsg, msg,
-                                                                      acts, plan.N, h, round_tf32 ? 1 : 0);
+  aggregate_kernel<float><<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(plan.tptr, plan.tmsg, msg,
+                                                                             acts, plan.N, h, round_tf32 ? 1 : 0);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+// same, message rows stored as FP16 with pitch h (TF32 mode, hidden sizes the fused kernels do not cover)
+int ggnn_aggregate_f16(ggnn_ctx* ctx, const ggnn_plan& plan, const void* msg_half, float* acts, int h,
+                       bool round_tf32, cudaStream_t st) {
+  if (plan.N == 0) return GGNN_OK;
+  prof_scope ps(ctx, GGNN_STAGE_AGG, st);
+  const int64_t threads = plan.N * 32;
+  aggregate_kernel<__half><<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(
+      plan.tptr, plan.tmsg, reinterpret_cast<const __half*>(msg_half), acts, plan.N, h, round_tf32 ? 1 : 0);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

@@ -518,11 +518,15 @@ int ggnn_step_tf32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.M = plan.max_tiles * GGNN_TILE_M;
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg;
+    // messages as FP16 (the 11-bit significand of a TF32 operand, half the bytes for the aggregation), as in the
+    // fused kernels; the training tape keeps FP32 messages
+    if (!bufs.tape_r) p.out_half = reinterpret_cast<__half*>(bufs.msg);
     p.b_bytes = ew.tm_rows * BKF * 4;
     GGNN_TRY(launch<MODE_MSG>(ctx, p, ew.tm_Wt, (unsigned)plan.max_tiles, st));
   }
   if (fused) return ggnn_gru_fused_step(ctx, plan, bufs.msg, h_state, last_step, st);
-  GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, /*round_tf32=*/true, st));
+  if (!bufs.tape_r) GGNN_TRY(ggnn_aggregate_f16(ctx, plan, bufs.msg, bufs.acts, h, /*round_tf32=*/true, st));
+  else GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, /*round_tf32=*/true, st));
   const unsigned mt = (unsigned)ceil_div64(plan.N, BM);
   {
     prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
