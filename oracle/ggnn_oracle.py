@@ -27,9 +27,14 @@ PINNING STATUS
   by the reference's own ``graph_to_adj_mat_bd`` / ``process_sentence`` run in
   the authoring container (scripts/make_golden.py -> tests/golden/*.npz) and
   against the conventions fixed by tests_chem.py:29-48.
-  floating-point part (message transform, aggregation, GRU): PARITY UNPINNED --
-  the reference has no test, golden vector or saved activation for it
-   and TensorFlow cannot be run here or on the GPU box.
+  floating-point part (message transform, aggregation, GRU): PINNED AT THE
+  REFERENCE'S OWN CALL SITES -- scripts/make_golden_fp.py executes the reference's
+  compute_final_node_representations / compute_timestep_fast / _normal
+  (chem_tensorflow_dense.py:312-437) over NumPy-backed stand-ins for the TF
+  primitives they call (GRUCell restated from TF's published GRUCell.call) and
+  commits tests/golden/ref_propagation.npz; tests/test_oracle.py holds every form
+  below to it at 1e-13 in FP64.  Not pinnable without TensorFlow itself: its
+  kernels' summation order (inside the norm-wise tolerance) and GRUCell's source.
 """
 from __future__ import annotations
 

@@ -17,8 +17,10 @@ Restated from (citations relative to /root/reference):
 
 PINNING: the NumPy part (masks, target formatting, decode, scorer) is PINNED against
 tests/golden/parser_decode.npz, produced by scripts/make_golden_parser.py running the reference's
-own functions.  The TF part (embedding lookup, matmul, softmax) is unpinned like the rest of the
-floating-point path.
+own functions.  The TF part (embedding lookup, concat / pad, the one-layer MLPs, softmax) is PINNED at the
+reference's own call sites: scripts/make_golden_heads.py executes get_initial_node_representation and
+gated_regression (with the reference's utils.MLP) over NumPy-backed TF primitives and commits
+tests/golden/ref_heads.npz; tests/test_oracle.py holds initial_node_representation() and heads() to it.
 """
 from __future__ import annotations
 

@@ -99,3 +99,29 @@ def test_front_end_and_heads_numerics():
     with pytest.raises(ValueError):                                         # index outside its table
         bad = idx.copy(); bad[0, 0, 1] = 99
         ev.embed(torch.from_numpy(bad).cuda())
+
+
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_front_end_and_heads_against_the_reference_functions_own_output(golden_dir, name):
+    """ggnn_embed_nodes / ggnn_heads_decode against tests/golden/ref_heads.npz: outputs of the reference's own
+    get_initial_node_representation and gated_regression (btb branch, utils.MLP) run over NumPy-backed TF
+    primitives by scripts/make_golden_heads.py."""
+    d = np.load(os.path.join(golden_dir, "ref_heads.npz"))
+    b, v, h, Osz, E_out = (int(x) for x in d[f"{name}_meta"])
+    heads = PE.ParserHeads(d[f"{name}_loc_embeddings"], d[f"{name}_pos_embeddings"], d[f"{name}_word_embeddings"],
+                           d[f"{name}_head_W"], d[f"{name}_head_b"], d[f"{name}_label_W"], d[f"{name}_label_b"])
+    ev = PE.ParserEvaluator(ggnn_b200.from_dict(O.make_weights(4, h, 0)), heads, "cuda:0", num_timesteps=1)
+    idx = np.ascontiguousarray(d[f"{name}_word_inputs"][..., :4])
+    h0 = ev.embed(torch.from_numpy(idx).cuda())
+    assert np.array_equal(h0.cpu().numpy(), d[f"{name}_h0_float32"])
+    hT = torch.from_numpy(d[f"{name}_h_T"]).cuda()
+    n_active = torch.full((b,), v, dtype=torch.int32)                      # every row active
+    pred, ph, pl = ev.decode(hT, h0, n_active, probs=True)
+    rph = d[f"{name}_p_head_float64"].reshape(b, v, Osz)
+    rpl = d[f"{name}_p_label_float64"].reshape(b, v, E_out)
+    # the product masks head positions >= n_active (get_mask, chem_tensorflow_dense.py:633-661)
+    assert np.abs(ph.cpu().numpy()[..., :v] - rph[..., :v]).max() <= 1e-6
+    assert np.abs(pl.cpu().numpy() - rpl).max() <= 1e-6
+    p = pred.cpu().numpy()
+    assert np.array_equal(p[:, 1:, 0], rph[:, 1:, :v].argmax(-1))
+    assert np.array_equal(p[:, 1:, 1], rpl[:, 1:].argmax(-1))

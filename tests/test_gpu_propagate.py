@@ -303,3 +303,36 @@ def test_misaligned_pointers_are_rejected():
     e = torch.zeros(0, 3, dtype=torch.int32, device="cuda")
     with pytest.raises(ValueError, match="aligned"):
         prop.propagate_edges(buf[1:].view(8, 16), e, num_timesteps=1)
+
+
+def _ref_case(d, name):
+    b, v, E, h, T, bias, fixed_ts = (int(x) for x in d[f"{name}_meta"])
+    adj = np.zeros((b, 2 * E, v, v), np.float32)
+    nz = d[f"{name}_adj_nz"]
+    adj[nz[:, 0], nz[:, 1], nz[:, 2], nz[:, 3]] = 1.0
+    keys = ["edge_weights", "edge_weights_fixed", "gru_gate_kernel", "gru_gate_bias", "gru_cand_kernel",
+            "gru_cand_bias"] + (["edge_biases", "edge_biases_fixed"] if bias else [])
+    w = {k: d[f"{name}_{k}"] for k in keys}
+    return b, v, E, h, T, (None if fixed_ts < 0 else fixed_ts), adj, w, d[f"{name}_h0"]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_against_the_reference_functions_own_output(golden_dir, name, precision):
+    """The CUDA path against tests/golden/ref_propagation.npz: outputs of the reference's own
+    compute_final_node_representations (chem_tensorflow_dense.py:312-437) run over NumPy-backed TF
+    primitives by scripts/make_golden_fp.py.  Dense route and edge-list route."""
+    d = np.load(os.path.join(golden_dir, "ref_propagation.npz"))
+    b, v, E, h, T, fixed_ts, adj, w, h0 = _ref_case(d, name)
+    ref = d[f"{name}_out_fast_float64"]
+    tol = {"fp32": 1e-5, "tf32": 2e-3, "f16": 2e-3}[precision]
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=T, fixed_ts=fixed_ts,
+                                                       precision=precision)
+    assert out.shape == ref.shape and out.dtype == np.float32
+    assert O.normwise_err(out, ref) <= tol
+    edges = O.dense_to_edges(adj)
+    sp = ggnn_b200.compute_final_node_representations_sparse(h0.reshape(b * v, h), edges, weights=w,
+                                                             num_timesteps=T, fixed_ts=fixed_ts, precision=precision)
+    assert O.normwise_err(sp.reshape(b, v, h), ref) <= tol
+    if precision == "fp32":
+        assert np.array_equal(sp.reshape(b, v, h), out)       # same summation order on both routes

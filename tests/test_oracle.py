@@ -281,3 +281,67 @@ def test_philox_known_answers():
     m = G.philox_mask(100003, seed=7, stream=3, keep=0.9)
     assert m.shape == (100003,) and abs(float(m.mean()) - 0.9) < 5e-3
     assert not np.array_equal(m, G.philox_mask(100003, seed=7, stream=4, keep=0.9))
+
+
+def _ref_case(d, name):
+    b, v, E, h, T, bias, fixed_ts = (int(x) for x in d[f"{name}_meta"])
+    adj = np.zeros((b, 2 * E, v, v), np.float32)
+    nz = d[f"{name}_adj_nz"]
+    adj[nz[:, 0], nz[:, 1], nz[:, 2], nz[:, 3]] = 1.0
+    w = {k: d[f"{name}_{k}"] for k in ("edge_weights", "edge_biases", "edge_weights_fixed", "edge_biases_fixed",
+                                        "gru_gate_kernel", "gru_gate_bias", "gru_cand_kernel", "gru_cand_bias")}
+    return b, v, E, h, T, bool(bias), (None if fixed_ts < 0 else fixed_ts), adj, w, d[f"{name}_h0"]
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_oracle_pinned_by_the_reference_functions_run_on_a_numpy_tf_shim(golden_dir, name):
+    """tests/golden/ref_propagation.npz holds outputs of the reference's OWN
+    compute_final_node_representations / compute_timestep_fast / compute_timestep_normal
+    (chem_tensorflow_dense.py:312-437) executed over NumPy-backed TF primitives
+    (scripts/make_golden_fp.py; GRUCell restated from TF's rnn_cell_impl).  Every form of the oracle
+    has to reproduce them."""
+    d = np.load(os.path.join(golden_dir, "ref_propagation.npz"))
+    b, v, E, h, T, bias, fixed_ts, adj, w, h0 = _ref_case(d, name)
+    ref = d[f"{name}_out_fast_float64"]
+    got = O.propagate_dense(h0, adj, w, T, fixed_ts=fixed_ts, use_bias=bias, dtype=np.float64, form="fast")
+    assert np.abs(got - ref).max() <= 1e-13
+    if fixed_ts is None:
+        assert np.abs(d[f"{name}_out_normal_float64"] - ref).max() <= 1e-13     # the reference's two forms agree
+        got = O.propagate_dense(h0, adj, w, T, use_bias=bias, dtype=np.float64, form="loop")
+        assert np.abs(got - d[f"{name}_out_normal_float64"]).max() <= 1e-13
+    edges = O.dense_to_edges(adj)
+    got = O.propagate_edges(h0.reshape(b * v, h), edges, w, T, fixed_ts=fixed_ts, use_bias=bias, dtype=np.float64)
+    assert np.abs(got.reshape(b, v, h) - ref).max() <= 1e-13
+    # FP32 evaluation of the reference's code and of the oracle: both inside the strict tolerance
+    assert O.normwise_err(d[f"{name}_out_fast_float32"], ref) <= 1e-5
+    got32 = O.propagate_dense(h0, adj, w, T, fixed_ts=fixed_ts, use_bias=bias, dtype=np.float32)
+    assert O.normwise_err(got32, ref) <= 1e-5
+    # torch-CPU restatement used as the timed CPU baseline
+    from oracle import cpu_reference as C
+    import torch
+    wt = O._select_weights(w, fixed_ts)
+    Tt = T if fixed_ts is None else fixed_ts
+    got_t = C.propagate_dense_torch_cpu(torch.from_numpy(h0), torch.from_numpy(adj), wt, Tt, use_bias=bias)
+    assert O.normwise_err(got_t.numpy(), ref) <= 1e-5
+    got_e = C.propagate_edges_torch_cpu(torch.from_numpy(h0.reshape(b * v, h)), torch.from_numpy(edges), wt, Tt,
+                                        use_bias=bias)
+    assert O.normwise_err(got_e.numpy().reshape(b, v, h), ref) <= 1e-5
+
+
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_front_end_and_heads_pinned_by_the_reference_functions(golden_dir, name):
+    """N1 / N2 floating-point part: tests/golden/ref_heads.npz holds the outputs of the reference's own
+    get_initial_node_representation (chem_tensorflow_dense.py:264-310) and gated_regression (:439-505, with
+    the reference's utils.MLP) executed over NumPy-backed TF primitives (scripts/make_golden_heads.py)."""
+    from oracle import parser_oracle as P
+    d = np.load(os.path.join(golden_dir, "ref_heads.npz"))
+    b, v, h, Osz, E_out = (int(x) for x in d[f"{name}_meta"])
+    h0 = P.initial_node_representation(d[f"{name}_word_inputs"], d[f"{name}_loc_embeddings"],
+                                       d[f"{name}_pos_embeddings"], d[f"{name}_word_embeddings"], h)
+    assert np.array_equal(h0, d[f"{name}_h0_float64"])                      # a gather + zero padding: exact
+    ph, pe = P.heads(d[f"{name}_h_T"], h0, d[f"{name}_head_W"], d[f"{name}_head_b"],
+                     d[f"{name}_label_W"], d[f"{name}_label_b"])
+    assert ph.shape == (b, v * Osz) and pe.shape == (b, v * E_out)
+    assert np.abs(ph - d[f"{name}_p_head_float64"]).max() <= 1e-14
+    assert np.abs(pe - d[f"{name}_p_label_float64"]).max() <= 1e-14
+    assert np.abs(d[f"{name}_p_head_float32"] - ph).max() <= 1e-6
