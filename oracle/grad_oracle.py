@@ -9,8 +9,11 @@ oracle therefore is torch-CPU FP64 autograd over the same restatement of the for
 ggnn_oracle.py holds (edge-list form, chem_tensorflow_dense.py:391-437 + TF GRUCell), with both
 dropouts at keep-probability 1.0 (or with externally supplied edge-weight masks).
 
-PARITY UNPINNED for the floating-point path (see ggnn_oracle.py): pinned only against the
-forward oracle (the FP64 forward here must equal ggnn_oracle.propagate_edges to 1e-12).
+PINNING: the FP64 forward here must equal ggnn_oracle.propagate_edges to 1e-12, which in turn is held to
+the outputs of the reference's own propagation functions (tests/golden/ref_propagation.npz, see
+ggnn_oracle.py); the gradients are autograd of that forward, cross-checked by central finite differences
+(tests/test_oracle.py).  The dropout semantics at keep < 1 (tf.nn.dropout, DropoutWrapper) are restated from
+TensorFlow's documentation and are not pinnable without TensorFlow.
 """
 from __future__ import annotations
 
