@@ -121,11 +121,13 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
     free_dev(c, c->edge[s].B);
     free_dev(c, c->edge[s].Wt_tf32);
     if (c->edge[s].Wt_f16) { cudaFree(c->edge[s].Wt_f16); c->edge[s].Wt_f16 = nullptr; }
+    free_dev(c, c->edge[s].B_pad16);
   }
   free_dev(c, c->Wg); free_dev(c, c->bg); free_dev(c, c->Wc); free_dev(c, c->bc);
   if (c->Wgt_f16) cudaFree(c->Wgt_f16);
   if (c->Wct_f16) cudaFree(c->Wct_f16);
   free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
+  free_dev(c, c->bg_w16); free_dev(c, c->bc_w16);
   if (c->ws) {
     ctx_ext* e = ext_of(c);
     for (auto& a : e->ar) if (a.p) cudaFree(a.p);
@@ -194,6 +196,18 @@ extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const
     ctx->two_e = two_e;
     ctx->h = h;
     ctx->hp = (int)align_up((size_t)h, 32);
+    const int hw = h > 128 ? (int)align_up((size_t)h, 64) : 0;
+    if (hw != ctx->hw16 || (h <= 128) != (ctx->hp_f16_narrow)) {   // the FP16 packs change layout: drop them
+      for (int s2 = 0; s2 < GGNN_MAX_SLOTS; ++s2) {
+        if (ctx->edge[s2].Wt_f16) { cudaFree(ctx->edge[s2].Wt_f16); ctx->edge[s2].Wt_f16 = nullptr; }
+        free_dev(ctx, ctx->edge[s2].B_pad16);
+      }
+      if (ctx->Wgt_f16) { cudaFree(ctx->Wgt_f16); ctx->Wgt_f16 = nullptr; }
+      if (ctx->Wct_f16) { cudaFree(ctx->Wct_f16); ctx->Wct_f16 = nullptr; }
+      free_dev(ctx, ctx->bg_w16); free_dev(ctx, ctx->bc_w16);
+    }
+    ctx->hw16 = hw;
+    ctx->hp_f16_narrow = h <= 128;
   }
   ggnn_edge_weights& ew = ctx->edge[slot];
   GGNN_TRY(dup_dev(ctx, ew.W, W, (size_t)two_e * h * h, st));
@@ -207,6 +221,7 @@ extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const
   }
   GGNN_TRY(ggnn_tf32_pack_weights(ctx, slot, has_gru, st));
   GGNN_TRY(ggnn_f16_pack_weights(ctx, slot, has_gru, st));
+  GGNN_TRY(ggnn_w16_pack_weights(ctx, slot, has_gru, st));
   ew.set = true;
   return GGNN_OK;
 }
@@ -241,8 +256,8 @@ int check_ready(ggnn_ctx* ctx, int slot, int precision) {
   if (!ctx->gru_set || !ctx->edge[slot].set) GGNN_FAIL(ctx, GGNN_E_STATE, "weights for slot %d not set", slot);
   if (precision != GGNN_PREC_FP32 && precision != GGNN_PREC_TF32 && precision != GGNN_PREC_F16)
     GGNN_FAIL(ctx, GGNN_E_ARG, "bad precision %d", precision);
-  if (precision == GGNN_PREC_F16 && !ggnn_f16_supported(ctx))
-    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "F16 path needs a hidden size in (96, 128], got h=%d", ctx->h);
+  if (precision == GGNN_PREC_F16 && !ggnn_f16_supported(ctx) && !ggnn_w16_supported(ctx))
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "F16 path needs a hidden size in (96, 512], got h=%d", ctx->h);
   if (precision == GGNN_PREC_TF32 && !ggnn_tf32_supported(ctx))
     GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "TF32 path does not support h=%d", ctx->h);
   return GGNN_OK;
@@ -260,13 +275,15 @@ int read_i64(ggnn_ctx* ctx, const int64_t* dev, int64_t* out, cudaStream_t st) {
 // GGNN_PREC_F16: before the planning synchronisation, convert the states to FP16 and collect
 // max|h0| (slot 6) and, once per weight set, max|W| / max|B| (slots 4, 5)
 int f16_prologue(ggnn_ctx* ctx, int slot, const float* h0, int64_t N, cudaStream_t st) {
-  GGNN_TRY(arena_reserve(ctx, 4, (size_t)N * 256 + 256, st));
+  const bool wide = ggnn_w16_supported(ctx);
+  GGNN_TRY(arena_reserve(ctx, 4, (size_t)N * (wide ? ctx->hw16 * 2 : 256) + 256, st));
   GGNN_CUDA(ctx, cudaMemsetAsync(ctx->d_mail + 4, 0, 3 * sizeof(int64_t), st));
   ggnn_edge_weights& ew = ctx->edge[slot];
   if (ew.absmax_w < 0.f) {
     GGNN_TRY(ggnn_absmax(ctx, ew.W, (int64_t)ctx->two_e * ctx->h * ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 4), st));
     if (ew.B) GGNN_TRY(ggnn_absmax(ctx, ew.B, (int64_t)ctx->two_e * ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 5), st));
   }
+  if (wide) return ggnn_w16_state_in(ctx, h0, ext_of(ctx)->ar[4].p, N, reinterpret_cast<unsigned*>(ctx->d_mail + 6), st);
   return ggnn_f16_state_in(ctx, h0, ext_of(ctx)->ar[4].p, N, reinterpret_cast<unsigned*>(ctx->d_mail + 6), st);
 }
 
@@ -360,8 +377,11 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
     return GGNN_OK;
   }
   if (precision == GGNN_PREC_F16) {           // states already converted by f16_prologue (arena 4)
-    for (int t = 0; t < T; ++t)
-      GGNN_TRY(ggnn_step_f16(ctx, slot, plan, sb.msg, ext_of(ctx)->ar[4].p, h_state, t == T - 1, st));
+    const bool wide = ggnn_w16_supported(ctx);
+    for (int t = 0; t < T; ++t) {
+      if (wide) GGNN_TRY(ggnn_step_w16(ctx, slot, plan, sb.msg, sb.acts, sb.rh, sb.u, ext_of(ctx)->ar[4].p, h_state, t == T - 1, st));
+      else GGNN_TRY(ggnn_step_f16(ctx, slot, plan, sb.msg, ext_of(ctx)->ar[4].p, h_state, t == T - 1, st));
+    }
     return GGNN_OK;
   }
   if (precision == GGNN_PREC_TF32 && T > 0)   // state is kept TF32-rounded between steps
@@ -599,6 +619,7 @@ extern "C" int ggnn_optimizer_step(ggnn_ctx* ctx, int slot, const float* grads, 
   ctx->repack_in_place = true;
   int rc = ggnn_tf32_pack_weights(ctx, slot, true, st);
   if (rc == GGNN_OK) rc = ggnn_f16_pack_weights(ctx, slot, true, st);
+  if (rc == GGNN_OK) rc = ggnn_w16_pack_weights(ctx, slot, true, st);
   ctx->repack_in_place = false;
   if (rc != GGNN_OK) return rc;
   ext_of(ctx)->tape.valid = false;

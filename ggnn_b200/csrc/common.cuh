@@ -17,8 +17,9 @@ struct ggnn_edge_weights {
   float* W = nullptr;      // [two_e, h, h]  FP32, reference layout (K rows, N cols)
   float* B = nullptr;      // [two_e, h] or nullptr
   float* Wt_tf32 = nullptr;// [two_e, hp, hp] TF32-rounded, transposed ([n][k]), zero padded to hp
-  void*  Wt_f16 = nullptr; // [two_e, 128, 128] FP16, transposed ([n][k]), zero padded (hp == 128 only)
+  void*  Wt_f16 = nullptr; // [two_e, P, P] FP16, transposed ([n][k]), zero padded; P = 128 (hp == 128) or hw16 (h > 128)
   CUtensorMap tm_Wt16;     // TMA view of Wt_f16 as [two_e*128 rows, 128 cols], box 64 x 128
+  float* B_pad16 = nullptr;// [two_e, hw16] FP32 zero-padded biases (wide16.cu, h > 128)
   float  absmax_w = -1.f;  // max|W|, max|B| of this slot (host copy, < 0 = not computed yet)
   float  absmax_b = 0.f;
   CUtensorMap tm_Wt;       // TMA view of Wt_tf32 as [two_e*hp rows, hp cols], box 32 x tm_rows
@@ -33,6 +34,8 @@ struct ggnn_ctx {
   int two_e = 0;
   int h = 0;
   int hp = 0;              // h padded to the tensor-core tile granularity
+  bool hp_f16_narrow = true; // the FP16 packs are the 128-pitch ones of f16.cu
+  int hw16 = 0;            // h > 128: h padded to 64 (pitch of the FP16 buffers of wide16.cu), else 0
   ggnn_edge_weights edge[GGNN_MAX_SLOTS];
   // GRU cell (shared by both slots)
   float* Wg = nullptr;     // [2h, 2h]
@@ -44,6 +47,8 @@ struct ggnn_ctx {
   void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
   void* Wct_f16 = nullptr;   // [128, 256]
   CUtensorMap tm_Wg16, tm_Wc16;
+  float* bg_w16 = nullptr;   // [2*hw16], [hw16] zero-padded GRU biases (wide16.cu)
+  float* bc_w16 = nullptr;
   CUtensorMap tm_Wg, tm_Wc, tm_Wg256;  // TMA views of the packed GRU kernels (256-row box: fused kernel)
   unsigned long long* dbg_trace = nullptr;   // device buffer for kernel phase traces (ggnn_debug_trace)
   bool   no_fused = false;   // debugging / A-B switch (GGNN_NO_FUSED=1)
@@ -72,7 +77,7 @@ struct ggnn_ctx {
 
 // cudaFuncSetAttribute is per device: remember per ctx (a process may own one ctx per GPU), not in a static
 enum { GGNN_ATTR_TF32_GEMM0 = 0 /* + mode 0..3 */, GGNN_ATTR_GRU_FUSED = 4, GGNN_ATTR_MSG_TC = 5, GGNN_ATTR_F16 = 6,
-       GGNN_ATTR_TN = 7 };
+       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2 */ };
 #define GGNN_ENSURE_SMEM(ctx, bit, kernel, bytes)                                                          \
   do {                                                                                                     \
     if (!((ctx)->attr_mask & (1u << (bit)))) {                                                             \

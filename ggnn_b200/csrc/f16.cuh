@@ -16,3 +16,13 @@ int ggnn_absmax(ggnn_ctx* ctx, const float* x, int64_t n, unsigned* out_bits, cu
 // unrounded FP32 state is also written to h_out [N, h]
 int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16,
                   float* h_out, bool last_step, cudaStream_t st);
+
+// ---- hidden sizes above 128 (wide16.cu): FP16 buffers of pitch ctx->hw16 = ceil64(h) <= 512 ----
+bool ggnn_w16_supported(const ggnn_ctx* ctx);
+int ggnn_w16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st);
+int ggnn_w16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, unsigned* absmax_bits,
+                      cudaStream_t st);
+// one timestep; msg16 [max_tiles*128, hw16], acts16 / rh16 / u16 [N, hw16] FP16 scratch; state16 in/out; on the
+// last step the FP32 state is also written to h_out [N, h]
+int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* acts16, void* rh16, void* u16,
+                  void* state16, float* h_out, bool last_step, cudaStream_t st);

@@ -1,0 +1,571 @@
+// wide16.cu -- GGNN_PREC_F16 for hidden sizes above 128 (C4: h = 256; the WSJ shapes: h = 400).
+//
+// The three contractions of a timestep
+//   MSG    M[r, :]  = f16(h[src(r), :]) @ f16(W[type]) + B[type]                      -> FP16 rows
+//   GATES  g = sigmoid([x, h] @ Wg + bg);  rh = f16(g[:, :h] * h);  u = f16(g[:, h:])
+//   CAND   c = tanh([x, rh] @ Wc + bc);    h' = c + u * (h - c)                        -> FP16 state (+ FP32 result)
+// run on ONE persistent, warp-specialised tcgen05 kernel (kind::f16, FP32 accumulators in TMEM).
+// The hidden size is padded to hw = a multiple of 64 (one 128-byte swizzle row of FP16).
+//
+// Tiling: the weight matrix is cut into column slices of NW <= 256 output columns whose K-major FP16
+// panel [NW x K] fits 128 KB of shared memory.  A CTA owns a contiguous range of (slice, 128-row tile)
+// work items, slice-major, so the panel stays RESIDENT while the CTA streams row tiles under it: only
+// the activations move through the 4 x 16 KB chunk ring (one [128 x 64] FP16 chunk per stage, by TMA
+// when the rows are contiguous, by 16-byte cp.async when they are gathered through msg_src).  At
+// h = 256 a both-operands-streamed 128 x 256 tile needs 96 B/clk/SM from L2 at the kind::f16 rate --
+// more than twice what the L2 delivers per SM -- while the resident panel needs 32 (MSG) / 64 (GRU).
+//
+// Warp roles (13 warps): 0-3 activation producers; 4 MMA issuer (also (re)loads the weight panel when the
+// (edge type, slice) key changes); 5-12 two epilogue teams of four warps (TMEM lane quarter = warp % 4),
+// each team owning alternate 64-column groups and its own 16 KB swizzled staging box that leaves by TMA
+// store.  Two TMEM accumulators (2 x 256 columns): the epilogue of item i runs under the MMAs of i+1.
+#include "f16.cuh"
+#include "tf32.cuh"
+#include "tc.cuh"
+#include <cuda_fp16.h>
+
+namespace w16 {
+
+constexpr int BM = 128;
+constexpr int BKH = 64;                         // halves per K chunk = one 128-byte swizzle row
+constexpr int CHUNK = BM * BKH * 2;             // 16 KB
+constexpr int STAGES = 4;
+constexpr int W_BYTES = 128 * 1024;             // resident weight panel
+constexpr int NPROD = 128;
+constexpr int WARP_MMA = 4;
+constexpr int WARP_EPI0 = 5;
+constexpr int N_EPI_WARPS = 8;
+constexpr int NTHREADS = (WARP_EPI0 + N_EPI_WARPS) * 32;     // 416
+constexpr int MAX_NW = 256;
+constexpr int SMEM_BYTES = W_BYTES + STAGES * CHUNK + 2 * CHUNK + 1024 /*align*/ + 256 /*barriers*/ + MAX_NW * 4;
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+constexpr float kLog2e = 1.4426950408889634f;
+
+enum { MODE_MSG = 0, MODE_GATES = 1, MODE_CAND = 2 };
+
+enum {
+  BAR_A_FULL = 0,                       // [STAGES]
+  BAR_A_EMPTY = BAR_A_FULL + STAGES,    // [STAGES] tcgen05.commit
+  BAR_W_FULL = BAR_A_EMPTY + STAGES,    // TMA bytes of the panel
+  BAR_W_FREE,                           // every MMA reading the old panel has retired
+  BAR_ACC_FULL,                         // [2]
+  BAR_ACC_EMPTY = BAR_ACC_FULL + 2,     // [2] 8 epilogue warps
+  BAR_COUNT = BAR_ACC_EMPTY + 2
+};
+static_assert(8 * BAR_COUNT + 8 <= 256, "barrier area");
+
+struct params {
+  const __half* A_gather;     // MSG, gathered rows: state16 [N, hw]
+  const int32_t* gather;      // msg_src [tiles*128] (-1 = padding) or null when the rows come by TMA
+  int tiles_per_type;         // MSG by TMA (dense-row plan): tile t reads node rows (t % tiles_per_type) * 128
+  const int32_t* tile_type;   // MSG: [tiles]
+  const int32_t* n_tiles_dev; // MSG: device-side tile count, else null
+  int n_tiles;                // row tiles when n_tiles_dev is null
+  int KC, KC1;                // K chunks in total / in the first K segment
+  int Ntot, NW, S;            // output columns, slice width, number of slices
+  const float* bias;          // [types][Ntot] zero-padded FP32
+  int hw, h;
+  int64_t N;                  // GATES / CAND: valid node rows
+  const __half* state16;      // GATES, CAND: h  [N, hw]
+  const __half* u16;          // CAND: u [N, hw]
+  float* h_out;               // CAND, last step: FP32 result [N, h] or null
+};
+
+__device__ __forceinline__ uint32_t sw_off(int r, int slot) {
+  return (r >> 3) * 1024 + (r & 7) * 128 + ((slot ^ (r & 7)) << 4);
+}
+__device__ __forceinline__ void unpack8(const uint4 v, float* f) {
+  const __half2* hp = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 t = __half22float2(hp[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 v;
+  __half2* hp = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) hp[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+  return v;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(NTHREADS, 1)
+wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+               const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmO0,
+               const __grid_constant__ CUtensorMap tmO1) {
+  extern __shared__ uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (base - tc::smem_u32(smem_raw));
+  const uint32_t sW = base;
+  const uint32_t sA = base + W_BYTES;
+  const uint32_t sO = sA + STAGES * CHUNK;
+  const uint32_t bars = sO + 2 * CHUNK;
+  auto bar = [&](int i) { return bars + 8u * i; };
+  const uint32_t tmem_slot = bars + 8u * BAR_COUNT;
+  float* s_bias = reinterpret_cast<float*>(smem_al + (bars + 256 - base));   // [NW]
+
+  const bool a_tma = p.gather == nullptr;
+  const int n_tiles = p.n_tiles_dev ? *p.n_tiles_dev : p.n_tiles;
+  const int64_t total = (int64_t)n_tiles * p.S;
+  const int64_t i_begin = total * blockIdx.x / gridDim.x;
+  const int64_t i_end = total * (blockIdx.x + 1) / gridDim.x;
+
+  if (warp == WARP_MMA && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      tc::mbar_init(bar(BAR_A_FULL + s), a_tma ? 1 : NPROD);
+      tc::mbar_init(bar(BAR_A_EMPTY + s), 1);
+    }
+    tc::mbar_init(bar(BAR_W_FULL), 1);
+    tc::mbar_init(bar(BAR_W_FREE), 1);
+    for (int s = 0; s < 2; ++s) {
+      tc::mbar_init(bar(BAR_ACC_FULL + s), 1);
+      tc::mbar_init(bar(BAR_ACC_EMPTY + s), N_EPI_WARPS);
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 0) {
+    if (lane == 0) {
+      tc::tma_prefetch_desc(&tmA1); tc::tma_prefetch_desc(&tmA2); tc::tma_prefetch_desc(&tmW);
+      tc::tma_prefetch_desc(&tmO0); tc::tma_prefetch_desc(&tmO1);
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, 512);
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
+
+  if (warp < 4) {
+    // =============================== activation producers ===============================
+    uint32_t c = 0;                                       // running chunk counter of this CTA
+    if (a_tma) {
+      if (tid == 0) {
+        for (int64_t i = i_begin; i < i_end; ++i) {
+          const int t = (int)(i % n_tiles);
+          const int row0 = (MODE == MODE_MSG ? (t % p.tiles_per_type) : t) * BM;
+          for (int kc = 0; kc < p.KC; ++kc, ++c) {
+            const int s = c % STAGES;
+            if (c >= STAGES) tc::mbar_wait(bar(BAR_A_EMPTY + s), ((c / STAGES) - 1) & 1);
+            tc::mbar_arrive_expect_tx(bar(BAR_A_FULL + s), CHUNK);
+            const bool seg2 = kc >= p.KC1;
+            tc::tma_load_2d(sA + s * CHUNK, seg2 ? &tmA2 : &tmA1, (seg2 ? kc - p.KC1 : kc) * BKH, row0,
+                            bar(BAR_A_FULL + s));
+          }
+        }
+      }
+    } else {
+      const int slot = tid & 7;                           // 16-byte slot within the 128-byte chunk row
+      const int rbase = tid >> 3;                         // rows rbase + 16*j, j = 0..7
+      uint32_t a_off[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a_off[j] = sw_off(rbase + 16 * j, slot);
+      for (int64_t i = i_begin; i < i_end; ++i) {
+        const int t = (int)(i % n_tiles);
+        int src[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) src[j] = __ldg(p.gather + (size_t)t * BM + rbase + 16 * j);
+        for (int kc = 0; kc < p.KC; ++kc, ++c) {
+          const int s = c % STAGES;
+          if (c >= STAGES) tc::mbar_wait(bar(BAR_A_EMPTY + s), ((c / STAGES) - 1) & 1);
+          const uint32_t a_st = sA + s * CHUNK;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const bool ok = src[j] >= 0;
+            tc::cp_async16(a_st + a_off[j],
+                           ok ? (const void*)(p.A_gather + (size_t)src[j] * p.hw + kc * BKH + slot * 8)
+                              : (const void*)p.A_gather,
+                           ok ? 16u : 0u);
+          }
+          tc::cp_async_arrive(bar(BAR_A_FULL + s));
+        }
+      }
+    }
+  } else if (warp == WARP_MMA) {
+    // =============================== MMA issuer + weight panel ===============================
+    if (lane == 0) {
+      uint32_t c = 0;
+      int it = 0, cur_key = -1, w_gen = 0;
+      const uint32_t panel_chunk = (uint32_t)p.NW * 128u;  // bytes of one K chunk of the panel
+      for (int64_t i = i_begin; i < i_end; ++i, ++it) {
+        const int sl = (int)(i / n_tiles), t = (int)(i % n_tiles);
+        const int type = MODE == MODE_MSG ? __ldg(p.tile_type + t) : 0;
+        const int key = type * p.S + sl;
+        const int n0 = sl * p.NW;
+        const int nw = min(p.NW, p.Ntot - n0);
+        if (key != cur_key) {
+          if (w_gen > 0) {                                 // MMAs still reading the old panel
+            tc::umma_commit(bar(BAR_W_FREE));
+            tc::mbar_wait(bar(BAR_W_FREE), (w_gen - 1) & 1);
+          }
+          tc::mbar_arrive_expect_tx(bar(BAR_W_FULL), (uint32_t)p.KC * panel_chunk);
+          for (int kc = 0; kc < p.KC; ++kc)
+            tc::tma_load_2d(sW + kc * panel_chunk, &tmW, kc * BKH, type * p.Ntot + n0, bar(BAR_W_FULL));
+          tc::mbar_wait(bar(BAR_W_FULL), w_gen & 1);
+          ++w_gen;
+          cur_key = key;
+        }
+        const int buf = it & 1;
+        if (it >= 2) tc::mbar_wait(bar(BAR_ACC_EMPTY + buf), ((it >> 1) - 1) & 1);
+        tc::fence_after_sync();
+        const uint32_t d = tmem_base + buf * MAX_NW;
+        const uint32_t idesc = tc::umma_idesc(0 /*F16*/, BM, nw);
+        for (int kc = 0; kc < p.KC; ++kc, ++c) {
+          const int s = c % STAGES;
+          tc::mbar_wait(bar(BAR_A_FULL + s), (c / STAGES) & 1);
+          tc::fence_after_sync();
+          const uint32_t a0 = sA + s * CHUNK, w0 = sW + kc * panel_chunk;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)                      // UMMA K = 16 halves = 32 bytes
+            tc::umma_f16(d, tc::umma_desc_sw128(a0 + k * 32), tc::umma_desc_sw128(w0 + k * 32), idesc,
+                         (kc | k) != 0);
+          tc::umma_commit(bar(BAR_A_EMPTY + s));
+        }
+        tc::umma_commit(bar(BAR_ACC_FULL + buf));
+      }
+    }
+    __syncwarp();
+  } else {
+    // =============================== epilogue teams ===============================
+    const int q = warp & 3;                                // TMEM lane quarter this warp may access
+    const int team = (warp - WARP_EPI0) >> 2;
+    const int r = q * 32 + lane;                           // row within the tile = TMEM lane
+    const int e256 = tid - WARP_EPI0 * 32;                 // 0..255 over both teams
+    const bool leader = (e256 & 127) == 0;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t box_addr = sO + team * CHUNK;
+    uint8_t* box = smem_al + (box_addr - base);
+    int it = 0, cur_key = -1;
+    for (int64_t i = i_begin; i < i_end; ++i, ++it) {
+      const int sl = (int)(i / n_tiles), t = (int)(i % n_tiles);
+      const int type = MODE == MODE_MSG ? __ldg(p.tile_type + t) : 0;
+      const int key = type * p.S + sl;
+      const int n0 = sl * p.NW;
+      const int nw = min(p.NW, p.Ntot - n0);
+      if (key != cur_key) {
+        tc::named_bar_sync(3, N_EPI_WARPS * 32);
+        for (int j = e256; j < nw; j += N_EPI_WARPS * 32) s_bias[j] = __ldg(p.bias + (size_t)type * p.Ntot + n0 + j);
+        tc::named_bar_sync(3, N_EPI_WARPS * 32);
+        cur_key = key;
+      }
+      const int buf = it & 1;
+      tc::mbar_wait(bar(BAR_ACC_FULL + buf), (it >> 1) & 1);
+      tc::fence_after_sync();
+      const int row0 = t * BM;
+      const int64_t grow = (int64_t)row0 + r;
+      const bool row_ok = MODE == MODE_MSG ? true : grow < p.N;
+      const int ngroups = nw >> 6;
+      for (int g = team; g < ngroups; g += 2) {
+        const int colbase = n0 + g * 64;                   // column in [0, Ntot)
+        const bool is_r = colbase < p.hw;                  // GATES: reset-gate half
+        const int hcol = is_r ? colbase : colbase - p.hw;  // column in [0, hw)
+        uint4 hv[8], uv[8];
+        if (MODE == MODE_GATES) {
+          if (is_r) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              hv[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(p.state16 + grow * p.hw + hcol) + j)
+                             : make_uint4(0u, 0u, 0u, 0u);
+          }
+        } else if (MODE == MODE_CAND) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            hv[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(p.state16 + grow * p.hw + hcol) + j)
+                           : make_uint4(0u, 0u, 0u, 0u);
+            uv[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(p.u16 + grow * p.hw + hcol) + j)
+                           : make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+        if (leader) tc::tma_store_wait_read();             // the team's box is free again
+        tc::named_bar_sync(1 + team, 128);
+#pragma unroll
+        for (int c16 = 0; c16 < 4; ++c16) {
+          uint32_t acc[16];
+          tc::tmem_ld16(t_lane + buf * MAX_NW + g * 64 + c16 * 16, acc);
+          tc::tmem_ld_wait();
+          const float* sb = s_bias + g * 64 + c16 * 16;
+          float o[16];
+          if (MODE == MODE_MSG) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) o[k] = __uint_as_float(acc[k]) + sb[k];
+          } else if (MODE == MODE_GATES) {
+            float hh[16];
+            if (is_r) { unpack8(hv[2 * c16], hh); unpack8(hv[2 * c16 + 1], hh + 8); }
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+              const float gate = tc::rcp_approx(1.0f + tc::ex2_approx(-kLog2e * (__uint_as_float(acc[k]) + sb[k])));
+              o[k] = is_r ? gate * hh[k] : gate;
+            }
+          } else {
+            float hh[16], uu[16];
+            unpack8(hv[2 * c16], hh); unpack8(hv[2 * c16 + 1], hh + 8);
+            unpack8(uv[2 * c16], uu); unpack8(uv[2 * c16 + 1], uu + 8);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+              const float cand = fmaf(-2.0f, tc::rcp_approx(1.0f + tc::ex2_approx(
+                                                 2.0f * kLog2e * (__uint_as_float(acc[k]) + sb[k]))), 1.0f);
+              o[k] = fmaf(uu[k], hh[k] - cand, cand);
+            }
+            if (p.h_out && row_ok) {
+              float* dst = p.h_out + grow * p.h + hcol + c16 * 16;
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4)
+                if (hcol + c16 * 16 + k4 * 4 < p.h)
+                  *reinterpret_cast<float4*>(dst + k4 * 4) = make_float4(o[k4 * 4], o[k4 * 4 + 1], o[k4 * 4 + 2], o[k4 * 4 + 3]);
+            }
+          }
+          *reinterpret_cast<uint4*>(box + sw_off(r, 2 * c16)) = pack8(o);
+          *reinterpret_cast<uint4*>(box + sw_off(r, 2 * c16 + 1)) = pack8(o + 8);
+        }
+        tc::fence_proxy_async();
+        tc::named_bar_sync(1 + team, 128);
+        if (leader) {
+          if (MODE == MODE_GATES && !is_r) tc::tma_store_2d(&tmO1, hcol, row0, box_addr);
+          else tc::tma_store_2d(&tmO0, hcol, row0, box_addr);
+          tc::tma_store_commit();
+        }
+      }
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(bar(BAR_ACC_EMPTY + buf));
+    }
+    if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem_base, 512);
+}
+
+// ---- packing ------------------------------------------------------------------------------
+// dst[e][n][k] (n, k < hw) = f16(src[e][k][n]) for k, n < h, else 0
+__global__ void pack_edge_kernel(const float* __restrict__ W, __half* __restrict__ Wt, int two_e, int h, int hw) {
+  const int64_t total = (int64_t)two_e * hw * hw;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % hw), n = (int)((i / hw) % hw);
+    const int64_t e = i / ((int64_t)hw * hw);
+    Wt[i] = __float2half_rn((k < h && n < h) ? W[(e * h + k) * h + n] : 0.f);
+  }
+}
+// src [2h, ncols*h] -> dst [ncols*hw, 2hw]: dst[nb*hw+n][kb*hw+k] = f16(src[kb*h+k][nb*h+n])
+__global__ void pack_gru_kernel(const float* __restrict__ src, __half* __restrict__ dst, int ncols, int h, int hw) {
+  const int Kp = 2 * hw, Np = ncols * hw;
+  const int64_t total = (int64_t)Np * Kp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % Kp), nn = (int)(i / Kp);
+    const int kb = kk / hw, k = kk % hw, nb = nn / hw, n = nn % hw;
+    dst[i] = __float2half_rn((k < h && n < h) ? src[(size_t)(kb * h + k) * (ncols * h) + nb * h + n] : 0.f);
+  }
+}
+// dst[b][n] (n < hw) = src[b][n] (n < h) else 0; src null -> zeros
+__global__ void pad_bias_kernel(const float* __restrict__ src, float* __restrict__ dst, int nblocks, int h, int hw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nblocks * hw) return;
+  const int nb = i / hw, n = i % hw;
+  dst[i] = (src && n < h) ? src[(size_t)nb * h + n] : 0.f;
+}
+// state16[n][c] = f16(h[n][c]) (c < h) or 0; one thread per 4 columns; max|h| -> *absmax (float bits)
+__global__ void state_in_kernel(const float* __restrict__ hs, __half* __restrict__ s16, int64_t N, int h, int hw,
+                                unsigned* __restrict__ absmax) {
+  const int q = hw / 4;
+  const int64_t total = N * q;
+  float m = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / q;
+    const int c = (int)(i % q) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < h) v = *reinterpret_cast<const float4*>(hs + n * h + c);
+    m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+    __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo); pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(s16 + n * hw + c) = pk;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (absmax && (threadIdx.x & 31) == 0 && m > 0.f) atomicMax(absmax, __float_as_uint(m));
+}
+
+// ---- aggregation: x[n, :] = sum of the FP16 message rows of node n (fixed order), FP32 sum -> FP16 ----
+__global__ void __launch_bounds__(256)
+aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg, const __half* __restrict__ msg,
+                 __half* __restrict__ acts, int64_t N, int hw) {
+  const int lane = threadIdx.x & 31;
+  const int64_t node = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (node >= N) return;
+  const int j0 = tptr[node], j1 = tptr[node + 1];
+  const int h8 = hw >> 3;
+  for (int c = lane; c < h8; c += 32) {
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    int j = j0;
+    for (; j + 4 <= j1; j += 4) {
+      const int r0 = __ldg(tmsg + j), r1 = __ldg(tmsg + j + 1), r2 = __ldg(tmsg + j + 2), r3 = __ldg(tmsg + j + 3);
+      const uint4 m0 = __ldg(reinterpret_cast<const uint4*>(msg + (size_t)r0 * hw) + c);
+      const uint4 m1 = __ldg(reinterpret_cast<const uint4*>(msg + (size_t)r1 * hw) + c);
+      const uint4 m2 = __ldg(reinterpret_cast<const uint4*>(msg + (size_t)r2 * hw) + c);
+      const uint4 m3 = __ldg(reinterpret_cast<const uint4*>(msg + (size_t)r3 * hw) + c);
+      float f[8];
+      unpack8(m0, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      unpack8(m1, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      unpack8(m2, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      unpack8(m3, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+    for (; j < j1; ++j) {
+      const int r0 = __ldg(tmsg + j);
+      float f[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(msg + (size_t)r0 * hw) + c), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+    reinterpret_cast<uint4*>(acts + (size_t)node * hw)[c] = pack8(acc);
+  }
+}
+
+// slice width: the widest multiple of 64 (<= 256) whose [NW x K] FP16 panel fits the resident 128 KB
+int slice_width(int K, int Ntot) {
+  int nw = (W_BYTES / (K * 2)) / 64 * 64;
+  if (nw > MAX_NW) nw = MAX_NW;
+  if (nw > Ntot) nw = Ntot;
+  return nw;
+}
+
+template <int MODE>
+int launch(ggnn_ctx* ctx, const params& p, const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w,
+           const CUtensorMap& o0, const CUtensorMap& o1, int64_t max_items, cudaStream_t st) {
+  GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_W16_0 + MODE, wgemm16_kernel<MODE>, SMEM_BYTES);
+  const int grid = (int)(max_items < ctx->sm_count ? max_items : ctx->sm_count);
+  if (grid <= 0) return GGNN_OK;
+  wgemm16_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(p, a1, a2, w, o0, o1);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+}  // namespace w16
+
+// =========================================================================================
+bool ggnn_w16_supported(const ggnn_ctx* ctx) {
+  return ctx->h > 128 && ctx->h % 4 == 0 && ctx->hw16 >= 192 && ctx->hw16 <= 512;
+}
+
+static int realloc_bytes(ggnn_ctx* ctx, void*& p, size_t bytes) {
+  if (p && ctx->repack_in_place) return GGNN_OK;
+  if (p) { cudaFree(p); p = nullptr; }
+  GGNN_CUDA(ctx, cudaMalloc(&p, bytes));
+  return GGNN_OK;
+}
+
+int ggnn_w16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st) {
+  if (!ggnn_w16_supported(ctx)) return GGNN_OK;
+  const int h = ctx->h, hw = ctx->hw16, two_e = ctx->two_e;
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  ew.absmax_w = -1.f;
+  GGNN_TRY(realloc_bytes(ctx, ew.Wt_f16, (size_t)two_e * hw * hw * 2));
+  w16::pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, reinterpret_cast<__half*>(ew.Wt_f16), two_e, h, hw);
+  GGNN_LAUNCHED(ctx);
+  void* bp = ew.B_pad16;
+  GGNN_TRY(realloc_bytes(ctx, bp, (size_t)two_e * hw * 4));
+  ew.B_pad16 = reinterpret_cast<float*>(bp);
+  w16::pad_bias_kernel<<<(two_e * hw + 255) / 256, 256, 0, st>>>(ew.B, ew.B_pad16, two_e, h, hw);
+  GGNN_LAUNCHED(ctx);
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ew.tm_Wt16, ew.Wt_f16, (int64_t)two_e * hw, hw, w16::BKH,
+                                 w16::slice_width(hw, hw)));
+  if (with_gru) {
+    GGNN_TRY(realloc_bytes(ctx, ctx->Wgt_f16, (size_t)4 * hw * hw * 2));
+    GGNN_TRY(realloc_bytes(ctx, ctx->Wct_f16, (size_t)2 * hw * hw * 2));
+    w16::pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, reinterpret_cast<__half*>(ctx->Wgt_f16), 2, h, hw);
+    GGNN_LAUNCHED(ctx);
+    w16::pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, reinterpret_cast<__half*>(ctx->Wct_f16), 1, h, hw);
+    GGNN_LAUNCHED(ctx);
+    void* g = ctx->bg_w16; void* c = ctx->bc_w16;
+    GGNN_TRY(realloc_bytes(ctx, g, (size_t)2 * hw * 4));
+    GGNN_TRY(realloc_bytes(ctx, c, (size_t)hw * 4));
+    ctx->bg_w16 = reinterpret_cast<float*>(g); ctx->bc_w16 = reinterpret_cast<float*>(c);
+    w16::pad_bias_kernel<<<(2 * hw + 255) / 256, 256, 0, st>>>(ctx->bg, ctx->bg_w16, 2, h, hw);
+    GGNN_LAUNCHED(ctx);
+    w16::pad_bias_kernel<<<(hw + 255) / 256, 256, 0, st>>>(ctx->bc, ctx->bc_w16, 1, h, hw);
+    GGNN_LAUNCHED(ctx);
+    GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wg16, ctx->Wgt_f16, 2 * hw, 2 * hw, w16::BKH,
+                                   w16::slice_width(2 * hw, 2 * hw)));
+    GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16, ctx->Wct_f16, hw, 2 * hw, w16::BKH,
+                                   w16::slice_width(2 * hw, hw)));
+  }
+  return GGNN_OK;
+}
+
+int ggnn_w16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, unsigned* absmax_bits,
+                      cudaStream_t st) {
+  if (N == 0) return GGNN_OK;
+  prof_scope ps(ctx, GGNN_STAGE_OTHER, st);
+  w16::state_in_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(h, reinterpret_cast<__half*>(state16), N, ctx->h,
+                                                           ctx->hw16, absmax_bits);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
+// One timestep.  Scratch (all FP16, pitch hw): msg16 [max_tiles*128], acts16 / rh16 / u16 [N]; state16 [N] in/out.
+int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* acts16, void* rh16, void* u16,
+                  void* state16, float* h_out, bool last_step, cudaStream_t st) {
+  using namespace w16;
+  if (plan.N == 0) return GGNN_OK;
+  const int h = ctx->h, hw = ctx->hw16;
+  const ggnn_edge_weights& ew = ctx->edge[slot];
+  const int n_row_tiles = (int)ceil_div64(plan.N, BM);
+  CUtensorMap tmState, tmActs, tmRh, tmU, tmMsg;
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmState, state16, plan.N, hw, BKH, BM));
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmActs, acts16, plan.N, hw, BKH, BM));
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmRh, rh16, plan.N, hw, BKH, BM));
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmU, u16, plan.N, hw, BKH, BM));
+  if (plan.max_tiles > 0 && plan.nnz > 0) {
+    GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmMsg, msg16, plan.max_tiles * (int64_t)BM, hw, BKH, BM));
+    params p{};
+    p.A_gather = reinterpret_cast<const __half*>(state16);
+    if (plan.dense_rows) { p.gather = nullptr; p.tiles_per_type = n_row_tiles; }
+    else { p.gather = plan.msg_src; p.tiles_per_type = 1; }
+    p.tile_type = plan.tile_type; p.n_tiles_dev = plan.n_tiles;
+    p.KC = hw / BKH; p.KC1 = p.KC;
+    p.Ntot = hw; p.NW = slice_width(hw, hw); p.S = (hw + p.NW - 1) / p.NW;
+    p.bias = ew.B_pad16; p.hw = hw; p.h = h; p.N = plan.N;
+    prof_scope ps(ctx, GGNN_STAGE_MSG, st);
+    GGNN_TRY(launch<MODE_MSG>(ctx, p, tmState, tmState, ew.tm_Wt16, tmMsg, tmMsg, plan.max_tiles * p.S, st));
+  }
+  {
+    prof_scope ps(ctx, GGNN_STAGE_AGG, st);
+    const int64_t threads = plan.N * 32;
+    aggregate_kernel<<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(
+        plan.tptr, plan.tmsg, reinterpret_cast<const __half*>(msg16), reinterpret_cast<__half*>(acts16), plan.N, hw);
+    GGNN_LAUNCHED(ctx);
+  }
+  {
+    params p{};
+    p.n_tiles = n_row_tiles;
+    p.KC = 2 * hw / BKH; p.KC1 = hw / BKH;
+    p.Ntot = 2 * hw; p.NW = slice_width(2 * hw, 2 * hw); p.S = (p.Ntot + p.NW - 1) / p.NW;
+    p.bias = ctx->bg_w16; p.hw = hw; p.h = h; p.N = plan.N;
+    p.state16 = reinterpret_cast<const __half*>(state16);
+    prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+    GGNN_TRY(launch<MODE_GATES>(ctx, p, tmActs, tmState, ctx->tm_Wg16, tmRh, tmU, (int64_t)n_row_tiles * p.S, st));
+  }
+  {
+    params p{};
+    p.n_tiles = n_row_tiles;
+    p.KC = 2 * hw / BKH; p.KC1 = hw / BKH;
+    p.Ntot = hw; p.NW = slice_width(2 * hw, hw); p.S = (p.Ntot + p.NW - 1) / p.NW;
+    p.bias = ctx->bc_w16; p.hw = hw; p.h = h; p.N = plan.N;
+    p.state16 = reinterpret_cast<const __half*>(state16);
+    p.u16 = reinterpret_cast<const __half*>(u16);
+    p.h_out = last_step ? h_out : nullptr;
+    prof_scope ps(ctx, GGNN_STAGE_GRU_CAND, st);
+    GGNN_TRY(launch<MODE_CAND>(ctx, p, tmActs, tmRh, ctx->tm_Wc16, tmState, tmState, (int64_t)n_row_tiles * p.S, st));
+  }
+  return GGNN_OK;
+}

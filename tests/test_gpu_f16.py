@@ -44,6 +44,79 @@ def test_random_trees(b, v, E, h, T):
     assert err <= TOL, err
 
 
+@pytest.mark.parametrize("b,v,E,h,T", [(4, 32, 10, 256, 4), (3, 20, 6, 400, 4), (5, 16, 6, 132, 2), (2, 130, 12, 192, 3),
+                                       (6, 40, 46, 320, 4), (3, 24, 5, 512, 2), (40, 64, 46, 400, 4)])
+def test_wide_hidden_sizes(b, v, E, h, T):
+    """h > 128 (wide16.cu): FP16 buffers of pitch ceil64(h), resident weight panels of 64..256 columns; covers one and
+    several column slices, narrower last slices (h = 320: 192 + 128), K segments of 3..8 chunks, padded columns."""
+    _, adj = _trees(b, v, E, seed=b + v)
+    w = O.make_weights(2 * E, h, 0)
+    h0 = _h0(b, v, h)
+    out = ggnn_b200.compute_final_node_representations(h0, adj, weights=w, num_timesteps=T, precision="f16")
+    err = O.normwise_err(out, O.propagate_dense(h0, adj, w, T))
+    assert err <= TOL, err
+
+
+def test_wide_edge_list_paths_and_golden(golden_dir):
+    """h = 256 through the edge-list form: gathered rows (nnz < N*2E) and the dense-row plan (rows by TMA), no bias,
+    fixed_ts weights; bit-identical between the dense and the edge-list route; reproducible."""
+    n, nodes, types, h = 2, 300, 4, 256
+    h0 = np.random.default_rng(0).uniform(-0.1, 0.1, (n * nodes, h)).astype(np.float32)
+    for base, scale in ((600, 1.0), (2400, 0.25)):      # in-degree 4 / 16 (scaled like test_sparse_large_graph_dense_mode)
+        edges = synth.random_multigraph(n, nodes, base, types, seed=3)
+        w = O.make_weights(2 * types, h, 0)
+        w["edge_weights"] = w["edge_weights"] * scale
+        out = ggnn_b200.compute_final_node_representations_sparse(h0, edges.numpy(), weights=w, num_timesteps=4,
+                                                                  precision="f16")
+        assert O.normwise_err(out, O.propagate_edges(h0, edges.numpy(), w, 4)) <= TOL
+        again = ggnn_b200.compute_final_node_representations_sparse(h0, edges.numpy(), weights=w, num_timesteps=4,
+                                                                    precision="f16")
+        assert np.array_equal(out, again)
+    tri, adj = _trees(6, 32, 8, seed=4, lengths=torch.tensor([31, 2, 1, 17, 9, 30]))
+    w = O.make_weights(16, 256, 2)
+    w2 = O.make_weights(16, 256, 102)
+    w["edge_weights_fixed"], w["edge_biases_fixed"] = w2["edge_weights"], w2["edge_biases"]
+    hd = _h0(6, 32, 256)
+    out1 = ggnn_b200.compute_final_node_representations(hd, adj, weights=w, fixed_ts=2, precision="f16")
+    assert O.normwise_err(out1, O.propagate_dense(hd, adj, w, 2, fixed_ts=2)) <= TOL
+    prop = Propagator(W.from_dict(w), "cuda:0")
+    d_h0, d_adj = torch.from_numpy(hd).cuda(), torch.from_numpy(adj).cuda()
+    dense = prop.propagate_dense(d_h0, d_adj, num_timesteps=3, precision="f16")
+    edges = synth.global_edge_list(tri, 32, 8).cuda()
+    sp = prop.propagate_edges(d_h0.view(-1, 256), edges, num_timesteps=3, precision="f16").view(6, 32, 256)
+    assert torch.equal(dense, sp)
+    wn = O.make_weights(6, 200, 1)
+    wn.pop("edge_biases")
+    adjg = (np.random.default_rng(5).random((3, 6, 20, 20)) < 0.15).astype(np.float32)
+    hg = _h0(3, 20, 200)
+    og = ggnn_b200.compute_final_node_representations(hg, adjg, weights=wn, num_timesteps=3, precision="f16")
+    assert O.normwise_err(og, O.propagate_dense(hg, adjg, wn, 3, use_bias=False)) <= TOL
+    o0 = ggnn_b200.compute_final_node_representations(hg, adjg, weights=wn, num_timesteps=0, precision="f16")
+    assert np.array_equal(o0, hg)
+
+
+def test_wide_large_batch_independence():
+    """C4-sized tiles at h = 256: a graph computed inside a large batch is bit-identical to the same graph alone
+    (tile / slice / CTA placement must not matter)."""
+    n, nodes, base, types, h, T = 24, 4096, 32768, 4, 256, 3
+    w = O.make_weights(2 * types, h, 0)
+    w["edge_weights"] = w["edge_weights"] * 0.25
+    prop = Propagator(W.from_dict(w), "cuda:0")
+    edges = synth.random_multigraph(n, nodes, base, types, seed=9).cuda()
+    h0 = (torch.rand(n * nodes, h, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5)) - 0.5) * 0.2
+    big = prop.propagate_edges(h0, edges, num_timesteps=T, precision="f16")
+    assert bool(torch.isfinite(big).all())
+    per = 2 * base
+    for g in (0, 13, 23):
+        eg = edges[g * per:(g + 1) * per].clone()
+        eg[:, 0] -= g * nodes
+        eg[:, 2] -= g * nodes
+        one = prop.propagate_edges(h0[g * nodes:(g + 1) * nodes].contiguous(), eg, num_timesteps=T, precision="f16")
+        assert torch.equal(one, big[g * nodes:(g + 1) * nodes])
+    ref = O.propagate_edges(h0[:nodes].cpu().numpy(), edges[:per].cpu().numpy(), w, T)
+    assert O.normwise_err(big[:nodes].cpu().numpy(), ref) <= TOL
+
+
 def test_matches_tf32_mode_closely_and_is_reproducible():
     """Same 11-bit operand significand as TF32: the two modes agree far inside the tolerance."""
     _, adj = _trees(16, 64, 20, seed=3)
