@@ -449,6 +449,7 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
   // chunk so that canonical rows stay well inside int32 and scratch stays bounded
   const int64_t rows_per_graph = (int64_t)two_e * v;
   int64_t chunk = ((int64_t)1 << 26) / rows_per_graph;
+  if (const char* e = getenv("GGNN_CHUNK")) { const int64_t c = atoll(e); if (c > 0 && c < chunk) chunk = c; }   // A-B switch
   if (chunk < 1) chunk = 1;
   if (chunk >= 16) chunk &= ~(int64_t)15;     // chunk starts stay 16-byte aligned for any v, 2E and adjacency dtype
   if (chunk > b) chunk = b;

@@ -249,24 +249,22 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
         cur_key = key;
       }
       const int buf = it & 1;
-      tc::mbar_wait(bar(BAR_ACC_FULL + buf), (it >> 1) & 1);
-      tc::fence_after_sync();
       const int row0 = t * BM;
       const int64_t grow = (int64_t)row0 + r;
       const bool row_ok = MODE == MODE_MSG ? true : grow < p.N;
       const int ngroups = nw >> 6;
-      for (int g = team; g < ngroups; g += 2) {
-        const int colbase = n0 + g * 64;                   // column in [0, Ntot)
-        const bool is_r = colbase < p.hw;                  // GATES: reset-gate half
-        const int hcol = is_r ? colbase : colbase - p.hw;  // column in [0, hw)
-        uint4 hv[8], uv[8];
-        if (MODE == MODE_GATES) {
-          if (is_r) {
+      // GATES / CAND: this row's h (and u) values of a 64-column group; the first group's are requested BEFORE the
+      // accumulator wait so their latency is not part of the per-item epilogue chain
+      uint4 hv[8], uv[8];
+      auto fetch = [&](int g) {
+        const int colbase = n0 + g * 64;
+        const bool is_r = colbase < p.hw;
+        const int hcol = is_r ? colbase : colbase - p.hw;
+        if (MODE == MODE_GATES && is_r) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              hv[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(p.state16 + grow * p.hw + hcol) + j)
-                             : make_uint4(0u, 0u, 0u, 0u);
-          }
+          for (int j = 0; j < 8; ++j)
+            hv[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(p.state16 + grow * p.hw + hcol) + j)
+                           : make_uint4(0u, 0u, 0u, 0u);
         } else if (MODE == MODE_CAND) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -276,6 +274,15 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
                            : make_uint4(0u, 0u, 0u, 0u);
           }
         }
+      };
+      if (team < ngroups) fetch(team);
+      tc::mbar_wait(bar(BAR_ACC_FULL + buf), (it >> 1) & 1);
+      tc::fence_after_sync();
+      for (int g = team; g < ngroups; g += 2) {
+        const int colbase = n0 + g * 64;                   // column in [0, Ntot)
+        const bool is_r = colbase < p.hw;                  // GATES: reset-gate half
+        const int hcol = is_r ? colbase : colbase - p.hw;  // column in [0, hw)
+        if (g != team) fetch(g);
         if (leader) tc::tma_store_wait_read();             // the team's box is free again
         tc::named_bar_sync(1 + team, 128);
 #pragma unroll

@@ -47,7 +47,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--data"); ap.add_argument("--restore")
     ap.add_argument("--sentences", type=int, default=2416)
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "f16"])
     ap.add_argument("--feed", default="edges", choices=["edges", "dense"])
     ap.add_argument("--check", type=int, default=0, help="also run the CPU oracle on this many sentences")
     ap.add_argument("--batch", type=int, default=20, help="sentences per batch within a bucket (reference: 20)")
