@@ -460,6 +460,297 @@ int launch(ggnn_ctx* ctx, const params& p, const CUtensorMap& a1, const CUtensor
 }  // namespace w16
 
 // =========================================================================================
+// GRU cell of a 128-node tile in ONE persistent kernel, hw <= 256 (the wide twin of f16.cu's gru_f16_kernel, without
+// the aggregation): x and h tiles resident in shared memory, the 6 hw^2 FP16 weights streamed from L2 through a
+// 3-slot ring of [hw n x 64 k] chunks, gates in TMEM.  r, u, r*h and the candidate never touch HBM:
+// per timestep the unfused GATES + CAND kernels move 9 node-state-sized arrays through HBM, this one 3
+// (x and h in, h' out).
+//   MMA order   u_x, u_h, r_h | r_x | cand_x, cand_rh          (u: TMEM columns 256.., r and cand: columns 0..)
+//   EPI-u       after u_h / r_h retire: u = sigmoid(.), packed with the row's h as (f16 u, f16 h) into u's own TMEM
+//               words -- h survives there while the h tile becomes r*h
+//   EPI-r       after r_x: r = sigmoid(.), f16(r*h) overwrites the h tile (the K operand of cand_rh)
+//   EPI-c       c = tanh(.), h' = c + u (h - c) -> FP16 into the (dead) x tile -> TMA store; FP32 result on the last step
+namespace gw16 {
+using namespace w16;
+
+constexpr int WSLOT = 32 * 1024;                 // one [256 n x 64 k] FP16 chunk
+constexpr int WSLOTS = 3;
+constexpr int TILE_BYTES = 4 * CHUNK;            // 64 KB: [128 x 256] FP16 as four swizzled 64-column chunks
+constexpr int WARP_TMA = 8, WARP_MMA = 9;        // warps 0-7: epilogue (lane quarter = warp % 4, column half = warp / 4)
+constexpr int NTHREADS = 10 * 32;
+constexpr int SMEM_BYTES = 2 * TILE_BYTES + WSLOTS * WSLOT + 1024 /*align*/ + 256 /*barriers*/;
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+
+enum {
+  BAR_W_FULL = 0,                     // [WSLOTS]
+  BAR_W_EMPTY = BAR_W_FULL + WSLOTS,  // [WSLOTS]
+  BAR_X_FULL = BAR_W_EMPTY + WSLOTS,
+  BAR_H_FULL,
+  BAR_X_EMPTY,                        // h' of the previous tile has left the x tile (leader, after the store has read it)
+  BAR_U_DONE,                         // u complete, every MMA reading the h tile retired
+  BAR_R_DONE,
+  BAR_RH_FULL,                        // 8 epilogue warps: r drained from TMEM, r*h in the h tile
+  BAR_C_DONE,                         // candidate complete (h tile free)
+  BAR_TMEM_FREE,                      // 8 epilogue warps: c and (u, h) read
+  BAR_COUNT
+};
+static_assert(8 * BAR_COUNT + 8 <= 256, "barrier area");
+
+struct params {
+  const float* bg;          // [2 hw] zero-padded
+  const float* bc;          // [hw]
+  float* h_out;             // [N, h] FP32 result (last step) or null
+  int64_t N;
+  int h, hw, n_tiles;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+gru_w16_kernel(const params p, const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmH,
+               const __grid_constant__ CUtensorMap tmWg, const __grid_constant__ CUtensorMap tmWc) {
+  extern __shared__ uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (base - tc::smem_u32(smem_raw));
+  const uint32_t sX = base, sH = base + TILE_BYTES, sW = sH + TILE_BYTES;
+  const uint32_t bars = sW + WSLOTS * WSLOT;
+  auto bar = [&](int i) { return bars + 8u * i; };
+  const uint32_t tmem_slot = bars + 8u * BAR_COUNT;
+  const int hw = p.hw, KC1 = hw / BKH;
+  const uint32_t wbytes = (uint32_t)hw * 128u;             // bytes one weight chunk delivers
+
+  if (warp == WARP_MMA && lane == 0) {
+    for (int s = 0; s < WSLOTS; ++s) { tc::mbar_init(bar(BAR_W_FULL + s), 1); tc::mbar_init(bar(BAR_W_EMPTY + s), 1); }
+    tc::mbar_init(bar(BAR_X_FULL), 1);
+    tc::mbar_init(bar(BAR_H_FULL), 1);
+    tc::mbar_init(bar(BAR_X_EMPTY), 1);
+    tc::mbar_init(bar(BAR_U_DONE), 1);
+    tc::mbar_init(bar(BAR_R_DONE), 1);
+    tc::mbar_init(bar(BAR_RH_FULL), 8);
+    tc::mbar_init(bar(BAR_C_DONE), 1);
+    tc::mbar_init(bar(BAR_TMEM_FREE), 8);
+    tc::fence_barrier_init();
+  }
+  if (warp == WARP_TMA) {
+    if (lane == 0) {
+      tc::tma_prefetch_desc(&tmX); tc::tma_prefetch_desc(&tmH); tc::tma_prefetch_desc(&tmWg); tc::tma_prefetch_desc(&tmWc);
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, 512);
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
+
+  if (warp == WARP_TMA) {
+    // =============================== TMA producer ===============================
+    if (lane == 0) {
+      uint32_t fill = 0;
+      auto w_fill = [&](const CUtensorMap* tm, int kcol, int nrow) {
+        const int s = fill % WSLOTS;
+        if (fill >= WSLOTS) tc::mbar_wait(bar(BAR_W_EMPTY + s), ((fill / WSLOTS) - 1) & 1);
+        tc::mbar_arrive_expect_tx(bar(BAR_W_FULL + s), wbytes);
+        tc::tma_load_2d(sW + s * WSLOT, tm, kcol, nrow, bar(BAR_W_FULL + s));
+        ++fill;
+      };
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        // the first ring-full of weights does not depend on the tiles being free
+        int issued = 0;
+        auto tiles_in = [&]() {
+          if (it > 0) {
+            tc::mbar_wait(bar(BAR_X_EMPTY), (it - 1) & 1);
+            tc::mbar_wait(bar(BAR_C_DONE), (it - 1) & 1);
+          }
+          tc::mbar_arrive_expect_tx(bar(BAR_X_FULL), (uint32_t)KC1 * CHUNK);
+          for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d(sX + kc * CHUNK, &tmX, kc * BKH, tile * BM, bar(BAR_X_FULL));
+          tc::mbar_arrive_expect_tx(bar(BAR_H_FULL), (uint32_t)KC1 * CHUNK);
+          for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d(sH + kc * CHUNK, &tmH, kc * BKH, tile * BM, bar(BAR_H_FULL));
+        };
+        auto step = [&](const CUtensorMap* tm, int kcol, int nrow) {
+          w_fill(tm, kcol, nrow);
+          if (++issued == WSLOTS) tiles_in();
+        };
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, hw);               // x   -> u
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, hw + kc * BKH, hw);          // h   -> u
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, hw + kc * BKH, 0);           // h   -> r
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, 0);                // x   -> r
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWc, kc * BKH, 0);                // x   -> cand
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWc, hw + kc * BKH, 0);           // r*h -> cand
+      }
+    }
+    __syncwarp();
+  } else if (warp == WARP_MMA) {
+    // =============================== MMA issuer ===============================
+    if (lane == 0) {
+      const uint32_t idesc = tc::umma_idesc(0 /*F16*/, BM, hw);
+      const uint32_t d_rc = tmem_base, d_u = tmem_base + 256;
+      uint32_t use = 0;
+      auto chunk_mma = [&](uint32_t d, uint32_t a, bool first) {
+        const int s = use % WSLOTS;
+        tc::mbar_wait(bar(BAR_W_FULL + s), (use / WSLOTS) & 1);
+        tc::fence_after_sync();
+        const uint32_t w = sW + s * WSLOT;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          tc::umma_f16(d, tc::umma_desc_sw128(a + k * 32), tc::umma_desc_sw128(w + k * 32), idesc, (first && k == 0) ? 0u : 1u);
+        tc::umma_commit(bar(BAR_W_EMPTY + s));
+        ++use;
+      };
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        if (it > 0) tc::mbar_wait(bar(BAR_TMEM_FREE), (it - 1) & 1);
+        tc::mbar_wait(bar(BAR_X_FULL), it & 1);
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sX + kc * CHUNK, kc == 0);      // x -> u
+        tc::mbar_wait(bar(BAR_H_FULL), it & 1);
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sH + kc * CHUNK, false);        // h -> u
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sH + kc * CHUNK, kc == 0);     // h -> r
+        tc::umma_commit(bar(BAR_U_DONE));
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sX + kc * CHUNK, false);       // x -> r
+        tc::umma_commit(bar(BAR_R_DONE));
+        tc::mbar_wait(bar(BAR_RH_FULL), it & 1);                                        // r drained, r*h in the h tile
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sX + kc * CHUNK, kc == 0);     // x -> cand
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sH + kc * CHUNK, false);       // r*h -> cand
+        tc::umma_commit(bar(BAR_C_DONE));
+      }
+    }
+    __syncwarp();
+  } else {
+    // =============================== epilogue (warps 0-7) ===============================
+    const int q = warp & 3, half = warp >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int ng = hw / 16;                                   // 16-column groups
+    const int g_begin = half * (ng / 2), g_end = half ? ng : ng / 2;
+    uint8_t* xt = smem_al + (sX - base);
+    uint8_t* ht = smem_al + (sH - base);
+    const bool leader = tid == 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+      const int64_t grow = (int64_t)tile * BM + r;
+      // ---- EPI-u
+      tc::mbar_wait(bar(BAR_U_DONE), it & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int g = g_begin; g < g_end; ++g) {
+        const int col0 = g * 16;
+        uint32_t au[16];
+        tc::tmem_ld16(t_lane + 256 + col0, au);
+        const uint8_t* hp = ht + (col0 >> 6) * CHUNK;
+        const int s0 = (col0 & 63) >> 3;
+        const uint4 h0 = *reinterpret_cast<const uint4*>(hp + sw_off(r, s0));
+        const uint4 h1 = *reinterpret_cast<const uint4*>(hp + sw_off(r, s0 + 1));
+        const uint32_t hb[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        float sb[16];
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bg + hw + col0) + k4);
+          sb[4 * k4] = b4.x; sb[4 * k4 + 1] = b4.y; sb[4 * k4 + 2] = b4.z; sb[4 * k4 + 3] = b4.w;
+        }
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float u = tc::rcp_approx(1.0f + tc::ex2_approx(-kLog2e * (__uint_as_float(au[k]) + sb[k])));
+          const uint32_t hbits = (k & 1) ? (hb[k >> 1] >> 16) : (hb[k >> 1] & 0xffffu);
+          au[k] = (uint32_t)__half_as_ushort(__float2half_rn(u)) | (hbits << 16);     // (f16 u, f16 h)
+        }
+        tc::tmem_st16(t_lane + 256 + col0, au);
+      }
+      tc::tmem_st_wait();
+      // ---- EPI-r: f16(r*h) replaces h in shared memory
+      tc::mbar_wait(bar(BAR_R_DONE), it & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int g = g_begin; g < g_end; ++g) {
+        const int col0 = g * 16;
+        uint32_t ar[16];
+        tc::tmem_ld16(t_lane + col0, ar);
+        uint8_t* hp = ht + (col0 >> 6) * CHUNK;
+        const int s0 = (col0 & 63) >> 3;
+        uint4* p0 = reinterpret_cast<uint4*>(hp + sw_off(r, s0));
+        uint4* p1 = reinterpret_cast<uint4*>(hp + sw_off(r, s0 + 1));
+        float hh[16];
+        unpack8(*p0, hh); unpack8(*p1, hh + 8);
+        float sb[16];
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bg + col0) + k4);
+          sb[4 * k4] = b4.x; sb[4 * k4 + 1] = b4.y; sb[4 * k4 + 2] = b4.z; sb[4 * k4 + 3] = b4.w;
+        }
+        tc::tmem_ld_wait();
+        float o[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          o[k] = tc::rcp_approx(1.0f + tc::ex2_approx(-kLog2e * (__uint_as_float(ar[k]) + sb[k]))) * hh[k];
+        *p0 = pack8(o);
+        *p1 = pack8(o + 8);
+      }
+      tc::fence_before_sync();
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(bar(BAR_RH_FULL));
+      // ---- EPI-c: candidate and the new state
+      tc::mbar_wait(bar(BAR_C_DONE), it & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int g = g_begin; g < g_end; ++g) {
+        const int col0 = g * 16;
+        uint32_t ac[16], uh[16];
+        tc::tmem_ld16(t_lane + col0, ac);
+        tc::tmem_ld16(t_lane + 256 + col0, uh);
+        float sb[16];
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bc + col0) + k4);
+          sb[4 * k4] = b4.x; sb[4 * k4 + 1] = b4.y; sb[4 * k4 + 2] = b4.z; sb[4 * k4 + 3] = b4.w;
+        }
+        tc::tmem_ld_wait();
+        float o[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float c = fmaf(-2.0f, tc::rcp_approx(1.0f + tc::ex2_approx(2.0f * kLog2e * (__uint_as_float(ac[k]) + sb[k]))), 1.0f);
+          const float u = __half2float(__ushort_as_half((unsigned short)(uh[k] & 0xffffu)));
+          const float hv = __half2float(__ushort_as_half((unsigned short)(uh[k] >> 16)));
+          o[k] = fmaf(u, hv - c, c);
+        }
+        uint8_t* xp = xt + (col0 >> 6) * CHUNK;
+        const int s0 = (col0 & 63) >> 3;
+        *reinterpret_cast<uint4*>(xp + sw_off(r, s0)) = pack8(o);
+        *reinterpret_cast<uint4*>(xp + sw_off(r, s0 + 1)) = pack8(o + 8);
+        if (p.h_out && grow < p.N) {
+          float* dst = p.h_out + grow * p.h + col0;
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)
+            if (col0 + k4 * 4 < p.h)
+              *reinterpret_cast<float4*>(dst + k4 * 4) = make_float4(o[k4 * 4], o[k4 * 4 + 1], o[k4 * 4 + 2], o[k4 * 4 + 3]);
+        }
+      }
+      tc::fence_before_sync();
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(bar(BAR_TMEM_FREE));
+      tc::named_bar_sync(1, 256);
+      if (leader) {
+        for (int kc = 0; kc < KC1; ++kc) tc::tma_store_2d(&tmH, kc * BKH, tile * BM, sX + kc * CHUNK);   // rows >= N clipped
+        tc::tma_store_commit();
+        tc::tma_store_wait_read();
+        tc::mbar_arrive(bar(BAR_X_EMPTY));
+      }
+    }
+    if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == WARP_TMA) tc::tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace gw16
+
+// =========================================================================================
 bool ggnn_w16_supported(const ggnn_ctx* ctx) {
   return ctx->h > 128 && ctx->h % 4 == 0 && ctx->hw16 >= 192 && ctx->hw16 <= 512;
 }
@@ -505,6 +796,10 @@ int ggnn_w16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t s
                                    w16::slice_width(2 * hw, 2 * hw)));
     GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16, ctx->Wct_f16, hw, 2 * hw, w16::BKH,
                                    w16::slice_width(2 * hw, hw)));
+    if (hw <= 256) {     // fused GRU kernel: [hw n x 64 k] chunks
+      GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wg16f, ctx->Wgt_f16, 2 * hw, 2 * hw, w16::BKH, hw));
+      GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16f, ctx->Wct_f16, hw, 2 * hw, w16::BKH, hw));
+    }
   }
   return GGNN_OK;
 }
@@ -551,6 +846,17 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     aggregate_kernel<<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(
         plan.tptr, plan.tmsg, reinterpret_cast<const __half*>(msg16), reinterpret_cast<__half*>(acts16), plan.N, hw);
     GGNN_LAUNCHED(ctx);
+  }
+  if (hw <= 256 && !ctx->no_fused) {       // GATES + CAND in one kernel, gates and r*h on chip
+    GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_W16_0 + 3, gw16::gru_w16_kernel, gw16::SMEM_BYTES);
+    gw16::params g{};
+    g.bg = ctx->bg_w16; g.bc = ctx->bc_w16; g.h_out = last_step ? h_out : nullptr;
+    g.N = plan.N; g.h = h; g.hw = hw; g.n_tiles = n_row_tiles;
+    const int grid = n_row_tiles < ctx->sm_count ? n_row_tiles : ctx->sm_count;
+    prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+    gw16::gru_w16_kernel<<<grid, gw16::NTHREADS, gw16::SMEM_BYTES, st>>>(g, tmActs, tmState, ctx->tm_Wg16f, ctx->tm_Wc16f);
+    GGNN_LAUNCHED(ctx);
+    return GGNN_OK;
   }
   {
     params p{};
