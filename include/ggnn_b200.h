@@ -57,7 +57,7 @@ extern "C" {
 #define GGNN_PREC_TF32  1   /* tcgen05 kind::tf32, FP32 accumulate, <= 2e-3 norm-wise   */
 #define GGNN_PREC_F16   2   /* tcgen05 kind::f16: operands rounded to FP16 (the same 11-bit significand
                              * as TF32) and held in 16-bit containers, FP32 accumulate, FP32 gate math,
-                             * FP32 result; <= 2e-3 norm-wise.  Hidden size <= 128.  Needs
+                             * FP32 result; <= 2e-3 norm-wise.  Hidden size in (96, 512].  Needs
                              * h*max|W|*max(max|h0|,1) + max|B| < 64 so nothing leaves the FP16 range;
                              * otherwise the call returns GGNN_E_UNSUPPORTED (use GGNN_PREC_TF32).    */
 
