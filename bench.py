@@ -599,6 +599,31 @@ def run_c4(args):
                 "achieved_tflops_algorithmic_per_gpu": flop_graph * per_gpu / (ms_per_step * 1e-3) / 1e12,
                 "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items() if v[0] > 0},
                 "clocks": clocks, "gpu_launches": int(launches)}
+        # per-stage roofline fractions on SURVEY 8(d)'s algorithmic work (per graph-step): W_e GEMM min(nnz, N*2E)*2h^2
+        # flops, GRU N*12h^2 flops, aggregation nnz*h*s_msg + nnz*4 + (N+1)*4 + N*h*4 bytes (s_msg = 2 with 16-bit messages)
+        peaks = load_peaks()
+        sm = line["stages_ms_per_step"]
+        gsteps = per_gpu * Tc
+        tpeak = peaks["bf16_tflops_sustained"] * (0.5 if args.precision == "tf32" else 1.0)
+        def tens(ms, flop):
+            a = flop * gsteps / (ms * 1e-3) / 1e12
+            return {"bound": "tensor", "ms_per_step": ms, "achieved": a, "unit": "TFLOP/s", "peak": tpeak, "frac": a / tpeak}
+        st = {}
+        if args.precision != "fp32":
+            if "msg" in sm:
+                st["msg"] = tens(sm["msg"], min(2 * BASE, Vn * CH) * 2 * Hc * Hc)
+            gru_ms = sm.get("gru_gates", 0.0) + sm.get("gru_cand", 0.0)
+            if gru_ms > 0:
+                st["gru"] = tens(gru_ms, Vn * 12 * Hc * Hc)
+        if "agg" in sm:
+            s_msg = 4 if args.precision == "fp32" else 2
+            by = 2 * BASE * Hc * s_msg + 2 * BASE * 4 + (Vn + 1) * 4 + Vn * Hc * 4
+            a = by * gsteps / (sm["agg"] * 1e-3) / 1e9
+            st["agg"] = {"bound": "hbm", "ms_per_step": sm["agg"], "achieved": a, "unit": "GB/s", "peak": peaks["hbm_gbs"],
+                         "frac": a / peaks["hbm_gbs"],
+                         "note": "algorithmic bytes (every gathered message row counted; about half are L2 hits: in-degree 16)"}
+        line["stages"] = st
+        line["peak_source"] = peaks["source"]
         if world == 1 and not args.no_cpu:
             from oracle import cpu_reference as R
             torch.set_num_threads(os.cpu_count() or 1)

@@ -15,6 +15,7 @@
 #include "tf32.cuh"
 #include "tc.cuh"
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -694,6 +695,7 @@ int ggnn_f16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t s
   pack_edge16_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, reinterpret_cast<__half*>(ew.Wt_f16), two_e, h);
   GGNN_LAUNCHED(ctx);
   GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ew.tm_Wt16, ew.Wt_f16, (int64_t)two_e * HP, HP, BKH, HP));
+  GGNN_TRY(ggnn_w16_pack_bias(ctx, slot, HP, st));
   if (with_gru) {
     GGNN_TRY(realloc_h(ctx, ctx->Wgt_f16, (size_t)4 * HP * HP));
     GGNN_TRY(realloc_h(ctx, ctx->Wct_f16, (size_t)2 * HP * HP));
@@ -732,7 +734,10 @@ int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     ctx->attr_mask |= 1u << GGNN_ATTR_F16;
   }
   const ggnn_edge_weights& ew = ctx->edge[slot];
-  if (plan.max_tiles > 0 && plan.nnz > 0) {
+  static const bool msg_w16 = getenv("GGNN_MSG_W16") != nullptr;      // A-B switch
+  if (msg_w16) {
+    GGNN_TRY(ggnn_w16_msg(ctx, slot, plan, msg16, state16, HP, st));
+  } else if (plan.max_tiles > 0 && plan.nnz > 0) {
     CUtensorMap tmOut;
     GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmOut, msg16, plan.max_tiles * (int64_t)BM, HP, BKH, BM));
     msg16::params p{};

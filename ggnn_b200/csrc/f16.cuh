@@ -26,3 +26,6 @@ int ggnn_w16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, u
 // last step the FP32 state is also written to h_out [N, h]
 int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* acts16, void* rh16, void* u16,
                   void* state16, float* h_out, bool last_step, cudaStream_t st);
+// message transform alone through wgemm16_kernel<MSG> (hw = 128 too) and the padded biases it reads
+int ggnn_w16_msg(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16, int hw, cudaStream_t st);
+int ggnn_w16_pack_bias(ggnn_ctx* ctx, int slot, int hw, cudaStream_t st);

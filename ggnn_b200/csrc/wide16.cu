@@ -814,6 +814,38 @@ int ggnn_w16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, u
   return GGNN_OK;
 }
 
+// message transform alone, any hw in {128, 192, .., 512}: used by f16.cu (hw = 128) as an A-B alternative to msg_f16_kernel
+int ggnn_w16_msg(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16, int hw, cudaStream_t st) {
+  using namespace w16;
+  const ggnn_edge_weights& ew = ctx->edge[slot];
+  if (plan.max_tiles <= 0 || plan.nnz <= 0) return GGNN_OK;
+  const int n_row_tiles = (int)ceil_div64(plan.N, BM);
+  CUtensorMap tmState, tmMsg;
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmState, state16, plan.N, hw, BKH, BM));
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmMsg, msg16, plan.max_tiles * (int64_t)BM, hw, BKH, BM));
+  params p{};
+  p.A_gather = reinterpret_cast<const __half*>(state16);
+  if (plan.dense_rows) { p.gather = nullptr; p.tiles_per_type = n_row_tiles; }
+  else { p.gather = plan.msg_src; p.tiles_per_type = 1; }
+  p.tile_type = plan.tile_type; p.n_tiles_dev = plan.n_tiles;
+  p.KC = hw / BKH; p.KC1 = p.KC;
+  p.Ntot = hw; p.NW = slice_width(hw, hw); p.S = (hw + p.NW - 1) / p.NW;
+  p.bias = ew.B_pad16; p.hw = hw; p.h = ctx->h; p.N = plan.N;
+  prof_scope ps(ctx, GGNN_STAGE_MSG, st);
+  return launch<MODE_MSG>(ctx, p, tmState, tmState, ew.tm_Wt16, tmMsg, tmMsg, plan.max_tiles * p.S, st);
+}
+
+// padded FP32 biases [two_e, hw] of `slot` (also needed by ggnn_w16_msg at hw = 128)
+int ggnn_w16_pack_bias(ggnn_ctx* ctx, int slot, int hw, cudaStream_t st) {
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  void* bp = ew.B_pad16;
+  GGNN_TRY(realloc_bytes(ctx, bp, (size_t)ctx->two_e * hw * 4));
+  ew.B_pad16 = reinterpret_cast<float*>(bp);
+  w16::pad_bias_kernel<<<(ctx->two_e * hw + 255) / 256, 256, 0, st>>>(ew.B, ew.B_pad16, ctx->two_e, ctx->h, hw);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
 // One timestep.  Scratch (all FP16, pitch hw): msg16 [max_tiles*128], acts16 / rh16 / u16 [N]; state16 [N] in/out.
 int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* acts16, void* rh16, void* u16,
                   void* state16, float* h_out, bool last_step, cudaStream_t st) {
