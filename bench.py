@@ -445,7 +445,7 @@ def run_c5(args):
     prop = ggnn_b200.Propagator(ggnn_b200.from_dict(wd), dev)
     h0, edges, d, N = c5_inputs(per_gpu, 1000 + rank, dev)
     grads = torch.zeros(prop.grad_floats, device=dev)
-    prec = "fp32" if args.precision == "fp32" else "tf32"      # the kind::f16 kernels have no training path
+    prec = args.precision      # "f16": forward on the FP16 kernels (h = 400 -> wide16.cu) with the FP32 tape, backward TF32
 
     step_no = [0]
 
@@ -486,25 +486,28 @@ def run_c5(args):
     ms_per_step = ms / args.steps
     nnz = int(edges.shape[0])
     other = None
-    if prec != "fp32" and not args.no_fp32:            # the strict-FP32 training step, same inputs
-        step("fp32"); barrier()
-        e0.record()
-        for _ in range(max(1, args.steps // 2)):
-            step("fp32")
-        e1.record(); barrier()
-        oms = e0.elapsed_time(e1) / max(1, args.steps // 2)
-        if world > 1:
-            t2 = torch.tensor([oms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-            oms = float(t2.item())
-        other = {"fp32": {"value": per_gpu * world / (oms * 1e-3), "unit": "graphs/s", "ms_per_step": oms}}
+    if prec != "fp32" and not args.no_fp32:            # the same training step in the other arithmetic modes, same inputs
+        other = {}
+        for mode in [m for m in ("tf32", "fp32") if m != prec]:
+            step(mode); barrier()
+            e0.record()
+            for _ in range(max(1, args.steps // 2)):
+                step(mode)
+            e1.record(); barrier()
+            oms = e0.elapsed_time(e1) / max(1, args.steps // 2)
+            if world > 1:
+                t2 = torch.tensor([oms], device=dev, dtype=torch.float64)
+                dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+                oms = float(t2.item())
+            other[mode] = {"value": per_gpu * world / (oms * 1e-3), "unit": "graphs/s", "ms_per_step": oms}
     if rank == 0:
         flop = 3 * Tc * (nnz * 2 * Hc * Hc + N * 12 * Hc * Hc)       # bwd counted as 2x fwd
         line = {"metric": "GGNN propagation training step graphs/sec (fwd+bwd+clip+Adam, T=4)",
                 "value": per_gpu * world / (ms_per_step * 1e-3), "unit": "graphs/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32" if prec == "fp32" else "tf32 operands, f32 accumulate / pointwise / optimiser",
+                "dtype": {"fp32": "f32", "tf32": "tf32 operands, f32 accumulate / pointwise / optimiser",
+                          "f16": "f16 operands forward, tf32 operands backward, f32 accumulate / pointwise / optimiser"}[prec],
                 "data": "synthetic", "other_modes": other,
                 "config": {"workload": "C5 synthetic WSJ-shaped trees, h=400 2E=92 T=4, fwd+bwd of the path + "
                                        "one all-reduce of the 62.9 MB flat weight gradient + per-variable clip_by_norm(1.0) + "

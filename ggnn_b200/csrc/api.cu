@@ -313,13 +313,16 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
   ggnn_tape& tape = ext_of(ctx)->tape;
   tape.valid = false;
   if (flags & GGNN_FLAG_SAVE_TAPE) {      // training forward: keep h, x, r, u, c of every step
-    if (precision != GGNN_PREC_FP32 && precision != GGNN_PREC_TF32)
-      GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE needs GGNN_PREC_FP32 or GGNN_PREC_TF32");
+    // GGNN_PREC_F16 (h > 128): forward on the FP16 kernels of wide16.cu, tape in FP32, backward on the TF32 tensor-core path
+    const bool f16t = precision == GGNN_PREC_F16;
+    if (f16t && !ggnn_w16_supported(ctx))
+      GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE with GGNN_PREC_F16 needs a hidden size in (128, 512], got h=%d; use GGNN_PREC_TF32", ctx->h);
     const bool tf = precision == GGNN_PREC_TF32;
+    void* state16 = ext_of(ctx)->ar[4].p;
     if (plan.dense_rows) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE: edge list is in dense-row mode (nnz >= N*2E)");
     const size_t nh = (size_t)plan.N * ctx->h;
     GGNN_TRY(arena_reserve(ctx, 2, (size_t)T * TAPE_ARRAYS * nh * 4 + 256, st));
-    tape.plan = plan; tape.T = T; tape.slot = slot; tape.h = ctx->h; tape.tf32 = tf;
+    tape.plan = plan; tape.T = T; tape.slot = slot; tape.h = ctx->h; tape.tf32 = tf || f16t;
     tape.acts = reinterpret_cast<float*>(ext_of(ctx)->ar[2].p);
     ctx_ext* ex = ext_of(ctx);
     tape.w_mask = tape.state_mask = nullptr; tape.keep = 1.f; tape.w_eff = nullptr;
@@ -354,7 +357,8 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
     }
     if (tf && T > 0) GGNN_TRY(ggnn_tf32_round_copy(ctx, h_state, h_state, (int64_t)nh, st));
     for (int t = 0; t < T; ++t) {
-      GGNN_CUDA(ctx, cudaMemcpyAsync(tape.at(t, TAPE_H), h_state, nh * 4, cudaMemcpyDeviceToDevice, st));
+      if (f16t) GGNN_TRY(ggnn_w16_state_out(ctx, state16, tape.at(t, TAPE_H), plan.N, st));
+      else GGNN_CUDA(ctx, cudaMemcpyAsync(tape.at(t, TAPE_H), h_state, nh * 4, cudaMemcpyDeviceToDevice, st));
       ggnn_step_bufs tb = sb;
       tb.acts = tape.at(t, TAPE_X); tb.u = tape.at(t, TAPE_U);
       tb.tape_r = tape.at(t, TAPE_R); tb.tape_c = tape.at(t, TAPE_C);
@@ -363,6 +367,16 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
                                  (int64_t)wn, false, st));
         tb.W_override = tape.w_eff;
         if (tf) GGNN_TRY(ggnn_tf32_repack_edge(ctx, slot, tape.w_eff, st));   // this step's packed operand
+        if (f16t) GGNN_TRY(ggnn_w16_repack_edge(ctx, slot, tape.w_eff, st));
+      }
+      if (f16t) {
+        const ggnn_w16_tape wt{tape.at(t, TAPE_X), tape.at(t, TAPE_R), tape.at(t, TAPE_U), tape.at(t, TAPE_C)};
+        GGNN_TRY(ggnn_step_w16(ctx, slot, plan, sb.msg, sb.acts, sb.rh, sb.u, state16, h_state, t == T - 1, st, &wt));
+        if (tape.state_mask) {
+          if (t < T - 1) GGNN_TRY(ggnn_w16_state_mask(ctx, state16, tape.state_mask + (size_t)t * nh, 1.0f / tape.keep, plan.N, st));
+          else GGNN_TRY(ggnn_mask_scale(ctx, h_state, tape.state_mask + (size_t)t * nh, 1.0f / tape.keep, h_state, (int64_t)nh, false, st));
+        }
+        continue;
       }
       if (tf) GGNN_TRY(ggnn_step_tf32(ctx, slot, plan, tb, h_state, t == T - 1, st));
       else GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, tb, h_state, st));
@@ -373,6 +387,7 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
       }
     }
     if (tf && tape.w_mask) GGNN_TRY(ggnn_tf32_repack_edge(ctx, slot, nullptr, st));   // back to the undropped weights
+    if (f16t && tape.w_mask) GGNN_TRY(ggnn_w16_repack_edge(ctx, slot, nullptr, st));
     tape.valid = true;
     return GGNN_OK;
   }

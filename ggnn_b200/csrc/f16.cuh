@@ -24,8 +24,13 @@ int ggnn_w16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, u
                       cudaStream_t st);
 // one timestep; msg16 [max_tiles*128, hw16], acts16 / rh16 / u16 [N, hw16] FP16 scratch; state16 in/out; on the
 // last step the FP32 state is also written to h_out [N, h]
+// tape != null (training forward): the unfused kernels also store x (FP16-rounded), r, u, c of this step as FP32 [N, h]
+struct ggnn_w16_tape { float *x, *r, *u, *c; };
 int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* acts16, void* rh16, void* u16,
-                  void* state16, float* h_out, bool last_step, cudaStream_t st);
+                  void* state16, float* h_out, bool last_step, cudaStream_t st, const ggnn_w16_tape* tape = nullptr);
+int ggnn_w16_state_out(ggnn_ctx* ctx, const void* state16, float* dst, int64_t N, cudaStream_t st);
+int ggnn_w16_state_mask(ggnn_ctx* ctx, void* state16, const float* mask, float scale, int64_t N, cudaStream_t st);
+int ggnn_w16_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st);
 // message transform alone through wgemm16_kernel<MSG> (hw = 128 too) and the padded biases it reads
 int ggnn_w16_msg(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16, int hw, cudaStream_t st);
 int ggnn_w16_pack_bias(ggnn_ctx* ctx, int slot, int hw, cudaStream_t st);

@@ -69,6 +69,8 @@ struct params {
   const __half* state16;      // GATES, CAND: h  [N, hw]
   const __half* u16;          // CAND: u [N, hw]
   float* h_out;               // CAND, last step: FP32 result [N, h] or null
+  float* tape_g;              // training tape, [N, h] FP32 or null: GATES r, CAND c
+  float* tape_u;              // GATES: u
 };
 
 __device__ __forceinline__ uint32_t sw_off(int r, int slot) {
@@ -302,6 +304,16 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
             for (int k = 0; k < 16; ++k) {
               const float gate = tc::rcp_approx(1.0f + tc::ex2_approx(-kLog2e * (__uint_as_float(acc[k]) + sb[k])));
               o[k] = is_r ? gate * hh[k] : gate;
+              if (p.tape_g) acc[k] = __float_as_uint(gate);     // the tape keeps the gate itself
+            }
+            if (p.tape_g && row_ok) {
+              float* dst = (is_r ? p.tape_g : p.tape_u) + grow * p.h + hcol + c16 * 16;
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4)
+                if (hcol + c16 * 16 + k4 * 4 < p.h)
+                  *reinterpret_cast<float4*>(dst + k4 * 4) =
+                      make_float4(__uint_as_float(acc[k4 * 4]), __uint_as_float(acc[k4 * 4 + 1]),
+                                  __uint_as_float(acc[k4 * 4 + 2]), __uint_as_float(acc[k4 * 4 + 3]));
             }
           } else {
             float hh[16], uu[16];
@@ -312,6 +324,16 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
               const float cand = fmaf(-2.0f, tc::rcp_approx(1.0f + tc::ex2_approx(
                                                  2.0f * kLog2e * (__uint_as_float(acc[k]) + sb[k]))), 1.0f);
               o[k] = fmaf(uu[k], hh[k] - cand, cand);
+              if (p.tape_g) acc[k] = __float_as_uint(cand);
+            }
+            if (p.tape_g && row_ok) {
+              float* dst = p.tape_g + grow * p.h + hcol + c16 * 16;
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4)
+                if (hcol + c16 * 16 + k4 * 4 < p.h)
+                  *reinterpret_cast<float4*>(dst + k4 * 4) =
+                      make_float4(__uint_as_float(acc[k4 * 4]), __uint_as_float(acc[k4 * 4 + 1]),
+                                  __uint_as_float(acc[k4 * 4 + 2]), __uint_as_float(acc[k4 * 4 + 3]));
             }
             if (p.h_out && row_ok) {
               float* dst = p.h_out + grow * p.h + hcol + c16 * 16;
@@ -396,7 +418,7 @@ __global__ void state_in_kernel(const float* __restrict__ hs, __half* __restrict
 // ---- aggregation: x[n, :] = sum of the FP16 message rows of node n (fixed order), FP32 sum -> FP16 ----
 __global__ void __launch_bounds__(256)
 aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ tmsg, const __half* __restrict__ msg,
-                 __half* __restrict__ acts, int64_t N, int hw) {
+                 __half* __restrict__ acts, int64_t N, int hw, float* __restrict__ acts32, int h) {
   const int lane = threadIdx.x & 31;
   const int64_t node = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (node >= N) return;
@@ -434,7 +456,47 @@ aggregate_kernel(const int32_t* __restrict__ tptr, const int32_t* __restrict__ t
 #pragma unroll
       for (int k = 0; k < 8; ++k) acc[k] += f[k];
     }
-    reinterpret_cast<uint4*>(acts + (size_t)node * hw)[c] = pack8(acc);
+    const uint4 pk = pack8(acc);
+    reinterpret_cast<uint4*>(acts + (size_t)node * hw)[c] = pk;
+    if (acts32 && c * 8 < h) {                 // training tape: the FP16-rounded operand, widened (h % 4 == 0)
+      float f[8];
+      unpack8(pk, f);
+      float* dst = acts32 + (size_t)node * h + c * 8;
+      *reinterpret_cast<float4*>(dst) = make_float4(f[0], f[1], f[2], f[3]);
+      if (c * 8 + 4 < h) *reinterpret_cast<float4*>(dst + 4) = make_float4(f[4], f[5], f[6], f[7]);
+    }
+  }
+}
+
+// dst [N, h] FP32 = state16 [N, hw] (training tape: the state a step started from)
+__global__ void state_out_kernel(const __half* __restrict__ s16, float* __restrict__ dst, int64_t N, int h, int hw) {
+  const int q = h / 4;
+  const int64_t total = N * q;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / q;
+    const int c = (int)(i % q) * 4;
+    const uint2 v = *reinterpret_cast<const uint2*>(s16 + n * hw + c);
+    const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+    const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+    *reinterpret_cast<float4*>(dst + n * h + c) = make_float4(lo.x, lo.y, hi.x, hi.y);
+  }
+}
+// state16 = f16(state16 * mask * scale): DropoutWrapper(state_keep_prob) on the new state
+__global__ void state_mask_kernel(__half* __restrict__ s16, const float* __restrict__ mask, float scale, int64_t N, int h,
+                                  int hw) {
+  const int q = h / 4;
+  const int64_t total = N * q;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / q;
+    const int c = (int)(i % q) * 4;
+    uint2 v = *reinterpret_cast<uint2*>(s16 + n * hw + c);
+    const float4 m = *reinterpret_cast<const float4*>(mask + n * h + c);
+    const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+    const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+    __half2 a = __floats2half2_rn(lo.x * m.x * scale, lo.y * m.y * scale);
+    __half2 b = __floats2half2_rn(hi.x * m.z * scale, hi.y * m.w * scale);
+    v.x = *reinterpret_cast<uint32_t*>(&a); v.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(s16 + n * hw + c) = v;
   }
 }
 
@@ -848,7 +910,7 @@ int ggnn_w16_pack_bias(ggnn_ctx* ctx, int slot, int hw, cudaStream_t st) {
 
 // One timestep.  Scratch (all FP16, pitch hw): msg16 [max_tiles*128], acts16 / rh16 / u16 [N]; state16 [N] in/out.
 int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* acts16, void* rh16, void* u16,
-                  void* state16, float* h_out, bool last_step, cudaStream_t st) {
+                  void* state16, float* h_out, bool last_step, cudaStream_t st, const ggnn_w16_tape* tape) {
   using namespace w16;
   if (plan.N == 0) return GGNN_OK;
   const int h = ctx->h, hw = ctx->hw16;
@@ -876,10 +938,11 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     prof_scope ps(ctx, GGNN_STAGE_AGG, st);
     const int64_t threads = plan.N * 32;
     aggregate_kernel<<<(unsigned)ceil_div64(threads, 256), 256, 0, st>>>(
-        plan.tptr, plan.tmsg, reinterpret_cast<const __half*>(msg16), reinterpret_cast<__half*>(acts16), plan.N, hw);
+        plan.tptr, plan.tmsg, reinterpret_cast<const __half*>(msg16), reinterpret_cast<__half*>(acts16), plan.N, hw,
+        tape ? tape->x : nullptr, h);
     GGNN_LAUNCHED(ctx);
   }
-  if (hw <= 256 && !ctx->no_fused) {       // GATES + CAND in one kernel, gates and r*h on chip
+  if (hw <= 256 && !ctx->no_fused && !tape) {       // GATES + CAND in one kernel, gates and r*h on chip
     GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_W16_0 + 3, gw16::gru_w16_kernel, gw16::SMEM_BYTES);
     gw16::params g{};
     g.bg = ctx->bg_w16; g.bc = ctx->bc_w16; g.h_out = last_step ? h_out : nullptr;
@@ -897,6 +960,7 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     p.Ntot = 2 * hw; p.NW = slice_width(2 * hw, 2 * hw); p.S = (p.Ntot + p.NW - 1) / p.NW;
     p.bias = ctx->bg_w16; p.hw = hw; p.h = h; p.N = plan.N;
     p.state16 = reinterpret_cast<const __half*>(state16);
+    if (tape) { p.tape_g = tape->r; p.tape_u = tape->u; }
     prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
     GGNN_TRY(launch<MODE_GATES>(ctx, p, tmActs, tmState, ctx->tm_Wg16, tmRh, tmU, (int64_t)n_row_tiles * p.S, st));
   }
@@ -909,8 +973,31 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     p.state16 = reinterpret_cast<const __half*>(state16);
     p.u16 = reinterpret_cast<const __half*>(u16);
     p.h_out = last_step ? h_out : nullptr;
+    if (tape) p.tape_g = tape->c;
     prof_scope ps(ctx, GGNN_STAGE_GRU_CAND, st);
     GGNN_TRY(launch<MODE_CAND>(ctx, p, tmActs, tmRh, ctx->tm_Wc16, tmState, tmState, (int64_t)n_row_tiles * p.S, st));
   }
+  return GGNN_OK;
+}
+
+// ---- training tape helpers (run_steps, SAVE_TAPE with GGNN_PREC_F16) ----------------------------------------
+int ggnn_w16_state_out(ggnn_ctx* ctx, const void* state16, float* dst, int64_t N, cudaStream_t st) {
+  if (N == 0) return GGNN_OK;
+  w16::state_out_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(reinterpret_cast<const __half*>(state16), dst, N, ctx->h, ctx->hw16);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+int ggnn_w16_state_mask(ggnn_ctx* ctx, void* state16, const float* mask, float scale, int64_t N, cudaStream_t st) {
+  if (N == 0) return GGNN_OK;
+  w16::state_mask_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(reinterpret_cast<__half*>(state16), mask, scale, N, ctx->h, ctx->hw16);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+// edge weights of `slot` re-packed from W_src (dropout: this step's effective weights; null = the slot's own)
+int ggnn_w16_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st) {
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  w16::pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src ? W_src : ew.W, reinterpret_cast<__half*>(ew.Wt_f16),
+                                                          ctx->two_e, ctx->h, ctx->hw16);
+  GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

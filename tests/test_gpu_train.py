@@ -251,6 +251,40 @@ def test_training_dropout_tf32():
     assert O.normwise_err(out.cpu().numpy(), O.propagate_edges(h0, edges.numpy(), w, T)) <= TOL_TF32
 
 
+@pytest.mark.parametrize("b,v,E,h,T", [(6, 24, 8, 400, 2), (40, 40, 46, 400, 4), (4, 16, 5, 256, 3), (3, 20, 4, 192, 2)])
+def test_backward_f16_forward_edges(b, v, E, h, T):
+    """Training forward on the FP16 kernels of wide16.cu (h > 128) with the FP32 tape, backward on the TF32 tensor-core
+    path: same tolerance as the TF32 mode against the FP64 autograd oracle."""
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=b + T)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision="f16",
+                              save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    _check_tf32(prop, hT, dh0, flat, G.grads(h0, edges.numpy(), w, T, d))
+
+
+def test_training_dropout_f16_forward_and_unsupported_sizes():
+    b, v, E, h, T, keep = 4, 16, 5, 256, 3, 0.9
+    tri, edges, w, h0, d = _case(b, v, E, h, seed=21)
+    rng = np.random.default_rng(3)
+    wm = (rng.random((T, 2 * E, h, h)) < keep).astype(np.float32)
+    sm = (rng.random((T, b * v, h)) < keep).astype(np.float32)
+    prop = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    prop.set_dropout(torch.from_numpy(wm).cuda(), torch.from_numpy(sm).cuda(), keep, T)
+    hT = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision="f16",
+                              save_tape=True)
+    dh0, flat = prop.backward(torch.from_numpy(d).cuda())
+    _check_tf32(prop, hT, dh0, flat, G.grads(h0, edges.numpy(), w, T, d, w_mask=wm, state_mask=sm, keep=keep))
+    # the packed FP16 weights are restored after the dropped forward
+    out = prop.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=T, precision="f16")
+    assert O.normwise_err(out.cpu().numpy(), O.propagate_edges(h0, edges.numpy(), w, T)) <= TOL_TF32
+    # h <= 128 has no FP16 training forward
+    tri, edges, w, h0, d = _case(2, 8, 3, 128, seed=1)
+    p128 = Propagator(ggnn_b200.from_dict(w), "cuda:0")
+    with pytest.raises(RuntimeError, match="SAVE_TAPE"):
+        p128.propagate_edges(torch.from_numpy(h0).cuda(), edges.cuda(), num_timesteps=2, precision="f16", save_tape=True)
+
+
 def test_training_loop_tf32_tracks_fp32():
     """20 optimiser steps on one batch in both modes from the same start: the TF32 loss curve follows the
     FP32 one (relative difference of the final loss below 2 %), and both fall."""
