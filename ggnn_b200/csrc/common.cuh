@@ -47,6 +47,7 @@ struct ggnn_ctx {
   void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
   void* Wct_f16 = nullptr;   // [128, 256]
   CUtensorMap tm_Wg16, tm_Wc16;
+  CUtensorMap tm_Wg16h, tm_Wc16h;   // same, boxes of hw16 / 2 rows (CTA pairs)
   CUtensorMap tm_Wg16f, tm_Wc16f;   // wide16.cu fused GRU kernel (hw16 <= 256): boxes of hw16 rows
   float* bg_w16 = nullptr;   // [2*hw16], [hw16] zero-padded GRU biases (wide16.cu)
   float* bc_w16 = nullptr;
@@ -78,7 +79,7 @@ struct ggnn_ctx {
 
 // cudaFuncSetAttribute is per device: remember per ctx (a process may own one ctx per GPU), not in a static
 enum { GGNN_ATTR_TF32_GEMM0 = 0 /* + mode 0..3 */, GGNN_ATTR_GRU_FUSED = 4, GGNN_ATTR_MSG_TC = 5, GGNN_ATTR_F16 = 6,
-       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU */ };
+       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */ };
 #define GGNN_ENSURE_SMEM(ctx, bit, kernel, bytes)                                                          \
   do {                                                                                                     \
     if (!((ctx)->attr_mask & (1u << (bit)))) {                                                             \

@@ -617,25 +617,24 @@ gru_w16_kernel(const params p, const __grid_constant__ CUtensorMap tmX, const __
       };
       int it = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
-        // the first ring-full of weights does not depend on the tiles being free
+        // the first ring-full of weights does not depend on the tiles being free; the h tile is free as soon as the
+        // previous candidate MMAs retire, the x tile (h' staging) only after the previous store has read it
         int issued = 0;
         auto tiles_in = [&]() {
-          if (it > 0) {
-            tc::mbar_wait(bar(BAR_X_EMPTY), (it - 1) & 1);
-            tc::mbar_wait(bar(BAR_C_DONE), (it - 1) & 1);
-          }
-          tc::mbar_arrive_expect_tx(bar(BAR_X_FULL), (uint32_t)KC1 * CHUNK);
-          for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d(sX + kc * CHUNK, &tmX, kc * BKH, tile * BM, bar(BAR_X_FULL));
+          if (it > 0) tc::mbar_wait(bar(BAR_C_DONE), (it - 1) & 1);
           tc::mbar_arrive_expect_tx(bar(BAR_H_FULL), (uint32_t)KC1 * CHUNK);
           for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d(sH + kc * CHUNK, &tmH, kc * BKH, tile * BM, bar(BAR_H_FULL));
+          if (it > 0) tc::mbar_wait(bar(BAR_X_EMPTY), (it - 1) & 1);
+          tc::mbar_arrive_expect_tx(bar(BAR_X_FULL), (uint32_t)KC1 * CHUNK);
+          for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d(sX + kc * CHUNK, &tmX, kc * BKH, tile * BM, bar(BAR_X_FULL));
         };
         auto step = [&](const CUtensorMap* tm, int kcol, int nrow) {
           w_fill(tm, kcol, nrow);
           if (++issued == WSLOTS) tiles_in();
         };
-        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, hw);               // x   -> u
         for (int kc = 0; kc < KC1; ++kc) step(&tmWg, hw + kc * BKH, hw);          // h   -> u
         for (int kc = 0; kc < KC1; ++kc) step(&tmWg, hw + kc * BKH, 0);           // h   -> r
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, hw);               // x   -> u
         for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, 0);                // x   -> r
         for (int kc = 0; kc < KC1; ++kc) step(&tmWc, kc * BKH, 0);                // x   -> cand
         for (int kc = 0; kc < KC1; ++kc) step(&tmWc, hw + kc * BKH, 0);           // r*h -> cand
@@ -662,13 +661,13 @@ gru_w16_kernel(const params p, const __grid_constant__ CUtensorMap tmX, const __
       int it = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
         if (it > 0) tc::mbar_wait(bar(BAR_TMEM_FREE), (it - 1) & 1);
-        tc::mbar_wait(bar(BAR_X_FULL), it & 1);
-        tc::fence_after_sync();
-        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sX + kc * CHUNK, kc == 0);      // x -> u
         tc::mbar_wait(bar(BAR_H_FULL), it & 1);
         tc::fence_after_sync();
-        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sH + kc * CHUNK, false);        // h -> u
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sH + kc * CHUNK, kc == 0);      // h -> u
         for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sH + kc * CHUNK, kc == 0);     // h -> r
+        tc::mbar_wait(bar(BAR_X_FULL), it & 1);                                         // x arrives under the h MMAs
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sX + kc * CHUNK, false);        // x -> u
         tc::umma_commit(bar(BAR_U_DONE));
         for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sX + kc * CHUNK, false);       // x -> r
         tc::umma_commit(bar(BAR_R_DONE));
@@ -813,6 +812,286 @@ gru_w16_kernel(const params p, const __grid_constant__ CUtensorMap tmX, const __
 }  // namespace gw16
 
 // =========================================================================================
+// The same GRU cell on CTA PAIRS (tcgen05 cta_group::2): the two CTAs of a cluster take two adjacent 128-node tiles as one
+// 256-row MMA tile.  Each CTA keeps its own x / h tiles and epilogues, but only HALF of every weight chunk ([hw/2 n x 64 k]):
+// the weight bytes an SM pulls from L2 per tile halve (768 -> 384 KB at hw = 256, the measured limiter of gru_w16_kernel)
+// and the ring holds six chunks instead of three.  The even CTA issues every MMA; TMA completions of both CTAs are counted on
+// its barriers, MMA completions are multicast to both.
+namespace gw16x2 {
+using namespace w16;
+
+constexpr int WSLOT = 16 * 1024;                 // one [128 n x 64 k] FP16 half chunk
+constexpr int WSLOTS = 6;
+constexpr int TILE_BYTES = 4 * CHUNK;
+constexpr int WARP_TMA = 8, WARP_MMA = 9;
+constexpr int NTHREADS = 10 * 32;
+constexpr int SMEM_BYTES = 2 * TILE_BYTES + WSLOTS * WSLOT + 1024 + 256;
+
+enum {
+  BAR_W_FULL = 0,                     // [WSLOTS] even CTA: bytes of both halves
+  BAR_W_EMPTY = BAR_W_FULL + WSLOTS,  // [WSLOTS] multicast commit
+  BAR_X_FULL = BAR_W_EMPTY + WSLOTS,  // even CTA: both x tiles
+  BAR_H_FULL,                         // even CTA: both h tiles
+  BAR_X_EMPTY,                        // local
+  BAR_U_DONE, BAR_R_DONE, BAR_C_DONE, // multicast commits
+  BAR_RH_FULL,                        // even CTA: 16 epilogue warps
+  BAR_TMEM_FREE,                      // even CTA: 16 epilogue warps
+  BAR_COUNT
+};
+static_assert(8 * BAR_COUNT + 8 <= 256, "barrier area");
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
+gru_w16x2_kernel(const gw16::params p, const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmH,
+                 const __grid_constant__ CUtensorMap tmWg, const __grid_constant__ CUtensorMap tmWc) {
+  extern __shared__ uint8_t smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (base - tc::smem_u32(smem_raw));
+  const uint32_t sX = base, sH = base + TILE_BYTES, sW = sH + TILE_BYTES;
+  const uint32_t bars = sW + WSLOTS * WSLOT;
+  auto bar = [&](int i) { return bars + 8u * i; };
+  const uint32_t tmem_slot = bars + 8u * BAR_COUNT;
+  const int hw = p.hw, KC1 = hw / BKH, hh = hw / 2;
+  const uint32_t rank = tc::cluster_ctarank();
+  const bool lead = rank == 0;
+  const int n_pairs = (p.n_tiles + 1) / 2;
+  const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+  const uint32_t wbytes = (uint32_t)hh * 128u;              // bytes one CTA's half chunk delivers
+
+  if (warp == WARP_MMA && lane == 0) {
+    for (int s = 0; s < WSLOTS; ++s) { tc::mbar_init(bar(BAR_W_FULL + s), 1); tc::mbar_init(bar(BAR_W_EMPTY + s), 1); }
+    tc::mbar_init(bar(BAR_X_FULL), 1);
+    tc::mbar_init(bar(BAR_H_FULL), 1);
+    tc::mbar_init(bar(BAR_X_EMPTY), 1);
+    tc::mbar_init(bar(BAR_U_DONE), 1);
+    tc::mbar_init(bar(BAR_R_DONE), 1);
+    tc::mbar_init(bar(BAR_C_DONE), 1);
+    tc::mbar_init(bar(BAR_RH_FULL), 16);
+    tc::mbar_init(bar(BAR_TMEM_FREE), 16);
+    tc::fence_barrier_init();
+  }
+  if (warp == WARP_TMA) {
+    if (lane == 0) {
+      tc::tma_prefetch_desc(&tmX); tc::tma_prefetch_desc(&tmH); tc::tma_prefetch_desc(&tmWg); tc::tma_prefetch_desc(&tmWc);
+    }
+    __syncwarp();
+    tc::tmem_alloc_pair(tmem_slot, 512);
+  }
+  tc::fence_before_sync();
+  tc::cluster_sync_all();                                   // barriers of both CTAs initialised, TMEM allocated
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
+
+  if (warp == WARP_TMA) {
+    // =============================== TMA producer (both CTAs) ===============================
+    if (lane == 0) {
+      uint32_t fill = 0;
+      auto w_fill = [&](const CUtensorMap* tm, int kcol, int nrow) {
+        const int s = fill % WSLOTS;
+        if (fill >= WSLOTS) tc::mbar_wait(bar(BAR_W_EMPTY + s), ((fill / WSLOTS) - 1) & 1);
+        if (lead) tc::mbar_arrive_expect_tx(bar(BAR_W_FULL + s), 2u * wbytes);
+        tc::tma_load_2d_pair(sW + s * WSLOT, tm, kcol, nrow + (int)rank * hh, bar(BAR_W_FULL + s));
+        ++fill;
+      };
+      int it = 0;
+      for (int pr = pair0; pr < n_pairs; pr += pair_stride, ++it) {
+        const int tile = 2 * pr + (int)rank;
+        int issued = 0;
+        auto tiles_in = [&]() {
+          if (it > 0) tc::mbar_wait(bar(BAR_C_DONE), (it - 1) & 1);
+          if (lead) tc::mbar_arrive_expect_tx(bar(BAR_H_FULL), 2u * (uint32_t)KC1 * CHUNK);
+          for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d_pair(sH + kc * CHUNK, &tmH, kc * BKH, tile * BM, bar(BAR_H_FULL));
+          if (it > 0) tc::mbar_wait(bar(BAR_X_EMPTY), (it - 1) & 1);
+          if (lead) tc::mbar_arrive_expect_tx(bar(BAR_X_FULL), 2u * (uint32_t)KC1 * CHUNK);
+          for (int kc = 0; kc < KC1; ++kc) tc::tma_load_2d_pair(sX + kc * CHUNK, &tmX, kc * BKH, tile * BM, bar(BAR_X_FULL));
+        };
+        auto step = [&](const CUtensorMap* tm, int kcol, int nrow) {
+          w_fill(tm, kcol, nrow);
+          if (++issued == WSLOTS) tiles_in();
+        };
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, hw + kc * BKH, hw);          // h   -> u
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, hw + kc * BKH, 0);           // h   -> r
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, hw);               // x   -> u
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWg, kc * BKH, 0);                // x   -> r
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWc, kc * BKH, 0);                // x   -> cand
+        for (int kc = 0; kc < KC1; ++kc) step(&tmWc, hw + kc * BKH, 0);           // r*h -> cand
+      }
+    }
+    __syncwarp();
+  } else if (warp == WARP_MMA) {
+    // =============================== MMA issuer (even CTA only) ===============================
+    if (lead && lane == 0) {
+      const uint32_t idesc = tc::umma_idesc(0 /*F16*/, 2 * BM, hw);
+      const uint32_t d_rc = tmem_base, d_u = tmem_base + 256;
+      uint32_t use = 0;
+      auto chunk_mma = [&](uint32_t d, uint32_t a, bool first) {
+        const int s = use % WSLOTS;
+        tc::mbar_wait_cluster(bar(BAR_W_FULL + s), (use / WSLOTS) & 1);
+        tc::fence_after_sync();
+        const uint32_t w = sW + s * WSLOT;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          tc::umma_f16_pair(d, tc::umma_desc_sw128(a + k * 32), tc::umma_desc_sw128(w + k * 32), idesc, (first && k == 0) ? 0u : 1u);
+        tc::umma_commit_pair(bar(BAR_W_EMPTY + s));
+        ++use;
+      };
+      int it = 0;
+      for (int pr = pair0; pr < n_pairs; pr += pair_stride, ++it) {
+        if (it > 0) tc::mbar_wait_cluster(bar(BAR_TMEM_FREE), (it - 1) & 1);
+        tc::mbar_wait_cluster(bar(BAR_H_FULL), it & 1);
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sH + kc * CHUNK, kc == 0);      // h -> u
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sH + kc * CHUNK, kc == 0);     // h -> r
+        tc::mbar_wait_cluster(bar(BAR_X_FULL), it & 1);
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_u, sX + kc * CHUNK, false);        // x -> u
+        tc::umma_commit_pair(bar(BAR_U_DONE));
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sX + kc * CHUNK, false);       // x -> r
+        tc::umma_commit_pair(bar(BAR_R_DONE));
+        tc::mbar_wait_cluster(bar(BAR_RH_FULL), it & 1);                                // both CTAs: r drained, r*h in place
+        tc::fence_after_sync();
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sX + kc * CHUNK, kc == 0);     // x -> cand
+        for (int kc = 0; kc < KC1; ++kc) chunk_mma(d_rc, sH + kc * CHUNK, false);       // r*h -> cand
+        tc::umma_commit_pair(bar(BAR_C_DONE));
+      }
+    }
+    __syncwarp();
+  } else {
+    // =============================== epilogue (warps 0-7, both CTAs; gru_w16_kernel's) ===============================
+    const int q = warp & 3, half = warp >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int ng = hw / 16;
+    const int g_begin = half * (ng / 2), g_end = half ? ng : ng / 2;
+    uint8_t* xt = smem_al + (sX - base);
+    uint8_t* ht = smem_al + (sH - base);
+    const bool leader = tid == 0;
+    int it = 0;
+    for (int pr = pair0; pr < n_pairs; pr += pair_stride, ++it) {
+      const int tile = 2 * pr + (int)rank;
+      const int64_t grow = (int64_t)tile * BM + r;
+      // ---- EPI-u
+      tc::mbar_wait(bar(BAR_U_DONE), it & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int g = g_begin; g < g_end; ++g) {
+        const int col0 = g * 16;
+        uint32_t au[16];
+        tc::tmem_ld16(t_lane + 256 + col0, au);
+        const uint8_t* hp = ht + (col0 >> 6) * CHUNK;
+        const int s0 = (col0 & 63) >> 3;
+        const uint4 h0 = *reinterpret_cast<const uint4*>(hp + sw_off(r, s0));
+        const uint4 h1 = *reinterpret_cast<const uint4*>(hp + sw_off(r, s0 + 1));
+        const uint32_t hb[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        float sb[16];
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bg + hw + col0) + k4);
+          sb[4 * k4] = b4.x; sb[4 * k4 + 1] = b4.y; sb[4 * k4 + 2] = b4.z; sb[4 * k4 + 3] = b4.w;
+        }
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float u = tc::rcp_approx(1.0f + tc::ex2_approx(-kLog2e * (__uint_as_float(au[k]) + sb[k])));
+          const uint32_t hbits = (k & 1) ? (hb[k >> 1] >> 16) : (hb[k >> 1] & 0xffffu);
+          au[k] = (uint32_t)__half_as_ushort(__float2half_rn(u)) | (hbits << 16);
+        }
+        tc::tmem_st16(t_lane + 256 + col0, au);
+      }
+      tc::tmem_st_wait();
+      // ---- EPI-r
+      tc::mbar_wait(bar(BAR_R_DONE), it & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int g = g_begin; g < g_end; ++g) {
+        const int col0 = g * 16;
+        uint32_t ar[16];
+        tc::tmem_ld16(t_lane + col0, ar);
+        uint8_t* hp = ht + (col0 >> 6) * CHUNK;
+        const int s0 = (col0 & 63) >> 3;
+        uint4* p0 = reinterpret_cast<uint4*>(hp + sw_off(r, s0));
+        uint4* p1 = reinterpret_cast<uint4*>(hp + sw_off(r, s0 + 1));
+        float hv[16];
+        unpack8(*p0, hv); unpack8(*p1, hv + 8);
+        float sb[16];
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bg + col0) + k4);
+          sb[4 * k4] = b4.x; sb[4 * k4 + 1] = b4.y; sb[4 * k4 + 2] = b4.z; sb[4 * k4 + 3] = b4.w;
+        }
+        tc::tmem_ld_wait();
+        float o[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          o[k] = tc::rcp_approx(1.0f + tc::ex2_approx(-kLog2e * (__uint_as_float(ar[k]) + sb[k]))) * hv[k];
+        *p0 = pack8(o);
+        *p1 = pack8(o + 8);
+      }
+      tc::fence_before_sync();
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive_cta0(bar(BAR_RH_FULL));
+      // ---- EPI-c
+      tc::mbar_wait(bar(BAR_C_DONE), it & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int g = g_begin; g < g_end; ++g) {
+        const int col0 = g * 16;
+        uint32_t ac[16], uh[16];
+        tc::tmem_ld16(t_lane + col0, ac);
+        tc::tmem_ld16(t_lane + 256 + col0, uh);
+        float sb[16];
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bc + col0) + k4);
+          sb[4 * k4] = b4.x; sb[4 * k4 + 1] = b4.y; sb[4 * k4 + 2] = b4.z; sb[4 * k4 + 3] = b4.w;
+        }
+        tc::tmem_ld_wait();
+        float o[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float c = fmaf(-2.0f, tc::rcp_approx(1.0f + tc::ex2_approx(2.0f * kLog2e * (__uint_as_float(ac[k]) + sb[k]))), 1.0f);
+          const float u = __half2float(__ushort_as_half((unsigned short)(uh[k] & 0xffffu)));
+          const float hv = __half2float(__ushort_as_half((unsigned short)(uh[k] >> 16)));
+          o[k] = fmaf(u, hv - c, c);
+        }
+        uint8_t* xp = xt + (col0 >> 6) * CHUNK;
+        const int s0 = (col0 & 63) >> 3;
+        *reinterpret_cast<uint4*>(xp + sw_off(r, s0)) = pack8(o);
+        *reinterpret_cast<uint4*>(xp + sw_off(r, s0 + 1)) = pack8(o + 8);
+        if (p.h_out && grow < p.N) {
+          float* dst = p.h_out + grow * p.h + col0;
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)
+            if (col0 + k4 * 4 < p.h)
+              *reinterpret_cast<float4*>(dst + k4 * 4) = make_float4(o[k4 * 4], o[k4 * 4 + 1], o[k4 * 4 + 2], o[k4 * 4 + 3]);
+        }
+      }
+      tc::fence_before_sync();
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive_cta0(bar(BAR_TMEM_FREE));
+      tc::named_bar_sync(1, 256);
+      if (leader) {
+        if (tile < p.n_tiles) {
+          for (int kc = 0; kc < KC1; ++kc) tc::tma_store_2d(&tmH, kc * BKH, tile * BM, sX + kc * CHUNK);
+          tc::tma_store_commit();
+          tc::tma_store_wait_read();
+        }
+        tc::mbar_arrive(bar(BAR_X_EMPTY));
+      }
+    }
+    if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc::fence_before_sync();
+  tc::cluster_sync_all();                                   // both CTAs are done with the pair's TMEM and barriers
+  if (warp == WARP_TMA) tc::tmem_dealloc_pair(tmem_base, 512);
+}
+
+}  // namespace gw16x2
+
+// =========================================================================================
 bool ggnn_w16_supported(const ggnn_ctx* ctx) {
   return ctx->h > 128 && ctx->h % 4 == 0 && ctx->hw16 >= 192 && ctx->hw16 <= 512;
 }
@@ -858,9 +1137,11 @@ int ggnn_w16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t s
                                    w16::slice_width(2 * hw, 2 * hw)));
     GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16, ctx->Wct_f16, hw, 2 * hw, w16::BKH,
                                    w16::slice_width(2 * hw, hw)));
-    if (hw <= 256) {     // fused GRU kernel: [hw n x 64 k] chunks
+    if (hw <= 256) {     // fused GRU kernel: [hw n x 64 k] chunks; CTA pairs: [hw/2 n x 64 k] half chunks
       GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wg16f, ctx->Wgt_f16, 2 * hw, 2 * hw, w16::BKH, hw));
       GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16f, ctx->Wct_f16, hw, 2 * hw, w16::BKH, hw));
+      GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wg16h, ctx->Wgt_f16, 2 * hw, 2 * hw, w16::BKH, hw / 2));
+      GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16h, ctx->Wct_f16, hw, 2 * hw, w16::BKH, hw / 2));
     }
   }
   return GGNN_OK;
@@ -947,6 +1228,17 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     gw16::params g{};
     g.bg = ctx->bg_w16; g.bc = ctx->bc_w16; g.h_out = last_step ? h_out : nullptr;
     g.N = plan.N; g.h = h; g.hw = hw; g.n_tiles = n_row_tiles;
+    static const bool pair = getenv("GGNN_GRU_2CTA") != nullptr;     // A-B switch
+    if (pair && hw == 256) {
+      GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_W16_0 + 4, gw16x2::gru_w16x2_kernel, gw16x2::SMEM_BYTES);
+      const int n_pairs = (n_row_tiles + 1) / 2;
+      const int clusters = n_pairs < ctx->sm_count / 2 ? n_pairs : ctx->sm_count / 2;
+      prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+      gw16x2::gru_w16x2_kernel<<<2 * clusters, gw16x2::NTHREADS, gw16x2::SMEM_BYTES, st>>>(g, tmActs, tmState, ctx->tm_Wg16h,
+                                                                                           ctx->tm_Wc16h);
+      GGNN_LAUNCHED(ctx);
+      return GGNN_OK;
+    }
     const int grid = n_row_tiles < ctx->sm_count ? n_row_tiles : ctx->sm_count;
     prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
     gw16::gru_w16_kernel<<<grid, gw16::NTHREADS, gw16::SMEM_BYTES, st>>>(g, tmActs, tmState, ctx->tm_Wg16f, ctx->tm_Wc16f);
