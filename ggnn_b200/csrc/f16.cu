@@ -84,7 +84,8 @@ namespace msg16 {
 constexpr int ASTAGES = 4;
 constexpr int A_BYTES = TILE16_BYTES;           // 32 KB per stage
 constexpr int W_BYTES = TILE16_BYTES;           // 32 KB
-constexpr int O_BYTES = TILE16_BYTES;           // 32 KB FP16 staging (two 64-column boxes)
+constexpr int O_BYTES = 2 * TILE16_BYTES;       // 2 x 32 KB FP16 staging (two 64-column boxes each): the epilogue of tile i+1
+                                                // fills one buffer while the TMA store of tile i still reads the other
 constexpr int NPROD = 128;
 constexpr int WARP_MMA = 4;
 constexpr int WARP_EPI0 = 5;
@@ -228,7 +229,6 @@ msg_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmW,
     const int r = q * 32 + lane;
     const int etid = tid - WARP_EPI0 * 32;
     const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
-    uint8_t* orow = smem_al + (sO - base) + r * 128;
     int cur_type = -1;
     for (int i = 0; i < my_tiles; ++i) {
       const int tile = t_begin + i, buf = i & 1;
@@ -240,8 +240,10 @@ msg_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmW,
       }
       tc::mbar_wait(bar(BAR_ACC_FULL + buf), (i >> 1) & 1);
       tc::fence_after_sync();
-      if (etid == 0) tc::tma_store_wait_read();
+      if (etid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store of tile i-2 has read this buffer
       tc::named_bar_sync(1, 128);
+      const uint32_t so_buf = sO + (uint32_t)(i & 1) * TILE16_BYTES;
+      uint8_t* orow = smem_al + (so_buf - base) + r * 128;
 #pragma unroll
       for (int cc = 0; cc < 4; ++cc) {
         uint32_t acc[32];
@@ -270,8 +272,8 @@ msg_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmW,
       tc::fence_proxy_async();
       tc::named_bar_sync(1, 128);
       if (etid == 0) {
-        tc::tma_store_2d(&tmOut, 0, tile * BM, sO);
-        tc::tma_store_2d(&tmOut, 64, tile * BM, sO + CHUNK_BYTES);
+        tc::tma_store_2d(&tmOut, 0, tile * BM, so_buf);
+        tc::tma_store_2d(&tmOut, 64, tile * BM, so_buf + CHUNK_BYTES);
         tc::tma_store_commit();
       }
     }
