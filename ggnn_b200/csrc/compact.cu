@@ -103,6 +103,39 @@ bitmask_f32_kernel(const float4* __restrict__ adj, int64_t n4, uint32_t* __restr
   }
 }
 
+// uint8 adjacency, 256-bit streaming loads: 32 bytes per thread -> one whole word of the bitmask, no shuffles.
+// n32 = number of words.  32-byte aligned input.
+__global__ void __launch_bounds__(P1_THREADS)
+bitmask_u8_v8_kernel(const uint8_t* __restrict__ adj, int64_t n32, uint32_t* __restrict__ bits) {
+  const int64_t stride = (int64_t)gridDim.x * P1_THREADS;
+  const int64_t iters = (n32 + stride * P1_UNROLL - 1) / (stride * P1_UNROLL);
+  int64_t i0 = (int64_t)blockIdx.x * P1_THREADS + threadIdx.x;
+  for (int64_t it = 0; it < iters; ++it, i0 += stride * P1_UNROLL) {
+    f32x8 x[P1_UNROLL];
+#pragma unroll
+    for (int u = 0; u < P1_UNROLL; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < n32) x[u] = ldg_stream_f8(reinterpret_cast<const float*>(adj + i * 32));
+      else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) x[u].u[q] = 0u;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < P1_UNROLL; ++u) {
+      const int64_t i = i0 + u * stride;
+      uint32_t m = 0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+#pragma unroll
+        for (int by = 0; by < 4; ++by)
+          m |= ((x[u].u[q] >> (8 * by)) & 0xffu) ? (1u << (q * 4 + by)) : 0u;
+      }
+      if (i < n32) bits[i] = m;
+    }
+  }
+}
+
 // 16 bytes per thread -> 16 bits; 2 adjacent lanes -> one word.  n16 = total / 16.
 __global__ void __launch_bounds__(P1_THREADS)
 bitmask_u8_kernel(const uint4* __restrict__ adj, int64_t n16, uint32_t* __restrict__ bits) {
@@ -246,7 +279,12 @@ int ggnn_compact_bitmask(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t 
       if (aligned) {
         vec_words = total / 32;
         int64_t n16 = vec_words * 2;
-        if (n16 > 0) {
+        if (n16 > 0 && (reinterpret_cast<uintptr_t>(adj) & 31u) == 0) {      // 256-bit loads
+          int64_t want = ceil_div64(vec_words, (int64_t)P1_THREADS * P1_UNROLL);
+          int grid = (int)(want < (int64_t)ctx->sm_count * 64 ? want : (int64_t)ctx->sm_count * 64);
+          bitmask_u8_v8_kernel<<<grid, P1_THREADS, 0, st>>>(reinterpret_cast<const uint8_t*>(adj), vec_words, bits);
+          GGNN_LAUNCHED(ctx);
+        } else if (n16 > 0) {
           int64_t want = ceil_div64(n16, (int64_t)P1_THREADS * P1_UNROLL);
           int grid = (int)(want < (int64_t)ctx->sm_count * 16 ? want : (int64_t)ctx->sm_count * 16);
           bitmask_u8_kernel<<<grid, P1_THREADS, 0, st>>>(
