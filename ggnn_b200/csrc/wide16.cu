@@ -4,10 +4,12 @@
 //   MSG    M[r, :]  = f16(h[src(r), :]) @ f16(W[type]) + B[type]                      -> FP16 rows
 //   GATES  g = sigmoid([x, h] @ Wg + bg);  rh = f16(g[:, :h] * h);  u = f16(g[:, h:])
 //   CAND   c = tanh([x, rh] @ Wc + bc);    h' = c + u * (h - c)                        -> FP16 state (+ FP32 result)
-// run on ONE persistent, warp-specialised tcgen05 kernel (kind::f16, FP32 accumulators in TMEM).
-// The hidden size is padded to hw = a multiple of 64 (one 128-byte swizzle row of FP16).
+// run on ONE persistent, warp-specialised tcgen05 kernel (wgemm16_kernel; kind::f16, FP32 accumulators in TMEM).
+// The hidden size is padded to hw = a multiple of 64 (one 128-byte swizzle row of FP16).  For hw <= 256 the GRU half
+// (GATES + CAND) runs as one fused kernel instead (gru_w16_kernel below; gru_w16x2_kernel is its CTA-pair variant).
+// With a training tape the unfused kernels also store x, r, u, c of the step as FP32 rows (forward of BASELINE config 5).
 //
-// Tiling: the weight matrix is cut into column slices of NW <= 256 output columns whose K-major FP16
+// Tiling of wgemm16_kernel: the weight matrix is cut into column slices of NW <= 256 output columns whose K-major FP16
 // panel [NW x K] fits 128 KB of shared memory.  A CTA owns a contiguous range of (slice, 128-row tile)
 // work items, slice-major, so the panel stays RESIDENT while the CTA streams row tiles under it: only
 // the activations move through the 4 x 16 KB chunk ring (one [128 x 64] FP16 chunk per stage, by TMA
