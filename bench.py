@@ -114,11 +114,10 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------
 def cpu_sample(n_graphs, seed=7):
     from ggnn_b200 import synth
-    from oracle import ggnn_oracle as O
     tri = synth.random_trees(n_graphs, V - 1, E, seed=seed)
     adj = synth.dense_adjacency(tri, V, E)
     h0 = (torch.rand(n_graphs, V, H, generator=torch.Generator().manual_seed(seed)) - 0.5) * 0.2
-    return h0, adj, O.make_weights(TWO_E, H, 0)
+    return h0, adj, synth.make_weights(TWO_E, H, 0)
 
 
 def cpu_baseline(target_seconds=12.0):
@@ -180,7 +179,6 @@ def run_gpu(args):
     import torch.distributed as dist
     import ggnn_b200
     from ggnn_b200 import synth
-    from oracle import ggnn_oracle as O            # weights generator only (same seed as CPU arm)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -194,7 +192,7 @@ def run_gpu(args):
 
     graphs_rank = args.graphs // world
     pool = min(args.pool, graphs_rank)
-    w = ggnn_b200.from_dict(O.make_weights(TWO_E, H, 0))
+    w = ggnn_b200.from_dict(synth.make_weights(TWO_E, H, 0))
     prop = ggnn_b200.Propagator(w, dev)
     precision = args.precision
 
@@ -453,8 +451,7 @@ def c5_inputs(n_graphs, seed, device):
 def run_c5(args):
     import torch.distributed as dist
     import ggnn_b200
-    from ggnn_b200 import dist as gdist
-    from oracle import ggnn_oracle as O
+    from ggnn_b200 import dist as gdist, synth
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -464,7 +461,7 @@ def run_c5(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     Hc, Tc, per_gpu = 400, 4, args.c5_graphs
-    wd = O.make_weights(TWO_E, Hc, 0)
+    wd = synth.make_weights(TWO_E, Hc, 0)
     prop = ggnn_b200.Propagator(ggnn_b200.from_dict(wd), dev)
     h0, edges, d, N = c5_inputs(per_gpu, 1000 + rank, dev)
     grads = torch.zeros(prop.grad_floats, device=dev)
@@ -563,7 +560,6 @@ def run_c4(args):
     import torch.distributed as dist
     import ggnn_b200
     from ggnn_b200 import synth
-    from oracle import ggnn_oracle as O
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -574,7 +570,7 @@ def run_c4(args):
     dev = torch.device("cuda", local)
     Vn, CH, BASE, Hc, Tc = 4096, 8, 32768, 256, 8
     per_gpu = args.c4_graphs
-    wd = O.make_weights(CH, Hc, 0)
+    wd = synth.make_weights(CH, Hc, 0)
     prop = ggnn_b200.Propagator(ggnn_b200.from_dict(wd), dev)
     edges = synth.random_multigraph(per_gpu, Vn, BASE, CH // 2, seed=1000 + rank).to(dev)
     gen = torch.Generator(device=dev).manual_seed(1 + rank)

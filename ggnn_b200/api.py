@@ -21,7 +21,11 @@ _cache = {}          # (thread id, device index, id(weights object)) -> (weights
 
 def get_propagator(weights, device=None) -> Propagator:
     """Propagator for these weights on this device, cached per host thread (a ctx is not
-    thread-safe).  ``weights``: path to a reference .pickle, its dict, or GGNNWeights."""
+    thread-safe).  ``weights``: path to a reference .pickle, its dict, or GGNNWeights.
+    The cache key is the path or the identity of the object: weights are treated as IMMUTABLE.  Mutating
+    the arrays of a cached dict in place (or rewriting the pickle) is not seen; and a Propagator whose
+    ``optimizer_step`` has run holds newer weights than ``Propagator.weights`` (``get_weights()`` returns
+    the current ones).  Build a new Propagator for new weights."""
     if isinstance(weights, Propagator):
         return weights
     if not torch.cuda.is_available():
@@ -150,7 +154,7 @@ def _back(out: torch.Tensor, kind: str):
 def compute_final_node_representations(initial_node_representations, adjacency_matrix,
                                        node_mask=None, weights=None, num_timesteps: Optional[int] = None,
                                        fixed_ts: Optional[int] = None, precision: str = "fp32",
-                                       skip_padded: bool = False):
+                                       skip_padded: bool = False, validate: bool = False):
     """T steps of GGNN propagation (message transform per edge type + bias, aggregation over
     the adjacency, GRU update) -- reference chem_tensorflow_dense.py:312-340, 391-437.
 
@@ -162,7 +166,10 @@ def compute_final_node_representations(initial_node_representations, adjacency_m
     weights                      : path to a reference .pickle, its dict, GGNNWeights, or Propagator
     num_timesteps                : defaults to the checkpoint's params['num_timesteps']
     fixed_ts                     : k -> use edge_weights_fixed / edge_biases_fixed for k steps
-    precision                    : "fp32" (strict) or "tf32" (tensor cores, FP32 accumulate)
+    precision                    : "fp32" (strict, <= 1e-5 norm-wise), "tf32" or "f16" (tensor cores: TF32 operands /
+                                   FP16 containers of the same 11-bit significand, FP32 accumulate, <= 2e-3)
+    validate                     : True -> raise ValueError unless every adjacency value is exactly 0 or 1 (the
+                                   path uses the adjacency as an edge set; see Propagator.propagate_dense)
     Returns float32 [b, v, h] of the same kind (numpy / torch cpu / torch cuda) as the input states.
     """
     if weights is None:
@@ -174,6 +181,12 @@ def compute_final_node_representations(initial_node_representations, adjacency_m
     if isinstance(adjacency_matrix, np.ndarray) and adjacency_matrix.dtype not in (np.float32, np.uint8):
         adjacency_matrix = adjacency_matrix.astype(np.float32)     # the placeholder is tf.float32
     host = lambda x: isinstance(x, np.ndarray) or (isinstance(x, torch.Tensor) and x.device.type == "cpu")
+    if validate:
+        a = adjacency_matrix
+        ok = bool(((a == 0) | (a == 1)).all())
+        if not ok:
+            raise ValueError("adjacency_matrix holds values other than 0 and 1: the path implements the reference's "
+                             "0/1 adjacency (graph_to_adj_mat_bd); weighted adjacencies are not supported")
     if host(initial_node_representations) and host(adjacency_matrix) and not skip_padded:
         kind = "numpy" if isinstance(initial_node_representations, np.ndarray) else "cpu"
         h0 = _as_host_tensor(initial_node_representations, np.float32)

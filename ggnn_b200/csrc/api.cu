@@ -611,15 +611,14 @@ extern "C" int ggnn_optimizer_step(ggnn_ctx* ctx, int slot, const float* grads, 
   const int h = ctx->h, two_e = ctx->two_e;
   const int64_t n = (int64_t)ggnn_grad_count(two_e, h);
   if (ex->adam_n != n) {                      // (re)create zeroed moments
-    GGNN_TRY(arena_reserve(ctx, 6, (size_t)(2 * n + 64) * 4, st));
-    GGNN_CUDA(ctx, cudaMemsetAsync(ex->ar[6].p, 0, (size_t)(2 * n + 64) * 4, st));
+    GGNN_TRY(arena_reserve(ctx, 6, (size_t)(2 * n + 6 * GGNN_SUMSQ_SLOT) * 4, st));
+    GGNN_CUDA(ctx, cudaMemsetAsync(ex->ar[6].p, 0, (size_t)(2 * n + 6 * GGNN_SUMSQ_SLOT) * 4, st));
     ex->adam_n = n;
     ex->adam_t = 0;
   }
   float* m = reinterpret_cast<float*>(ex->ar[6].p);
   float* v = m + n;
-  float* norms = v + n;                       // 6 slots
-  GGNN_CUDA(ctx, cudaMemsetAsync(norms, 0, 8 * sizeof(float), st));
+  float* norms = v + n;                       // 6 slots of per-block partial sums
   const int64_t t = ++ex->adam_t;
   const float lr_t = lr * sqrtf(1.f - powf(beta2, (float)t)) / (1.f - powf(beta1, (float)t));
   ggnn_edge_weights& ew = ctx->edge[slot];
@@ -627,7 +626,7 @@ extern "C" int ggnn_optimizer_step(ggnn_ctx* ctx, int slot, const float* grads, 
   const int64_t sizes[6] = {(int64_t)two_e * h * h, (int64_t)two_e * h, (int64_t)4 * h * h, 2 * h, (int64_t)2 * h * h, h};
   int64_t off = 0;
   for (int i = 0; i < 6; ++i) {
-    GGNN_TRY(ggnn_adam_segment(ctx, params[i], grads + off, m + off, v + off, sizes[i], norms + i, clip_norm, lr_t,
+    GGNN_TRY(ggnn_adam_segment(ctx, params[i], grads + off, m + off, v + off, sizes[i], norms + (size_t)i * GGNN_SUMSQ_SLOT, clip_norm, lr_t,
                                beta1, beta2, eps, st));
     off += sizes[i];
   }

@@ -38,7 +38,8 @@ __device__ __forceinline__ int block_excl_scan(int x, int* total) {
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-tile_reduce_kernel(const int32_t* __restrict__ in, int64_t n, int32_t* __restrict__ sums) {
+tile_reduce_kernel(const int32_t* __restrict__ in, int64_t n, int32_t* __restrict__ sums,
+                   unsigned long long* __restrict__ total64) {
   const int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
   int acc = 0;
 #pragma unroll
@@ -48,7 +49,13 @@ tile_reduce_kernel(const int32_t* __restrict__ in, int64_t n, int32_t* __restric
   }
   int total;
   block_excl_scan(acc, &total);
-  if (threadIdx.x == 0) sums[blockIdx.x] = total;
+  if (threadIdx.x == 0) {
+    sums[blockIdx.x] = total;
+    // the grand total is carried in 64 bits (integer atomics: order-independent), so a sum >= 2^31 is
+    // REPORTED instead of wrapping silently; the int32 prefix array is invalid in that case and callers
+    // check the total before using it
+    if (total64) atomicAdd(total64, (unsigned long long)(unsigned)total);
+  }
 }
 
 // offsets == nullptr: single tile (n <= SCAN_TILE).  total_out (int64) optional.
@@ -105,12 +112,13 @@ int ggnn_exclusive_scan_i32(ggnn_ctx* ctx, const int32_t* in, int32_t* out, int6
   if (tiles > 0x7fffffffLL) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "scan too large");
   if (tmp_elems < align_up((size_t)tiles, 64)) GGNN_FAIL(ctx, GGNN_E_CAPACITY, "scan tmp too small");
   int32_t* sums = tmp;
-  tile_reduce_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(in, n, sums);
+  if (total_out_dev) GGNN_CUDA(ctx, cudaMemsetAsync(total_out_dev, 0, sizeof(int64_t), st));
+  tile_reduce_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(in, n, sums, reinterpret_cast<unsigned long long*>(total_out_dev));
   GGNN_LAUNCHED(ctx);
   GGNN_TRY(ggnn_exclusive_scan_i32(ctx, sums, sums, tiles, nullptr,
                                    tmp + align_up((size_t)tiles, 64),
                                    tmp_elems - align_up((size_t)tiles, 64), st));
-  tile_scan_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(in, out, n, sums, total_out_dev);
+  tile_scan_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(in, out, n, sums, nullptr);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

@@ -47,13 +47,14 @@ sgemm_kernel(const sgemm_params p) {
   __shared__ __align__(16) float Bs[2][BK][BN];
 
   const int tid = threadIdx.x;
-  const int64_t row0 = (int64_t)blockIdx.y * BM;
-  const int col0 = blockIdx.x * BN;
+  // row tiles ride on gridDim.x (limit 2^31-1), column tiles on gridDim.y: a 65 536 x 128-node batch has 65 536 row tiles
+  const int64_t row0 = (int64_t)blockIdx.x * BM;
+  const int col0 = blockIdx.y * BN;
   const float* Bmat = p.Bmat;
   const float* bias = p.bias;
   if (MODE == MODE_MSG) {
-    if ((int)blockIdx.y >= *p.n_tiles) return;
-    const int type = p.tile_type[blockIdx.y];
+    if ((int)blockIdx.x >= *p.n_tiles) return;
+    const int type = p.tile_type[blockIdx.x];
     Bmat += (size_t)type * p.K1 * p.N;
     if (bias) bias += (size_t)type * p.N;
   }
@@ -267,7 +268,7 @@ int ggnn_sgemm_concat(ggnn_ctx* ctx, const float* A1, const float* A2, int K1, i
   sgemm_params p{};
   p.A1 = A1; p.A2 = A2; p.gather = nullptr; p.K1 = K1; p.K2 = K2; p.lda = lda;
   p.Bmat = B; p.bias = bias; p.N = N; p.M = M; p.out0 = out; p.h = N;
-  dim3 grid((N + BN - 1) / BN, (unsigned)ceil_div64(M, BM));
+  dim3 grid((unsigned)ceil_div64(M, BM), (N + BN - 1) / BN);
   sgemm_kernel<MODE_PLAIN><<<grid, NT, 0, st>>>(p);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
@@ -288,7 +289,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.M = plan.max_tiles * GGNN_TILE_M;
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg; p.h = h;
-    dim3 grid((h + BN - 1) / BN, (unsigned)plan.max_tiles);
+    dim3 grid((unsigned)plan.max_tiles, (h + BN - 1) / BN);
     sgemm_kernel<MODE_MSG><<<grid, NT, 0, st>>>(p);
     GGNN_LAUNCHED(ctx);
   }
@@ -301,7 +302,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.K1 = h; p.K2 = h; p.lda = h;
     p.Bmat = ctx->Wg; p.bias = ctx->bg; p.N = 2 * h; p.M = plan.N;
     p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state; p.h = h; p.out_r = bufs.tape_r;
-    dim3 grid((2 * h + BN - 1) / BN, mt);
+    dim3 grid(mt, (2 * h + BN - 1) / BN);
     sgemm_kernel<MODE_GATES><<<grid, NT, 0, st>>>(p);
     GGNN_LAUNCHED(ctx);
   }
@@ -312,7 +313,7 @@ int ggnn_step_fp32(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_st
     p.K1 = h; p.K2 = h; p.lda = h;
     p.Bmat = ctx->Wc; p.bias = ctx->bc; p.N = h; p.M = plan.N;
     p.out0 = h_state; p.ubuf = bufs.u; p.h = h; p.out_c = bufs.tape_c;
-    dim3 grid((h + BN - 1) / BN, mt);
+    dim3 grid(mt, (h + BN - 1) / BN);
     sgemm_kernel<MODE_CAND><<<grid, NT, 0, st>>>(p);
     GGNN_LAUNCHED(ctx);
   }

@@ -70,16 +70,17 @@ __global__ void __launch_bounds__(NTHREADS)
 gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
   extern __shared__ uint8_t smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t row0 = (int64_t)blockIdx.y * BM;
-  const int n0 = blockIdx.x * BN;
+  // row tiles on gridDim.x (limit 2^31-1), column tiles on gridDim.y
+  const int64_t row0 = (int64_t)blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
   const int n_tile = min(BN, p.Np - n0);              // multiple of 32
 
   const float* Bt = p.Bt;
   const float* bias = p.bias;
   const bool grouped = MODE == MODE_MSG || (MODE == MODE_NT && p.tile_type != nullptr);
   if (grouped) {
-    if ((int)blockIdx.y >= *p.n_tiles) return;        // uniform across the CTA
-    const int type = p.tile_type[blockIdx.y];
+    if ((int)blockIdx.x >= *p.n_tiles) return;        // uniform across the CTA
+    const int type = p.tile_type[blockIdx.x];
     Bt += (size_t)type * p.Np * p.Kp;
     if (bias) bias += (size_t)type * p.h;
   }
@@ -127,7 +128,7 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
       }
     }
     int b_row = n0;
-    if (grouped) b_row += p.tile_type[blockIdx.y] * p.Np;
+    if (grouped) b_row += p.tile_type[blockIdx.x] * p.Np;
     uint32_t a_off[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -362,7 +363,7 @@ int launch(ggnn_ctx* ctx, const tparams& p_in, const CUtensorMap& tm, unsigned m
   if (p.lda1 == 0) p.lda1 = p.h;
   if (p.lda2 == 0) p.lda2 = p.h;
   GGNN_ENSURE_SMEM(ctx, GGNN_ATTR_TF32_GEMM0 + MODE, gemm_tf32_kernel<MODE>, SMEM_BYTES);
-  dim3 grid((p.Np + BN - 1) / BN, mtiles);
+  dim3 grid(mtiles, (p.Np + BN - 1) / BN);
   gemm_tf32_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(p, tm);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;

@@ -45,7 +45,8 @@ size_t ggnn_grad_count(int two_e, int h);
 int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scratch& s,
                        const float* d_hT, float* d_h0, float* grads, cudaStream_t st);
 
-// N4: one variable of the flat buffer: clip_by_norm(grad, clip) then Adam; *sumsq_slot (zeroed by the caller)
-// receives ||grad||^2
+// N4: one variable of the flat buffer: clip_by_norm(grad, clip) then Adam; `partials` (GGNN_SUMSQ_SLOT floats)
+// receives the per-block partial sums of ||grad||^2, reduced in a fixed order (bit-repeatable clip scale)
+#define GGNN_SUMSQ_SLOT 2048
 int ggnn_adam_segment(ggnn_ctx* ctx, float* param, const float* grad, float* m, float* v, int64_t n,
-                      float* sumsq_slot, float clip, float lr_t, float b1, float b2, float eps, cudaStream_t st);
+                      float* partials, float clip, float lr_t, float b1, float b2, float eps, cudaStream_t st);

@@ -42,12 +42,12 @@ nt_kernel(const nt_params p) {
   __shared__ __align__(16) float As[2][BK][BM + 4];
   __shared__ __align__(16) float Bs[2][BK][BN + 4];
   const int tid = threadIdx.x;
-  const int64_t row0 = (int64_t)blockIdx.y * BM;
-  const int col0 = blockIdx.x * BN;
+  const int64_t row0 = (int64_t)blockIdx.x * BM;          // row tiles on gridDim.x (limit 2^31-1)
+  const int col0 = blockIdx.y * BN;
   const float* Bm = p.B;
   if (p.tile_type) {
-    if ((int)blockIdx.y >= *p.n_tiles) return;
-    Bm += (size_t)p.tile_type[blockIdx.y] * p.b_type_stride;
+    if ((int)blockIdx.x >= *p.n_tiles) return;
+    Bm += (size_t)p.tile_type[blockIdx.x] * p.b_type_stride;
   }
   const int K = p.K1 + p.K2;
   const int lrow = tid >> 1, lk4 = (tid & 1) * 4;        // both loaders: row = tid/2, 4 consecutive k
@@ -240,12 +240,12 @@ colsum_kernel(const float* __restrict__ D, int ldd, const int32_t* __restrict__ 
               const int32_t* __restrict__ n_tiles, int out_type_stride) {
   __shared__ float4 part[8][32];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int64_t r_begin = (int64_t)blockIdx.y * GGNN_TILE_M;
+  const int64_t r_begin = (int64_t)blockIdx.x * GGNN_TILE_M;   // row tiles on gridDim.x
   if (tile_type) R = (int64_t)(*n_tiles) * GGNN_TILE_M;
   int64_t r_end = r_begin + GGNN_TILE_M;
   if (r_end > R) r_end = R;
   if (r_begin >= r_end) return;
-  const int n = blockIdx.x * 128 + tx * 4;                     // N % 4 == 0
+  const int n = blockIdx.y * 128 + tx * 4;                     // N % 4 == 0
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (n < N) {
 #pragma unroll 4
@@ -399,7 +399,7 @@ namespace {
 
 int launch_nt(ggnn_ctx* ctx, const nt_params& p, unsigned mtiles, cudaStream_t st) {
   if (mtiles == 0 || p.N == 0) return GGNN_OK;
-  dim3 grid((p.N + BN - 1) / BN, mtiles);
+  dim3 grid(mtiles, (p.N + BN - 1) / BN);
   nt_kernel<<<grid, NT, 0, st>>>(p);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
@@ -416,7 +416,7 @@ int launch_tn(ggnn_ctx* ctx, const tn_params& p, int64_t rows_bound, cudaStream_
 int launch_colsum(ggnn_ctx* ctx, const float* D, int ldd, const int32_t* map, int N, int64_t R,
                   float* out, const int32_t* tile_type, const int32_t* n_tiles, int stride, cudaStream_t st) {
   if (R <= 0) return GGNN_OK;
-  dim3 grid((N + 127) / 128, (unsigned)ceil_div64(R, GGNN_TILE_M));
+  dim3 grid((unsigned)ceil_div64(R, GGNN_TILE_M), (N + 127) / 128);
   colsum_kernel<<<grid, 256, 0, st>>>(D, ldd, map, N, R, out, tile_type, n_tiles, stride);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
@@ -571,28 +571,41 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
 // chem_tensorflow.py:483-506: AdamOptimizer(lr, beta1=0.9, beta2=0.999), tf.clip_by_norm per variable)
 namespace {
 
+// Fixed-order two-stage norm: every block writes ONE partial (no float atomics), and every block of the Adam kernel
+// re-reduces the same partials in the same order, so the clip scale is bit-identical from run to run and from rank
+// to rank (the all-reduced gradient is) and data-parallel replicas cannot drift apart.
+constexpr int SUMSQ_MAX_BLOCKS = 2048;
+
+__device__ __forceinline__ float block_sum_fixed(float s, float* ws /* [8] */) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) t += ws[w];
+  return t;
+}
+
 __global__ void __launch_bounds__(256)
-sumsq_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ out) {
+sumsq_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ partial) {
+  __shared__ float ws[8];
   float s = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     s = fmaf(g[i], g[i], s);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  __shared__ float ws[8];
-  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float t = 0.f;
-    for (int w = 0; w < 8; ++w) t += ws[w];
-    atomicAdd(out, t);
-  }
+  const float t = block_sum_fixed(s, ws);
+  if (threadIdx.x == 0) partial[blockIdx.x] = t;
 }
 
 // g_c = g * clip / max(||g||, clip);  m, v, p updated in place (TF1 AdamOptimizer: eps outside the sqrt)
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-            int64_t n, const float* __restrict__ sumsq, float clip, float lr_t, float b1, float b2, float eps) {
-  const float norm = sqrtf(*sumsq);
+            int64_t n, const float* __restrict__ partial, int n_partial, float clip, float lr_t, float b1, float b2,
+            float eps) {
+  __shared__ float ws[8];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n_partial; i += 256) s += partial[i];
+  const float norm = sqrtf(block_sum_fixed(s, ws));
   const float scale = clip > 0.f ? clip / fmaxf(norm, clip) : 1.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float gc = g[i] * scale;
@@ -606,12 +619,16 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
 }  // namespace
 
 int ggnn_adam_segment(ggnn_ctx* ctx, float* param, const float* grad, float* m, float* v, int64_t n,
-                      float* sumsq_slot, float clip, float lr_t, float b1, float b2, float eps, cudaStream_t st) {
+                      float* partials /* [GGNN_SUMSQ_SLOT] */, float clip, float lr_t, float b1, float b2, float eps,
+                      cudaStream_t st) {
   if (n <= 0 || !param) return GGNN_OK;
-  const int grid = (int)(ceil_div64(n, 256) < (int64_t)ctx->sm_count * 8 ? ceil_div64(n, 256) : (int64_t)ctx->sm_count * 8);
-  sumsq_kernel<<<grid, 256, 0, st>>>(grad, n, sumsq_slot);
+  int64_t want = ceil_div64(n, 256);
+  if (want > (int64_t)ctx->sm_count * 8) want = (int64_t)ctx->sm_count * 8;
+  const int grid = (int)(want < SUMSQ_MAX_BLOCKS ? want : SUMSQ_MAX_BLOCKS);
+  static_assert(SUMSQ_MAX_BLOCKS == GGNN_SUMSQ_SLOT, "partial-sum slot size");
+  sumsq_kernel<<<grid, 256, 0, st>>>(grad, n, partials);
   GGNN_LAUNCHED(ctx);
-  adam_kernel<<<grid, 256, 0, st>>>(param, grad, m, v, n, sumsq_slot, clip, lr_t, b1, b2, eps);
+  adam_kernel<<<grid, 256, 0, st>>>(param, grad, m, v, n, partials, grid, clip, lr_t, b1, b2, eps);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

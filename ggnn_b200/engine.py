@@ -177,11 +177,18 @@ class Propagator:
 
     def propagate_dense(self, h0: torch.Tensor, adj: torch.Tensor, num_timesteps=None, fixed_ts=None,
                         precision: str = "fp32", out: Optional[torch.Tensor] = None,
-                        save_tape: bool = False) -> torch.Tensor:
+                        save_tape: bool = False, validate: bool = False) -> torch.Tensor:
+        """``validate=True`` checks that every adjacency value is exactly 0 or 1 (one extra pass over the tensor):
+        the path treats the adjacency as an edge SET (`A != 0`), which equals the reference's
+        ``tf.matmul(adj, m)`` (chem_tensorflow_dense.py:428) only for the 0/1 matrices graph_to_adj_mat_bd
+        builds; a weighted or normalised adjacency would give different numbers and is refused."""
         if precision not in _PREC:
             raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
         h0 = self._state(h0, 3)
         adj, dt = self._adj(adj)
+        if validate and adj.numel() and not bool(((adj == 0) | (adj == 1)).all()):
+            raise ValueError("adjacency_matrix holds values other than 0 and 1: the path implements the reference's "
+                             "0/1 adjacency (graph_to_adj_mat_bd); weighted adjacencies are not supported")
         b, v, h = h0.shape
         if adj.shape[0] != b or adj.shape[2] != v or adj.shape[1] != self.weights.two_e:
             raise ValueError(f"adjacency {tuple(adj.shape)} does not match states {tuple(h0.shape)} "

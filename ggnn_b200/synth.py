@@ -10,7 +10,30 @@ from __future__ import annotations
 import math
 from typing import Optional
 
+import numpy as np
 import torch
+
+
+def glorot_init(rng, shape):
+    """The reference's initialiser (utils.py:11-14), with a local Generator."""
+    r = np.sqrt(6.0 / (shape[-2] + shape[-1]))
+    return rng.uniform(low=-r, high=r, size=shape).astype(np.float32)
+
+
+def make_weights(two_e: int, h: int, seed: int = 0, bias_std: float = 0.05) -> dict:
+    """Synthetic parameters in the reference's shapes (chem_tensorflow_dense.py:202-212, 237-241; TF
+    GRUCell init: gate bias 1.0, candidate bias 0).  Edge biases are N(0, bias_std) rather than the
+    reference's zeros so that the per-edge bias rule is exercised.  Same stream of
+    draws as the test oracle's generator, so a seed names the same weights on both sides."""
+    rng = np.random.default_rng(seed)
+    return {
+        "edge_weights": glorot_init(rng, (two_e, h, h)),
+        "edge_biases": (rng.standard_normal((two_e, 1, h)) * bias_std).astype(np.float32),
+        "gru_gate_kernel": glorot_init(rng, (2 * h, 2 * h)),
+        "gru_gate_bias": np.ones((2 * h,), np.float32),
+        "gru_cand_kernel": glorot_init(rng, (2 * h, h)),
+        "gru_cand_bias": np.zeros((h,), np.float32),
+    }
 
 
 def zipf_probs(n: int, s: float = 1.1) -> torch.Tensor:

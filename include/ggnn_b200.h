@@ -68,10 +68,12 @@ extern "C" {
 #define GGNN_SLOT_MAIN   0
 #define GGNN_SLOT_FIXED  1
 
-/* flags */
-#define GGNN_FLAG_LOOP_ORDER  1u  /* reserved: summation order of compute_timestep_normal */
+/* flags.  (There is no flag for compute_timestep_normal, chem_tensorflow_dense.py:350-389: a node's
+ * messages are always summed in ascending (channel, source) order, which IS the loop form's accumulation
+ * order, so both reference forms map to the same call; tests hold the result to the goldens of both.) */
 #define GGNN_FLAG_SAVE_TAPE   2u  /* training forward: keep every step's activations in the ctx for
-                                   * ggnn_propagate_backward (GGNN_PREC_FP32 only, one chunk)      */
+                                   * ggnn_propagate_backward.  All three arithmetic modes (GGNN_PREC_F16
+                                   * needs a hidden size in (128, 512]); the batch must fit one chunk. */
 
 typedef struct ggnn_ctx ggnn_ctx;
 
@@ -100,7 +102,8 @@ int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h,
  *   rows = (b, e, target) row-major, rowptr int32 [b*two_e*v + 1], col int32 = source,
  * i.e. exactly np.argwhere(adj != 0) order.  *nnz_out_dev (device int64) receives nnz.
  * If nnz > col_capacity only the first col_capacity columns are written and
- * *nnz_out_dev still holds the true count (caller checks).  No synchronisation. */
+ * *nnz_out_dev still holds the true count (caller checks).  The count is carried in 64 bits: when it
+ * is >= 2^31 the int32 rowptr / col are not valid (split the batch).  No synchronisation. */
 int ggnn_compact_adjacency(ggnn_ctx* ctx, const void* adj, int adj_dtype,
                            int b, int two_e, int v,
                            int32_t* rowptr, int32_t* col, int64_t col_capacity,
@@ -195,7 +198,8 @@ int ggnn_heads_decode(ggnn_ctx* ctx, const float* hT, const float* h0, int64_t N
                       const int32_t* n_active, int32_t* pred, float* p_head_or_null, float* p_lab_or_null,
                       void* stream);
 
-/* bytes of ctx-owned scratch a propagate call of this size will hold */
+/* UPPER-BOUND ESTIMATE (closed form, independent of the arithmetic mode) of the ctx-owned scratch a
+ * propagate_edges / propagate_csr call of this size will hold; the ctx sizes its arenas exactly at call time */
 size_t ggnn_workspace_bytes(const ggnn_ctx* ctx, int64_t N, int64_t nnz, int two_e, int h);
 
 /* instrumentation: number of kernel launches this ctx has issued so far */

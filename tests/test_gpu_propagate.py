@@ -329,9 +329,41 @@ def test_against_the_reference_functions_own_output(golden_dir, name, precision)
                                                        precision=precision)
     assert out.shape == ref.shape and out.dtype == np.float32
     assert O.normwise_err(out, ref) <= tol
+    # A5: the reference's per-edge-type loop form (compute_timestep_normal, :350-389; --old) is the same sum in
+    # another FP order; the CUDA path serves both forms, so it is held to that function's own output too
+    if f"{name}_out_normal_float64" in d.files:           # (case c is the fixed_ts call: fast form only)
+        assert O.normwise_err(out, d[f"{name}_out_normal_float64"]) <= tol
     edges = O.dense_to_edges(adj)
     sp = ggnn_b200.compute_final_node_representations_sparse(h0.reshape(b * v, h), edges, weights=w,
                                                              num_timesteps=T, fixed_ts=fixed_ts, precision=precision)
     assert O.normwise_err(sp.reshape(b, v, h), ref) <= tol
     if precision == "fp32":
         assert np.array_equal(sp.reshape(b, v, h), out)       # same summation order on both routes
+
+
+@pytest.mark.parametrize("precision,h", [("fp32", 128), ("tf32", 256)])
+def test_more_than_65535_row_tiles_in_one_call(precision, h):
+    """One edge-list call over 65 536 x 128 nodes: 65 536 node tiles and > 260 000 message tiles.  Row tiles ride on
+    gridDim.x (limit 2^31-1), not gridDim.y (65 535) -- the whole C3 batch as ONE edge list must work in the strict
+    mode and on the generic TF32 kernels.  16 distinct trees are replicated, so every replica must reproduce its
+    original bit for bit, and the originals are held to the FP64 oracle."""
+    v, E, reps, base = 128, 5, 4096, 16
+    tri = synth.random_trees(base, v - 1, E, seed=11)
+    e0 = synth.global_edge_list(tri, v, E)                          # [base*508, 3] node ids in [0, base*v)
+    w = _weights(2 * E, h, 3)
+    h_base = np.random.default_rng(5).uniform(-0.1, 0.1, (base * v, h)).astype(np.float32)
+    ref = O.propagate_edges(h_base, e0.numpy(), w, 1)
+    dev = torch.device("cuda:0")
+    e = e0.to(dev).unsqueeze(0).repeat(reps, 1, 1)
+    off = (torch.arange(reps, device=dev, dtype=torch.int32) * (base * v)).view(reps, 1)
+    e[:, :, 0] += off
+    e[:, :, 2] += off
+    edges = e.view(-1, 3).contiguous()
+    N = reps * base * v
+    assert N // 128 > 65535 and edges.shape[0] // 128 > 65535
+    hd = torch.from_numpy(h_base).to(dev).repeat(reps, 1)
+    prop = Propagator(ggnn_b200.from_dict(w), dev)
+    out = prop.propagate_edges(hd, edges, num_timesteps=1, precision=precision)
+    first = out[:base * v]
+    assert O.normwise_err(first.cpu().numpy(), ref) <= TOL[precision]
+    assert torch.equal(out.view(reps, base * v, h), first.unsqueeze(0).expand(reps, -1, -1))
