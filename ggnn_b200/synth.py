@@ -24,7 +24,7 @@ def make_weights(two_e: int, h: int, seed: int = 0, bias_std: float = 0.05) -> d
     """Synthetic parameters in the reference's shapes (chem_tensorflow_dense.py:202-212, 237-241; TF
     GRUCell init: gate bias 1.0, candidate bias 0).  Edge biases are N(0, bias_std) rather than the
     reference's zeros so that the per-edge bias rule is exercised.  Same stream of
-    draws as the test oracle's generator, so a seed names the same weights on both sides."""
+    draws as the generator the tests use, so a seed names the same weights on both sides."""
     rng = np.random.default_rng(seed)
     return {
         "edge_weights": glorot_init(rng, (two_e, h, h)),
