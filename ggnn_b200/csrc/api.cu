@@ -20,9 +20,21 @@ struct arena {
 // buffers.  They are separate because [1] is sized only after the edge count is known and
 // must not move [0].
 // [2] training tape (per-step activations), [3] backward scratch, [4] FP16 node states,
-// [5] effective edge weights of the dropout path, [6] Adam moments + norm slots.
+// [5] effective edge weights of the dropout path, [6] Adam moments + norm slots,
+// [7], [8] bitmask + queue control of a prefetched adjacency (ggnn_dense_prefetch), used alternately.
+struct prefetch_rec {
+  bool active = false;
+  const void* adj = nullptr;
+  int dtype = 0, b = 0, v = 0, two_e = 0, buf = 0;
+};
+
 struct ctx_ext {
-  arena ar[7];
+  arena ar[9];
+  // ggnn_dense_prefetch: side stream the background bitmask pass runs on, its completion events, the record
+  cudaStream_t side = nullptr;
+  cudaEvent_t pf_done[2] = {nullptr, nullptr};
+  prefetch_rec pf;
+  int pf_last_buf = 1;       // buffer of the last CONSUMED prefetch: the next one goes to the other
   int64_t adam_n = 0;       // floats the moment buffers were sized (and zeroed) for
   int64_t adam_t = 0;       // steps taken
   ggnn_tape tape;
@@ -80,6 +92,24 @@ struct device_guard {
   ~device_guard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// graphs per chunk of the dense path: canonical rows stay well inside int32 and scratch stays bounded
+int64_t dense_chunk(int two_e, int v) {
+  int64_t chunk = ((int64_t)1 << 26) / ((int64_t)two_e * v);
+  if (const char* e = getenv("GGNN_CHUNK")) { const int64_t c = atoll(e); if (c > 0 && c < chunk) chunk = c; }   // A-B switch
+  if (chunk < 1) chunk = 1;
+  if (chunk >= 16) chunk &= ~(int64_t)15;     // chunk starts stay 16-byte aligned for any v, 2E and adjacency dtype
+  return chunk;
+}
+
+// drop an unconsumed prefetch: wait for its background pass so that its buffer can be reused
+void prefetch_cancel(ggnn_ctx* ctx) {
+  ctx_ext* ex = ext_of(ctx);
+  if (ex->pf.active) {
+    cudaStreamSynchronize(ex->side);
+    ex->pf.active = false;
+  }
+}
+
 }  // namespace
 
 extern "C" int ggnn_version(void) { return 100; }
@@ -131,6 +161,8 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
   if (c->ws) {
     ctx_ext* e = ext_of(c);
     for (auto& a : e->ar) if (a.p) cudaFree(a.p);
+    if (e->side) cudaStreamDestroy(e->side);
+    for (auto& ev : e->pf_done) if (ev) cudaEventDestroy(ev);
     delete e;
   }
   for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -190,6 +222,7 @@ extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const
     GGNN_FAIL(ctx, GGNN_E_SHAPE, "set_weights: slot %d must match slot 0 (two_e=%d, h=%d)", slot, ctx->two_e, ctx->h);
   device_guard g(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
+  prefetch_cancel(ctx);
   ext_of(ctx)->tape.valid = false;     // a tape belongs to the weights it was recorded with
   if (slot == GGNN_SLOT_MAIN) {
     if (ctx->two_e != two_e || ctx->h != h) ctx->edge[GGNN_SLOT_FIXED].set = false;
@@ -463,11 +496,15 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
     GGNN_CUDA(ctx, cudaMemcpyAsync(h_out, h0, (size_t)b * v * h * sizeof(float), cudaMemcpyDeviceToDevice, st));
   // chunk so that canonical rows stay well inside int32 and scratch stays bounded
   const int64_t rows_per_graph = (int64_t)two_e * v;
-  int64_t chunk = ((int64_t)1 << 26) / rows_per_graph;
-  if (const char* e = getenv("GGNN_CHUNK")) { const int64_t c = atoll(e); if (c > 0 && c < chunk) chunk = c; }   // A-B switch
-  if (chunk < 1) chunk = 1;
-  if (chunk >= 16) chunk &= ~(int64_t)15;     // chunk starts stay 16-byte aligned for any v, 2E and adjacency dtype
+  int64_t chunk = dense_chunk(two_e, v);
   if (chunk > b) chunk = b;
+  // a prefetched adjacency (ggnn_dense_prefetch) is consumed by the call it was announced for, and only by that one
+  ctx_ext* ex = ext_of(ctx);
+  const prefetch_rec pf = ex->pf;
+  const bool use_pf = pf.active && pf.adj == adj && pf.dtype == adj_dtype && pf.b == b && pf.v == v &&
+                      pf.two_e == two_e && chunk == b && ggnn_plan_bits_supported(two_e, v) && !ctx->no_bits_plan;
+  if (pf.active && !use_pf) prefetch_cancel(ctx);
+  ex->pf.active = false;
   if ((flags & GGNN_FLAG_SAVE_TAPE) && chunk < b)
     GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "SAVE_TAPE: batch of %d graphs needs more than one chunk (%lld graphs)", b, (long long)chunk);
   for (int64_t g0 = 0; g0 < b; g0 += chunk) {
@@ -486,7 +523,20 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
       ws_alloc a0(ext_of(ctx)->ar[0].p);
       ggnn_plan_bits_take_pre(a0, bc, two_e, v, &pre);
       if (precision == GGNN_PREC_F16) GGNN_TRY(f16_prologue(ctx, slot, h_chunk, bc * v, st));
-      GGNN_TRY(ggnn_compact_bitmask(ctx, adj_c, adj_dtype, rows * v, pre.bits, st));
+      if (use_pf) {
+        // the background pass has been streaming this adjacency since the prefetch call: take the slices that are
+        // left at full occupancy, then wait for the background CTAs' last slices
+        char* pb = ex->ar[7 + pf.buf].p;
+        pre.bits = reinterpret_cast<uint32_t*>(pb + 4096);
+        {
+          prof_scope ps(ctx, GGNN_STAGE_COMPACT_MASK, st);
+          GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj_c, adj_dtype, rows * v, pre.bits, reinterpret_cast<unsigned*>(pb), false, st));
+        }
+        GGNN_CUDA(ctx, cudaStreamWaitEvent(st, ex->pf_done[pf.buf], 0));
+        ex->pf_last_buf = pf.buf;
+      } else {
+        GGNN_TRY(ggnn_compact_bitmask(ctx, adj_c, adj_dtype, rows * v, pre.bits, st));
+      }
       GGNN_TRY(ggnn_plan_bits_count(ctx, pre, bc, two_e, v, ctx->d_mail, st));
       int64_t nnz = 0;
       GGNN_TRY(read_i64(ctx, ctx->d_mail, &nnz, st));     // the one planning sync
@@ -525,6 +575,43 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
     GGNN_TRY(propagate_csr_chunk(ctx, slot, h_out + (size_t)g0 * v * h, rowptr, col, bc, v, nnz,
                                  T, precision, flags, col_bytes, st));
   }
+  return GGNN_OK;
+}
+
+// Announce the adjacency of the NEXT ggnn_propagate_dense call: its bitmask pass starts now, on the ctx's own side
+// stream, as a background kernel that shares the SMs with whatever the caller's stream is running (header).
+extern "C" int ggnn_dense_prefetch(ggnn_ctx* ctx, const void* adj, int adj_dtype, int b, int v, void* ready_event) {
+  if (!ctx) return GGNN_E_ARG;
+  if (b < 0 || v <= 0) GGNN_FAIL(ctx, GGNN_E_ARG, "dense_prefetch: bad sizes b=%d v=%d", b, v);
+  if (b > 0 && !adj) GGNN_FAIL(ctx, GGNN_E_ARG, "dense_prefetch: null pointer");
+  if (adj_dtype != GGNN_ADJ_F32 && adj_dtype != GGNN_ADJ_U8) GGNN_FAIL(ctx, GGNN_E_ARG, "bad adj_dtype %d", adj_dtype);
+  if (!ctx->gru_set) GGNN_FAIL(ctx, GGNN_E_STATE, "dense_prefetch: weights not set");
+  device_guard g(ctx->device);
+  ctx_ext* ex = ext_of(ctx);
+  const int two_e = ctx->two_e;
+  const int64_t total = (int64_t)b * two_e * v * v;
+  // a hint: shapes the fast route does not serve are simply not prefetched
+  if (b == 0 || !ggnn_plan_bits_supported(two_e, v) || ctx->no_bits_plan || dense_chunk(two_e, v) < b ||
+      !ggnn_bitmask_queue_supported(adj, total)) {
+    prefetch_cancel(ctx);
+    return GGNN_OK;
+  }
+  if (!ex->side) {
+    GGNN_CUDA(ctx, cudaStreamCreateWithFlags(&ex->side, cudaStreamNonBlocking));
+    for (auto& e : ex->pf_done) GGNN_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  int buf = ex->pf_last_buf ^ 1;
+  if (ex->pf.active) { buf = ex->pf.buf; prefetch_cancel(ctx); }   // replaced before it was used: same buffer
+  const size_t words = (size_t)(total / 32);
+  GGNN_TRY(arena_reserve(ctx, 7 + buf, 4096 + words * 4 + 256, ex->side));
+  char* pb = ex->ar[7 + buf].p;
+  GGNN_CUDA(ctx, cudaMemsetAsync(pb, 0, ggnn_bitmask_queue_ctl_bytes(), ex->side));
+  if (ready_event) GGNN_CUDA(ctx, cudaStreamWaitEvent(ex->side, (cudaEvent_t)ready_event, 0));
+  GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj, adj_dtype, total, reinterpret_cast<uint32_t*>(pb + 4096),
+                                     reinterpret_cast<unsigned*>(pb), true, ex->side));
+  GGNN_CUDA(ctx, cudaEventRecord(ex->pf_done[buf], ex->side));
+  ex->pf.active = true; ex->pf.adj = adj; ex->pf.dtype = adj_dtype; ex->pf.b = b; ex->pf.v = v;
+  ex->pf.two_e = two_e; ex->pf.buf = buf;
   return GGNN_OK;
 }
 

@@ -79,7 +79,7 @@ struct ggnn_ctx {
 
 // cudaFuncSetAttribute is per device: remember per ctx (a process may own one ctx per GPU), not in a static
 enum { GGNN_ATTR_TF32_GEMM0 = 0 /* + mode 0..3 */, GGNN_ATTR_GRU_FUSED = 4, GGNN_ATTR_MSG_TC = 5, GGNN_ATTR_F16 = 6,
-       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */ };
+       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */, GGNN_ATTR_BMQ = 13 };
 #define GGNN_ENSURE_SMEM(ctx, bit, kernel, bytes)                                                          \
   do {                                                                                                     \
     if (!((ctx)->attr_mask & (1u << (bit)))) {                                                             \
@@ -163,6 +163,10 @@ size_t ggnn_scan_tmp_elems(int64_t n);
 size_t ggnn_compact_tmp_bytes(int64_t total_elems, int64_t rows);
 int ggnn_compact_bitmask(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t total, uint32_t* bits,
                          cudaStream_t st);
+bool ggnn_bitmask_queue_supported(const void* adj, int64_t total);
+size_t ggnn_bitmask_queue_ctl_bytes();
+int ggnn_bitmask_queue_launch(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t total, uint32_t* bits,
+                              unsigned* ctl, bool background, cudaStream_t st);
 int ggnn_compact_count(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t rows, int v,
                        int32_t* rowptr, int64_t* nnz_out_dev, char* tmp, cudaStream_t st);
 int ggnn_compact_fill(ggnn_ctx* ctx, int64_t rows, int v, const int32_t* rowptr, int32_t* col,

@@ -10,6 +10,7 @@
 //   P3  exclusive scan of rowptr in place (scan.cu) -> nnz
 //   P4  per-row bit iteration -> col
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -168,6 +169,86 @@ bitmask_u8_kernel(const uint4* __restrict__ adj, int64_t n16, uint32_t* __restri
   }
 }
 
+// ---- the same pass as a WORK QUEUE (ggnn_dense_prefetch) ---------------------------------------------------
+// The bitmask pass is pure HBM streaming; the propagation kernels of the PREVIOUS batch are latency-bound and leave
+// most of the HBM bandwidth idle.  So the pass is also available as slices of 256 KB handed out by an atomic
+// counter to two kinds of CTAs:
+//   background  launched on the ctx's side stream while the previous batch's msg / GRU kernels run: at most ONE
+//               live CTA per SM (a per-SM claim; surplus CTAs exit at once) with a footprint (256 threads x 40
+//               registers, no dynamic shared memory) that fits NEXT TO one CTA of those persistent kernels;
+//   drain       launched on the caller's stream by the propagate call that consumes the prefetch, at full occupancy:
+//               takes whatever slices are left.
+// Nobody waits on anybody (the queue is a counter), so the two launches need not run concurrently.
+constexpr int64_t Q_SLICE = 12288;   // work items (32-byte groups) per slice = 384 KB: whole iterations for 256- and 384-thread CTAs
+
+// ctl[0] = next slice, ctl[8 + smid] = background CTAs that have claimed SM smid
+template <bool U8>
+__global__ void __maxnreg__(40)      // (not combinable with __launch_bounds__; always launched with P1_THREADS)
+bitmask_queue_kernel(const void* __restrict__ adj_v, int64_t n_items, uint32_t* __restrict__ bits,
+                     unsigned* __restrict__ ctl, int one_per_sm) {
+  __shared__ unsigned s_next;
+  const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    unsigned claim = 0;
+    if (one_per_sm) {
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      claim = atomicAdd(ctl + 8 + (smid & 255u), 1u);
+    }
+    s_next = claim ? 0xffffffffu : atomicAdd(ctl, 1u);
+  }
+  __syncthreads();
+  unsigned cur = s_next;
+  __syncthreads();
+  const int64_t n_slices = (n_items + Q_SLICE - 1) / Q_SLICE;
+  const float* adj = reinterpret_cast<const float*>(adj_v);
+  while ((int64_t)cur < n_slices) {
+    unsigned nxt = 0;
+    if (threadIdx.x == 0) nxt = atomicAdd(ctl, 1u);          // in flight while this slice streams
+    const int64_t g0 = (int64_t)cur * Q_SLICE + threadIdx.x;
+    const int nthr = blockDim.x;                               // 256 or 384: Q_SLICE is a multiple of 4 * nthr
+#pragma unroll 1
+    for (int off = 0; off < (int)Q_SLICE; off += nthr * P1_UNROLL) {
+      const int64_t i0 = g0 + off;
+      f32x8 x[P1_UNROLL];
+#pragma unroll
+      for (int u = 0; u < P1_UNROLL; ++u) {
+        const int64_t i = i0 + u * nthr;
+        if (i < n_items) x[u] = ldg_stream_f8(adj + i * 8);
+        else {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) x[u].u[q] = 0u;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < P1_UNROLL; ++u) {
+        const int64_t i = i0 + u * nthr;
+        if (U8) {                       // 32 bytes -> one whole word
+          uint32_t m = 0;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+#pragma unroll
+            for (int by = 0; by < 4; ++by) m |= ((x[u].u[q] >> (8 * by)) & 0xffu) ? (1u << (q * 4 + by)) : 0u;
+          }
+          if (i < n_items) bits[i] = m;
+        } else {                        // 8 floats -> one byte; 4 adjacent lanes -> one word
+          uint32_t by = 0;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) by |= (__uint_as_float(x[u].u[q]) != 0.f ? 1u : 0u) << q;
+          uint32_t w = by << ((lane & 3) * 8);
+          w |= __shfl_xor_sync(0xffffffffu, w, 1);
+          w |= __shfl_xor_sync(0xffffffffu, w, 2);
+          if ((lane & 3) == 0 && i < n_items) bits[i >> 2] = w;
+        }
+      }
+    }
+    if (threadIdx.x == 0) s_next = nxt;
+    __syncthreads();
+    cur = s_next;
+    __syncthreads();
+  }
+}
+
 // scalar tail / unaligned fallback: one thread per bitmask word over [first_word, words)
 template <typename T>
 __global__ void bitmask_scalar_kernel(const T* __restrict__ adj, int64_t total,
@@ -300,6 +381,37 @@ int ggnn_compact_bitmask(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t 
       }
     }
   }
+  return GGNN_OK;
+}
+
+// work-queue form: only for 32-byte-aligned inputs made of whole words (anything else takes the plain pass)
+bool ggnn_bitmask_queue_supported(const void* adj, int64_t total) {
+  return total > 0 && total % 32 == 0 && (reinterpret_cast<uintptr_t>(adj) & 31u) == 0;
+}
+size_t ggnn_bitmask_queue_ctl_bytes() { return (8 + 256) * sizeof(unsigned); }
+
+// background == true: persistent one-CTA-per-SM launch (side stream); false: the drain at full occupancy
+int ggnn_bitmask_queue_launch(ggnn_ctx* ctx, const void* adj, int adj_dtype, int64_t total, uint32_t* bits,
+                              unsigned* ctl, bool background, cudaStream_t st) {
+  const int64_t n_items = adj_dtype == GGNN_ADJ_F32 ? total / 8 : total / 32;
+  const int64_t n_slices = ceil_div64(n_items, Q_SLICE);
+  if (!(ctx->attr_mask & (1u << GGNN_ATTR_BMQ))) {
+    // the same shared-memory configuration as the persistent kernels it has to sit next to
+    GGNN_CUDA(ctx, cudaFuncSetAttribute(bitmask_queue_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    GGNN_CUDA(ctx, cudaFuncSetAttribute(bitmask_queue_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    ctx->attr_mask |= 1u << GGNN_ATTR_BMQ;
+  }
+  int64_t grid = background ? (int64_t)ctx->sm_count * 4 : (int64_t)ctx->sm_count * 8;
+  if (!background && grid > n_slices) grid = n_slices;
+  if (grid < 1) grid = 1;
+  // background CTA: 12 warps x 32 x 40 registers = 3 warps per scheduler partition, what the 16-warp GRU kernel leaves free
+  static const int bg_threads = getenv("GGNN_BMQ_THREADS") ? atoi(getenv("GGNN_BMQ_THREADS")) : 384;
+  const int threads = background && (bg_threads == 256 || bg_threads == 384) ? bg_threads : P1_THREADS;
+  if (adj_dtype == GGNN_ADJ_F32)
+    bitmask_queue_kernel<false><<<(unsigned)grid, threads, 0, st>>>(adj, n_items, bits, ctl, background ? 1 : 0);
+  else
+    bitmask_queue_kernel<true><<<(unsigned)grid, threads, 0, st>>>(adj, n_items, bits, ctl, background ? 1 : 0);
+  GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
 

@@ -294,15 +294,20 @@ namespace gru16 {
 
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int WSTAGES = 8;                               // weight ring: 8 x 16 KB [128 n x 64 k] slots
-constexpr int N_AGG_WARPS = 8;
+constexpr int N_AGG_WARPS = 6;                           // rows of a tile: 22, 22, 21, 21, 21, 21
 constexpr int N_EPI_WARPS = 8;
 constexpr int WARP_EPI0 = 0;                             // 0..7 (warp % 4 = TMEM lane quarter)
 constexpr int WARP_MMA = 8;
-constexpr int WARP_TMA = 9;                              // warps 10, 11 only take part in the block syncs
-constexpr int WARP_AGG0 = 12;                            // 12..19
-constexpr int NTHREADS = (WARP_AGG0 + N_AGG_WARPS) * 32; // 640
-constexpr int SMEM_BYTES = 3 * TILE16_BYTES + WSTAGES * CHUNK_BYTES + 1024 /*align*/ + 256 /*barriers*/ +
-                           3 * HP * 4 /*biases*/;        // 232 192 <= 232 448
+constexpr int WARP_TMA = 9;
+constexpr int WARP_AGG0 = 10;                            // 10..15
+// 16 warps = 4 per scheduler partition (the register file is split four ways: 16 384 registers per partition):
+// 4 x 32 x 96 = 12 288 registers used per partition, 4 096 free, and 1 KB of shared memory left over -- one
+// background CTA of the adjacency bitmask queue (compact.cu: 8 warps x 32 x 40 registers, 2 warps per partition)
+// fits next to this kernel, so the next batch's adjacency streams from HBM while this kernel waits on its
+// latency chains.  (With 18 or 20 warps one partition holds 5 warps and has no room for a single queue warp.)
+constexpr int NTHREADS = (WARP_AGG0 + N_AGG_WARPS) * 32; // 512
+constexpr int SMEM_BYTES = 3 * TILE16_BYTES + WSTAGES * CHUNK_BYTES + 256 /*barriers*/ +
+                           3 * HP * 4 /*biases*/;        // 231 168 (dynamic shared memory starts 1024-byte aligned)
 
 enum {
   BAR_W_FULL = 0,                    // [WSTAGES]
@@ -359,14 +364,15 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return v;
 }
 
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __maxnreg__(96)      // 4 warps x 32 x 96 registers per scheduler partition (see NTHREADS)
 gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
                const __grid_constant__ CUtensorMap tmWg, const __grid_constant__ CUtensorMap tmWc) {
-  extern __shared__ uint8_t smem_raw[];
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem_al = smem_raw + (base - tc::smem_u32(smem_raw));
+  const uint32_t base = tc::smem_u32(smem_raw);
+  // (128B-swizzled tiles need a 1024-byte aligned base: guaranteed by __align__(1024) on the dynamic array)
+  uint8_t* smem_al = smem_raw;
   const uint32_t sX = base;                              // two x tiles
   const uint32_t sH = base + 2 * TILE16_BYTES;           // h tile, later r*h, later h' staging
   const uint32_t sW = sH + TILE16_BYTES;                 // weight ring
@@ -411,11 +417,13 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
 
   if (warp >= WARP_AGG0) {
     // =============================== aggregation ===============================
-    const int aw = warp - WARP_AGG0;                          // rows 16*aw .. 16*aw+15 of the tile
-    auto load_ptr = [&](int tile) -> int {                    // tptr[r0 .. r0+16] -> lanes 0..16 (clamped at N)
-      int64_t rr = (int64_t)tile * BM + aw * 16 + lane;
+    const int aw = warp - WARP_AGG0;
+    const int R = BM / N_AGG_WARPS + (aw < BM % N_AGG_WARPS ? 1 : 0);          // rows of this warp (<= 31)
+    const int row0 = aw * (BM / N_AGG_WARPS) + min(aw, BM % N_AGG_WARPS);      // first of them
+    auto load_ptr = [&](int tile) -> int {                    // tptr[r0 .. r0+R] -> lanes 0..R (clamped at N)
+      int64_t rr = (int64_t)tile * BM + row0 + lane;
       if (rr > p.N) rr = p.N;
-      return lane <= 16 ? __ldg(p.tptr + rr) : 0;
+      return lane <= R ? __ldg(p.tptr + rr) : 0x7fffffff;
     };
     int it = 0;
     int my_ptr = blockIdx.x < p.n_tiles ? load_ptr(blockIdx.x) : 0;
@@ -423,7 +431,7 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
       const int xb = it & 1;
       uint8_t* xtile = smem_al + (sX - base) + xb * TILE16_BYTES;
       const int P0 = __shfl_sync(0xffffffffu, my_ptr, 0);
-      const int P1 = __shfl_sync(0xffffffffu, my_ptr, 16);
+      const int P1 = __shfl_sync(0xffffffffu, my_ptr, R);
       int my_idx = (P0 + lane < P1) ? __ldg(p.tmsg + P0 + lane) : 0;
       int nidx = (P0 + 32 + lane < P1) ? __ldg(p.tmsg + P0 + 32 + lane) : 0;
       const int next_tile = tile + gridDim.x;
@@ -440,11 +448,11 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
       if (it >= 2) tc::mbar_wait_relaxed(bar(BAR_X_EMPTY + xb), ((it >> 1) - 1) & 1);
       {   // rows without any message are written as zeros up front
         const int nxt_p = __shfl_down_sync(0xffffffffu, my_ptr, 1);
-        unsigned empty = __ballot_sync(0xffffffffu, lane < 16 && nxt_p == my_ptr);
+        unsigned empty = __ballot_sync(0xffffffffu, lane < R && nxt_p == my_ptr);
         while (empty) {
           const int r = __ffs(empty) - 1;
           empty &= empty - 1;
-          emit_row(xtile, aw * 16 + r, lane, make_float4(0.f, 0.f, 0.f, 0.f));
+          emit_row(xtile, row0 + r, lane, make_float4(0.f, 0.f, 0.f, 0.f));
         }
       }
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -453,8 +461,9 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
         const int pos_l = pb + lane;
         int rowid = 0;
 #pragma unroll
-        for (int k = 1; k <= 16; ++k) rowid += (__shfl_sync(0xffffffffu, my_ptr, k) <= pos_l) ? 1 : 0;
-        const int rend = __shfl_sync(0xffffffffu, my_ptr, min(rowid + 1, 16));
+        for (int k = 1; k <= BM / N_AGG_WARPS + 1; ++k)       // lanes above R hold INT_MAX: never counted
+          rowid += (__shfl_sync(0xffffffffu, my_ptr, k) <= pos_l) ? 1 : 0;
+        const int rend = __shfl_sync(0xffffffffu, my_ptr, min(rowid + 1, R));
         const unsigned lastmask = __ballot_sync(0xffffffffu, pos_l < P1 && pos_l + 1 == rend);
         const unsigned valid = (P1 - pb >= 32) ? 0xffffffffu : ((1u << (P1 - pb)) - 1u);
 #pragma unroll
@@ -464,7 +473,7 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
             const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&cur[j].y));
             acc.x += lo.x; acc.y += lo.y; acc.z += hi.x; acc.w += hi.y;
             if (lastmask & (1u << j)) {
-              emit_row(xtile, aw * 16 + __shfl_sync(0xffffffffu, rowid, j), lane, acc);
+              emit_row(xtile, row0 + __shfl_sync(0xffffffffu, rowid, j), lane, acc);
               acc = make_float4(0.f, 0.f, 0.f, 0.f);
             }
           }

@@ -203,6 +203,20 @@ class Propagator:
         self._check(rc, "ggnn_propagate_dense")
         return out
 
+    def prefetch_dense(self, adj: torch.Tensor, ready_event: Optional[torch.cuda.Event] = None):
+        """Announce the adjacency of the NEXT ``propagate_dense`` call: its dense -> bitmask pass starts now in the
+        background of the work already queued (the reference's ThreadedIterator prepares the next batch the same
+        way, utils.py:17-37).  ``adj`` must be final (or ``ready_event`` marks it) and must be the very tensor the
+        next call receives."""
+        adj, dt = self._adj(adj)
+        b, c, v, _ = adj.shape
+        if c != self.weights.two_e:
+            raise ValueError(f"adjacency has {c} channels, the weights have 2E={self.weights.two_e}")
+        ev = C.c_void_p(ready_event.cuda_event if ready_event is not None else 0)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_dense_prefetch(self._ctx, _ptr(adj), dt, b, v, ev)
+        self._check(rc, "ggnn_dense_prefetch")
+
     def propagate_csr(self, h0, rowptr, col, num_timesteps=None, fixed_ts=None, precision="fp32", out=None,
                       save_tape=False):
         if precision not in _PREC:

@@ -119,6 +119,20 @@ int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0,
                          int b, int v, int T, int precision, unsigned flags,
                          float* h_out, void* stream);
 
+/* Batch pipelining for ggnn_propagate_dense -- the counterpart of the reference's ThreadedIterator, which
+ * builds the next batch while sess.run works on the current one (utils.py:17-37, chem_tensorflow.py:541).
+ * Announces the adjacency of the NEXT ggnn_propagate_dense call on this ctx.  Its dense -> bitmask pass (the
+ * HBM-bound half of the path) starts at once on a ctx-owned side stream as a small background kernel that
+ * shares the SMs with the msg / GRU kernels still running on the caller's stream; the propagate call that
+ * follows with the SAME (adj, adj_dtype, b, v) finishes whatever is left of the pass and goes on as usual --
+ * same results, bit for bit.  Any other ggnn_propagate_dense call, a second prefetch, or ggnn_set_weights drops
+ * the announcement (after waiting for the background pass).
+ *   - `adj` must already hold its final contents when this is called, or `ready_event` (a cudaEvent_t as void*,
+ *     else NULL) must mark their completion; it must stay valid until the consuming call's work has finished;
+ *   - a hint: batches the fast route does not serve (more than one chunk, v > 255, unaligned adjacency) are
+ *     accepted and simply not prefetched.  No synchronisation unless an announcement is dropped. */
+int ggnn_dense_prefetch(ggnn_ctx* ctx, const void* adj, int adj_dtype, int b, int v, void* ready_event_or_null);
+
 int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0,
                        const int32_t* rowptr, const int32_t* col,
                        int b, int v, int T, int precision, unsigned flags,
