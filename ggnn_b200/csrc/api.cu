@@ -152,6 +152,8 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
     free_dev(c, c->edge[s].Wt_tf32);
     if (c->edge[s].Wt_f16) { cudaFree(c->edge[s].Wt_f16); c->edge[s].Wt_f16 = nullptr; }
     free_dev(c, c->edge[s].B_pad16);
+    if (c->edge[s].fold_f16) { cudaFree(c->edge[s].fold_f16); c->edge[s].fold_f16 = nullptr; }
+    free_dev(c, c->edge[s].fold_bias);
   }
   free_dev(c, c->Wg); free_dev(c, c->bg); free_dev(c, c->Wc); free_dev(c, c->bc);
   if (c->Wgt_f16) cudaFree(c->Wgt_f16);
@@ -537,7 +539,11 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
       } else {
         GGNN_TRY(ggnn_compact_bitmask(ctx, adj_c, adj_dtype, rows * v, pre.bits, st));
       }
-      GGNN_TRY(ggnn_plan_bits_count(ctx, pre, bc, two_e, v, ctx->d_mail, st));
+      // GGNN_PREC_F16, h <= 128, v == 128: graphs whose word-order channels are exactly t-1 -> t / t+1 -> t keep those
+      // edges out of the plan; the GRU kernel forms them from the resident h tile (f16.cu)
+      const bool word_fold = precision == GGNN_PREC_F16 && v == GGNN_TILE_M && !(flags & GGNN_FLAG_SAVE_TAPE) &&
+                             ggnn_f16_word_fold_ready(ctx, slot);
+      GGNN_TRY(ggnn_plan_bits_count(ctx, pre, bc, two_e, v, word_fold, ctx->d_mail, st));
       int64_t nnz = 0;
       GGNN_TRY(read_i64(ctx, ctx->d_mail, &nnz, st));     // the one planning sync
       if (precision == GGNN_PREC_F16) GGNN_TRY(f16_check(ctx, slot));
@@ -552,6 +558,7 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
       }
       ws_alloc a1(ext_of(ctx)->ar[1].p);
       GGNN_TRY(ggnn_plan_bits_place(ctx, pre, bc, two_e, v, nnz, &plan, a1, false, st));
+      if (word_fold) plan.tile_regular = pre.regular;
       take_step_bufs(a1, plan, h, &sb);
       GGNN_TRY(run_steps(ctx, slot, plan, sb, h_chunk, T, precision, flags, st));
       continue;

@@ -20,6 +20,11 @@ struct ggnn_edge_weights {
   void*  Wt_f16 = nullptr; // [two_e, P, P] FP16, transposed ([n][k]), zero padded; P = 128 (hp == 128) or hw16 (h > 128)
   CUtensorMap tm_Wt16;     // TMA view of Wt_f16 as [two_e*128 rows, 128 cols], box 64 x 128
   float* B_pad16 = nullptr;// [two_e, hw16] FP32 zero-padded biases (wide16.cu, h > 128)
+  // word-order channels E-1 / 2E-1 folded through the GRU input weights (f16.cu, hp == 128, two_e even)
+  void*  fold_f16 = nullptr;   // [2][384][128] FP16, K-major
+  float* fold_bias = nullptr;  // [3][384] scaled biases of a word-order tile
+  CUtensorMap tm_fold;
+  bool   fold_ok = false;
   float  absmax_w = -1.f;  // max|W|, max|B| of this slot (host copy, < 0 = not computed yet)
   float  absmax_b = 0.f;
   CUtensorMap tm_Wt;       // TMA view of Wt_tf32 as [two_e*hp rows, hp cols], box 32 x tm_rows

@@ -65,6 +65,51 @@ __global__ void state_in_kernel(const float* __restrict__ hs, __half* __restrict
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
   if (absmax && (threadIdx.x & 31) == 0 && m > 0.f) atomicMax(absmax, __float_as_uint(m));
 }
+// ---- word-order channels folded through the GRU's input weights (gru16::gru_f16_kernel) ------------------------
+// F[d][n][k] = f16( (W[e_d] @ [Wg[:h, :2h] | Wc[:h, :h]])[k][n] ),  e_0 = E-1 (t-1 -> t), e_1 = 2E-1 (t+1 -> t);
+// n = 128-column blocks r | u | cand, zero padded like the other packs.  One CTA per (d, n), thread = k.
+__global__ void fold_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wc,
+                            __half* __restrict__ F, int two_e, int h) {
+  const int d = blockIdx.x / (3 * HP), n = blockIdx.x % (3 * HP), k = threadIdx.x;
+  const int e = d == 0 ? two_e / 2 - 1 : two_e - 1;
+  const int nb = n / HP, nn = n % HP;
+  float acc = 0.f;
+  if (k < h && nn < h) {
+    const float* wrow = W + ((size_t)e * h + k) * h;
+    for (int j = 0; j < h; ++j) {
+      const float wx = nb < 2 ? Wg[(size_t)j * 2 * h + nb * h + nn] : Wc[(size_t)j * h + nn];
+      acc = fmaf(wrow[j], wx, acc);
+    }
+  }
+  F[((size_t)d * 3 * HP + n) * HP + k] = __float2half_rn(acc);
+}
+// scaled bias vectors of a word-order tile [3][384]: inner rows (both word-order messages), first row (t+1 -> t
+// only), last row (t-1 -> t only); scale = -log2e for the gates, 2 log2e for the candidate (the epilogue's forms)
+__global__ void fold_bias_kernel(const float* __restrict__ B, const float* __restrict__ Wg, const float* __restrict__ Wc,
+                                 const float* __restrict__ bg, const float* __restrict__ bc, float* __restrict__ out,
+                                 int two_e, int h) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= 3 * HP) return;
+  const int nb = n / HP, nn = n % HP;
+  float plain = 0.f, dp = 0.f, dn = 0.f;
+  if (nn < h) {
+    plain = nb < 2 ? bg[nb * h + nn] : bc[nn];
+    if (B) {
+      const float* bp = B + (size_t)(two_e / 2 - 1) * h;
+      const float* bn = B + (size_t)(two_e - 1) * h;
+      for (int j = 0; j < h; ++j) {
+        const float wx = nb < 2 ? Wg[(size_t)j * 2 * h + nb * h + nn] : Wc[(size_t)j * h + nn];
+        dp = fmaf(bp[j], wx, dp);
+        dn = fmaf(bn[j], wx, dn);
+      }
+    }
+  }
+  const float sc = nb < 2 ? -1.4426950408889634f : 2.0f * 1.4426950408889634f;
+  out[n] = sc * (plain + dp + dn);
+  out[3 * HP + n] = sc * (plain + dn);
+  out[6 * HP + n] = sc * (plain + dp);
+}
+
 __global__ void absmax_kernel(const float* __restrict__ x, int64_t n, unsigned* __restrict__ out) {
   float m = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -293,7 +338,7 @@ msg_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmW,
 namespace gru16 {
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int WSTAGES = 8;                               // weight ring: 8 x 16 KB [128 n x 64 k] slots
+constexpr int WSTAGES = 7;                               // weight ring: 7 x 16 KB [128 n x 64 k] slots
 constexpr int N_AGG_WARPS = 6;                           // rows of a tile: 22, 22, 21, 21, 21, 21
 constexpr int N_EPI_WARPS = 8;
 constexpr int WARP_EPI0 = 0;                             // 0..7 (warp % 4 = TMEM lane quarter)
@@ -301,23 +346,31 @@ constexpr int WARP_MMA = 8;
 constexpr int WARP_TMA = 9;
 constexpr int WARP_AGG0 = 10;                            // 10..15
 // 16 warps = 4 per scheduler partition (the register file is split four ways: 16 384 registers per partition):
-// 4 x 32 x 96 = 12 288 registers used per partition, 4 096 free, and 1 KB of shared memory left over -- one
-// background CTA of the adjacency bitmask queue (compact.cu: 8 warps x 32 x 40 registers, 2 warps per partition)
+// 4 x 32 x 96 = 12 288 registers used per partition, 4 096 free, and > 1 KB of shared memory left over -- one
+// background CTA of the adjacency bitmask queue (compact.cu: 12 warps x 32 x 40 registers, 3 warps per partition)
 // fits next to this kernel, so the next batch's adjacency streams from HBM while this kernel waits on its
 // latency chains.  (With 18 or 20 warps one partition holds 5 warps and has no room for a single queue warp.)
 constexpr int NTHREADS = (WARP_AGG0 + N_AGG_WARPS) * 32; // 512
-constexpr int SMEM_BYTES = 3 * TILE16_BYTES + WSTAGES * CHUNK_BYTES + 256 /*barriers*/ +
-                           3 * HP * 4 /*biases*/;        // 231 168 (dynamic shared memory starts 1024-byte aligned)
+// The h tile sits between 1 KB gaps that stay ZERO: an A-operand descriptor that starts one 128-byte row below /
+// above a 128B-swizzled chunk makes MMA row r read tile row r-1 / r+1 (the swizzle is a function of the absolute
+// shared-memory address: scripts/micro/desc_shift.cu), and the row that falls off the tile reads the gap.
+constexpr int HGAP = 1024;
+constexpr int HCHUNK_STRIDE = CHUNK_BYTES + HGAP;
+constexpr int H_BYTES = 2 * HCHUNK_STRIDE + HGAP;        // gap | chunk 0 | gap | chunk 1 | gap
+constexpr int NB = 3 * HP;                               // bias vector: r | u | cand
+constexpr int SMEM_BYTES = 2 * TILE16_BYTES + H_BYTES + WSTAGES * CHUNK_BYTES + 256 /*barriers*/ +
+                           4 * NB * 4 /*biases: plain, word-order tile: inner rows, first row, last row*/;   // 222 464
 
 enum {
   BAR_W_FULL = 0,                    // [WSTAGES]
   BAR_W_EMPTY = BAR_W_FULL + WSTAGES,
   BAR_X_FULL = BAR_W_EMPTY + WSTAGES,   // [2]
-  BAR_X_EMPTY = BAR_X_FULL + 2,         // [2]
+  BAR_X_EMPTY = BAR_X_FULL + 2,         // [2] every MMA reading this x buffer (x, later r*h) has retired
   BAR_H_FULL = BAR_X_EMPTY + 2,
   BAR_H_EMPTY,
-  BAR_R_DONE,                        // r accumulator complete and every MMA reading the h tile retired
-  BAR_UC_DONE,                       // u accumulator and the x part of cand complete
+  BAR_R_DONE,                        // r accumulator complete
+  BAR_X_READ,                        // the MMAs reading x of this tile have retired: the buffer may take r*h
+  BAR_UC_DONE,                       // u accumulator complete
   BAR_RH_FULL,
   BAR_CAND_DONE,
   BAR_TMEM_EMPTY,
@@ -329,6 +382,8 @@ struct params {
   const __half* msg;        // [*, 128] FP16 message rows
   const int32_t* tptr;      // [N+1]
   const int32_t* tmsg;      // [nnz]
+  const int32_t* regular;   // [n_tiles] 1 = word-order tile (see plan_bits.cu) or null
+  const float* fold_bias;   // [3][384] scaled biases of a word-order tile: inner rows, first row, last row (or null)
   float* h_out;             // [N, h] FP32 result (written on the last step only) or null
   const float* bg_pad;      // [256]
   const float* bc;          // [h]
@@ -364,22 +419,30 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return v;
 }
 
+// Per 128-node tile:
+//   x      = sum of the incoming FP16 message rows (aggregation warps, fixed order)            -> x buffer
+//   r      = sigmoid([x, h] @ Wg[:, :h] + bg_r);  r*h (FP16) overwrites the x buffer once its readers have retired
+//   u      = sigmoid([x, h] @ Wg[:, h:] + bg_u);  cand = tanh(x @ Wc[:h] + (r*h) @ Wc[h:] + bc)
+//   h'     = cand + u * (h - cand)                                                              -> h tile -> TMA store
+// Word-order tile (params::regular): the messages of channels E-1 (t-1 -> t) and 2E-1 (t+1 -> t) never exist as
+// rows; their contribution to the three pre-activations is formed from the RESIDENT h tile with row-shifted
+// A descriptors and the folded weights F = W_channel @ [Wg[:h] | Wc[:h]] (packed by fold_kernel).
 __global__ void __maxnreg__(96)      // 4 warps x 32 x 96 registers per scheduler partition (see NTHREADS)
-gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
-               const __grid_constant__ CUtensorMap tmWg, const __grid_constant__ CUtensorMap tmWc) {
+gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmWg,
+               const __grid_constant__ CUtensorMap tmWc, const __grid_constant__ CUtensorMap tmF) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  const uint32_t base = tc::smem_u32(smem_raw);
-  // (128B-swizzled tiles need a 1024-byte aligned base: guaranteed by __align__(1024) on the dynamic array)
+  const uint32_t base = tc::smem_u32(smem_raw);          // 1024-byte aligned (__align__ on the dynamic array)
   uint8_t* smem_al = smem_raw;
   const uint32_t sX = base;                              // two x tiles
-  const uint32_t sH = base + 2 * TILE16_BYTES;           // h tile, later r*h, later h' staging
-  const uint32_t sW = sH + TILE16_BYTES;                 // weight ring
+  const uint32_t sHg = base + 2 * TILE16_BYTES;          // gap | h chunk 0 | gap | h chunk 1 | gap
+  const uint32_t sW = sHg + H_BYTES;                     // weight ring
   const uint32_t bars = sW + WSTAGES * CHUNK_BYTES;
   auto bar = [&](int i) { return bars + 8u * i; };
+  auto sHc = [&](int kc) { return sHg + HGAP + (uint32_t)kc * HCHUNK_STRIDE; };   // K chunk kc of the h tile
   const uint32_t tmem_slot = bars + 8u * BAR_COUNT;
-  float* s_bias = reinterpret_cast<float*>(smem_al + (bars + 256 - base));   // [-log2e*bg (256) | 2log2e*bc (128)]
+  float* s_bias = reinterpret_cast<float*>(smem_al + (bars + 256 - base));   // [4][384]: -log2e*bg (256) | 2log2e*bc (128)
 
   if (warp == WARP_MMA && lane == 0) {
     for (int s = 0; s < WSTAGES; ++s) {
@@ -393,6 +456,7 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
     tc::mbar_init(bar(BAR_H_FULL), 1);
     tc::mbar_init(bar(BAR_H_EMPTY), 1);
     tc::mbar_init(bar(BAR_R_DONE), 1);
+    tc::mbar_init(bar(BAR_X_READ), 1);
     tc::mbar_init(bar(BAR_UC_DONE), 1);
     tc::mbar_init(bar(BAR_RH_FULL), N_EPI_WARPS);
     tc::mbar_init(bar(BAR_CAND_DONE), 1);
@@ -404,12 +468,20 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
       tc::tma_prefetch_desc(&tmH);
       tc::tma_prefetch_desc(&tmWg);
       tc::tma_prefetch_desc(&tmWc);
+      tc::tma_prefetch_desc(&tmF);
     }
     __syncwarp();
     tc::tmem_alloc(tmem_slot, 512);
   }
-  if (tid < 2 * HP) s_bias[tid] = -kLog2e * p.bg_pad[tid];
-  else if (tid < 3 * HP) s_bias[tid] = (tid - 2 * HP) < p.h ? 2.0f * kLog2e * p.bc[tid - 2 * HP] : 0.f;
+  for (int i = tid; i < 3 * HGAP / 4; i += NTHREADS)      // the three gaps around the h chunks: zero, for good
+    reinterpret_cast<uint32_t*>(smem_al + (sHg - base) + (i / (HGAP / 4)) * HCHUNK_STRIDE)[i % (HGAP / 4)] = 0u;
+  for (int i = tid; i < NB; i += NTHREADS) {
+    const float pl = i < 2 * HP ? -kLog2e * p.bg_pad[i] : ((i - 2 * HP) < p.h ? 2.0f * kLog2e * p.bc[i - 2 * HP] : 0.f);
+    s_bias[i] = pl;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) s_bias[(q + 1) * NB + i] = p.fold_bias ? p.fold_bias[q * NB + i] : pl;
+  }
+  tc::fence_proxy_async();                                // the zeroed gaps are read by the tensor core
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -500,24 +572,26 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
         tc::tma_load_2d(sW + s * CHUNK_BYTES, tm, kcol, nrow, bar(BAR_W_FULL + s));
         ++fill;
       };
+      auto w_pair = [&](const CUtensorMap* tm, int kcol, int nrow) {       // both K chunks of a [128 x 128] block
+        w_fill(tm, kcol, nrow);
+        w_fill(tm, kcol + BKH, nrow);
+      };
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) w_fill(&tmWg, kc * BKH, 0);               // x   -> r
-        if (it > 0) tc::mbar_wait_relaxed(bar(BAR_H_EMPTY), (it - 1) & 1);      // previous h' stored
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {   // order = the MMA issuer's
+        const bool reg = p.regular && __ldg(p.regular + tile) != 0;
+        w_pair(&tmWg, 0, 0);                                                // x      -> r
+        if (it > 0) tc::mbar_wait_relaxed(bar(BAR_H_EMPTY), (it - 1) & 1); // previous h' stored
         tc::mbar_arrive_expect_tx(bar(BAR_H_FULL), TILE16_BYTES);
-        tc::tma_load_2d(sH, &tmH, 0, tile * BM, bar(BAR_H_FULL));
-        tc::tma_load_2d(sH + CHUNK_BYTES, &tmH, BKH, tile * BM, bar(BAR_H_FULL));
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) w_fill(&tmWg, HP + kc * BKH, 0);          // h   -> r
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) w_fill(&tmWg, HP + kc * BKH, HP);         // h   -> u
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) w_fill(&tmWg, kc * BKH, HP);              // x   -> u
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) w_fill(&tmWc, kc * BKH, 0);               // x   -> cand
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) w_fill(&tmWc, HP + kc * BKH, 0);          // r*h -> cand
+        tc::tma_load_2d(sHc(0), &tmH, 0, tile * BM, bar(BAR_H_FULL));
+        tc::tma_load_2d(sHc(1), &tmH, BKH, tile * BM, bar(BAR_H_FULL));
+        w_pair(&tmWg, HP, 0);                                               // h      -> r
+        if (reg) { w_pair(&tmF, 0, 0); w_pair(&tmF, 0, NB); }               // h[t-1], h[t+1] -> r
+        w_pair(&tmWg, 0, HP);                                               // x      -> u
+        w_pair(&tmWc, 0, 0);                                                // x      -> cand
+        w_pair(&tmWg, HP, HP);                                              // h      -> u
+        if (reg) { w_pair(&tmF, 0, HP); w_pair(&tmF, 0, NB + HP); }         // h[t-1], h[t+1] -> u
+        if (reg) { w_pair(&tmF, 0, 2 * HP); w_pair(&tmF, 0, NB + 2 * HP); } // h[t-1], h[t+1] -> cand
+        w_pair(&tmWc, HP, 0);                                               // r*h    -> cand
       }
     }
     __syncwarp();
@@ -539,32 +613,45 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
         tc::umma_commit(bar(BAR_W_EMPTY + s));
         ++use;
       };
+      // both K chunks of an A tile whose chunks are `stride` bytes apart; shift = -128 / +128: rows t-1 / t+1
+      auto tile_mma = [&](uint32_t d, uint32_t a0, uint32_t stride, bool first) {
+        chunk_mma(d, a0, first);
+        chunk_mma(d, a0 + stride, false);
+      };
       int it = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        const bool reg = p.regular && __ldg(p.regular + tile) != 0;
         const int xb = it & 1;
-        const uint32_t x0 = sX + xb * TILE16_BYTES;
+        const uint32_t x0 = sX + xb * TILE16_BYTES, h0 = sHc(0);
         if (it > 0) tc::mbar_wait(bar(BAR_TMEM_EMPTY), (it - 1) & 1);
         tc::mbar_wait(bar(BAR_X_FULL + xb), (it >> 1) & 1);
         tc::fence_after_sync();
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) chunk_mma(d_r, x0 + kc * CHUNK_BYTES, kc == 0);      // x -> r
+        tile_mma(d_r, x0, CHUNK_BYTES, true);                               // x -> r
         tc::mbar_wait(bar(BAR_H_FULL), it & 1);
         tc::fence_after_sync();
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) chunk_mma(d_r, sH + kc * CHUNK_BYTES, false);        // h -> r
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) chunk_mma(d_u, sH + kc * CHUNK_BYTES, kc == 0);      // h -> u
-        tc::umma_commit(bar(BAR_R_DONE));                     // r complete; the h tile may become r*h
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) chunk_mma(d_u, x0 + kc * CHUNK_BYTES, false);        // x -> u
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) chunk_mma(d_cand, x0 + kc * CHUNK_BYTES, kc == 0);   // x -> cand
-        tc::umma_commit(bar(BAR_X_EMPTY + xb));               // this x buffer may be refilled
-        tc::umma_commit(bar(BAR_UC_DONE));
-        tc::mbar_wait(bar(BAR_RH_FULL), it & 1);              // epilogue replaced h by f16(r*h)
+        tile_mma(d_r, h0, HCHUNK_STRIDE, false);                            // h -> r
+        if (reg) {
+          tile_mma(d_r, h0 - 128, HCHUNK_STRIDE, false);                    // h[t-1] -> r
+          tile_mma(d_r, h0 + 128, HCHUNK_STRIDE, false);                    // h[t+1] -> r
+        }
+        tc::umma_commit(bar(BAR_R_DONE));
+        tile_mma(d_u, x0, CHUNK_BYTES, true);                               // x -> u
+        tile_mma(d_cand, x0, CHUNK_BYTES, true);                            // x -> cand
+        tc::umma_commit(bar(BAR_X_READ));                                   // the x buffer may take r*h
+        tile_mma(d_u, h0, HCHUNK_STRIDE, false);                            // h -> u
+        if (reg) {
+          tile_mma(d_u, h0 - 128, HCHUNK_STRIDE, false);
+          tile_mma(d_u, h0 + 128, HCHUNK_STRIDE, false);
+        }
+        tc::umma_commit(bar(BAR_UC_DONE));                                  // u complete: the update-gate pass may start
+        if (reg) {
+          tile_mma(d_cand, h0 - 128, HCHUNK_STRIDE, false);
+          tile_mma(d_cand, h0 + 128, HCHUNK_STRIDE, false);
+        }
+        tc::mbar_wait(bar(BAR_RH_FULL), it & 1);                            // f16(r*h) is in the x buffer
         tc::fence_after_sync();
-#pragma unroll 1
-        for (int kc = 0; kc < 2; ++kc) chunk_mma(d_cand, sH + kc * CHUNK_BYTES, false);     // r*h -> cand
+        tile_mma(d_cand, x0, CHUNK_BYTES, false);                           // r*h -> cand
+        tc::umma_commit(bar(BAR_X_EMPTY + xb));                             // this x buffer may be refilled
         tc::umma_commit(bar(BAR_CAND_DONE));
       }
     }
@@ -573,16 +660,19 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
   else if (warp < WARP_EPI0 + N_EPI_WARPS) {
     // =============================== epilogue (warps 0-7) ===============================
     const int ew = warp & 3;                                  // TMEM lane quarter this warp may access
-    const int chalf = (warp - WARP_EPI0) >> 2;                // which 64 columns = which K chunk of the h tile
+    const int chalf = (warp - WARP_EPI0) >> 2;                // which 64 columns = which K chunk of the tiles
     const int r = ew * 32 + lane;                             // row within the tile = TMEM lane
     const uint32_t t_lane = tmem_base + ((uint32_t)(ew * 32) << 16);
-    const float* s_bg = s_bias;
-    const float* s_bc = s_bias + 2 * HP;
-    uint8_t* hrow = smem_al + (sH - base) + chalf * CHUNK_BYTES;     // + sw_off(r, slot)
+    uint8_t* hrow = smem_al + (sHc(chalf) - base);            // + sw_off(r, slot): this thread's h row, its 64 columns
     const bool leader = tid == WARP_EPI0 * 32;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
-      // ---- EPI1a: reset gate; r*h (FP16) replaces h in smem; h itself is parked in TMEM (cols 384..)
+      const bool reg = p.regular && __ldg(p.regular + tile) != 0;
+      // biases of this row: plain, or (word-order tile) with the folded edge biases of the word-order messages it gets
+      const float* s_bg = s_bias + (!reg ? 0 : (r == 0 ? 2 * NB : (r == BM - 1 ? 3 * NB : NB)));
+      const float* s_bc = s_bg + 2 * HP;
+      uint8_t* xrow = smem_al + (sX - base) + (it & 1) * TILE16_BYTES + chalf * CHUNK_BYTES;
+      // ---- EPI1a: reset gate; f16(r*h) goes into the x buffer (its readers have retired); h stays where it is
       tc::mbar_wait(bar(BAR_R_DONE), it & 1);
       tc::fence_after_sync();
 #pragma unroll 1
@@ -590,12 +680,11 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
         const int col0 = chalf * 64 + c16 * 16;
         uint32_t ar[16];
         tc::tmem_ld16(t_lane + col0, ar);
-        uint4* s0 = reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16));
-        uint4* s1 = reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16 + 1));
         float hh[16];
         {
           float t0[8], t1[8];
-          unpack8(*s0, t0); unpack8(*s1, t1);
+          unpack8(*reinterpret_cast<const uint4*>(hrow + sw_off(r, 2 * c16)), t0);
+          unpack8(*reinterpret_cast<const uint4*>(hrow + sw_off(r, 2 * c16 + 1)), t1);
 #pragma unroll
           for (int i = 0; i < 8; ++i) { hh[i] = t0[i]; hh[8 + i] = t1[i]; }
         }
@@ -606,16 +695,15 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
           const float rg = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(ar[i]), -kLog2e, s_bg[col0 + i])));
           const float v = rg * hh[i];
           if (i < 8) o0[i] = v; else o1[i - 8] = v;
-          ar[i] = __float_as_uint(hh[i]);                     // park h for EPI2
         }
-        *s0 = pack8(o0);
-        *s1 = pack8(o1);
-        tc::tmem_st16(t_lane + 384 + col0, ar);
+        if (c16 == 0) tc::mbar_wait(bar(BAR_X_READ), it & 1);
+        *reinterpret_cast<uint4*>(xrow + sw_off(r, 2 * c16)) = pack8(o0);
+        *reinterpret_cast<uint4*>(xrow + sw_off(r, 2 * c16 + 1)) = pack8(o1);
       }
       tc::fence_proxy_async();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(bar(BAR_RH_FULL));
-      // ---- EPI1b (overlaps MMA2): update gate, in place in TMEM
+      // ---- EPI1b (overlaps the r*h MMAs): update gate, in place in TMEM
       tc::mbar_wait(bar(BAR_UC_DONE), it & 1);
       tc::fence_after_sync();
 #pragma unroll 1
@@ -630,29 +718,37 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
         tc::tmem_st16(t_lane + 128 + col0, au);
       }
       tc::tmem_st_wait();
-      // ---- EPI2: candidate and new state h' = c + u*(h - c): FP16 into the (now free) h tile for the
-      //      TMA store of the state; the unrounded FP32 straight to h_out on the last step
+      // ---- EPI2: candidate and new state h' = c + u*(h - c): FP16 over h in the h tile (every MMA reading it has
+      //      retired) for the TMA store of the state; the unrounded FP32 straight to h_out on the last step
       tc::mbar_wait(bar(BAR_CAND_DONE), it & 1);
       tc::fence_after_sync();
       const int64_t grow = (int64_t)tile * BM + r;
 #pragma unroll 1
       for (int c16 = 0; c16 < 4; ++c16) {
         const int col0 = chalf * 64 + c16 * 16;
-        uint32_t ac[16], uu[16], hh[16];
+        uint32_t ac[16], uu[16];
         tc::tmem_ld16(t_lane + 256 + col0, ac);
         tc::tmem_ld16(t_lane + 128 + col0, uu);
-        tc::tmem_ld16(t_lane + 384 + col0, hh);
+        uint4* s0 = reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16));
+        uint4* s1 = reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16 + 1));
+        float hh[16];
+        {
+          float t0[8], t1[8];
+          unpack8(*s0, t0); unpack8(*s1, t1);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { hh[i] = t0[i]; hh[8 + i] = t1[i]; }
+        }
         tc::tmem_ld_wait();
         float o0[8], o1[8];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const float c = fmaf(-2.0f, tc::rcp_approx(1.0f + tc::ex2_approx(
                                           fmaf(__uint_as_float(ac[i]), 2.0f * kLog2e, s_bc[col0 + i]))), 1.0f);
-          const float v = fmaf(__uint_as_float(uu[i]), __uint_as_float(hh[i]) - c, c);
+          const float v = fmaf(__uint_as_float(uu[i]), hh[i] - c, c);
           if (i < 8) o0[i] = v; else o1[i - 8] = v;
         }
-        *reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16)) = pack8(o0);
-        *reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16 + 1)) = pack8(o1);
+        *s0 = pack8(o0);
+        *s1 = pack8(o1);
         if (p.h_out && grow < p.N) {
           float* dst = p.h_out + grow * p.h + col0;
 #pragma unroll
@@ -670,8 +766,8 @@ gru_f16_kernel(const params p, const __grid_constant__ CUtensorMap tmH,
       if (lane == 0) tc::mbar_arrive(bar(BAR_TMEM_EMPTY));
       tc::named_bar_sync(1, N_EPI_WARPS * 32);
       if (leader) {
-        tc::tma_store_2d(&tmH, 0, tile * BM, sH);             // rows >= N clipped by the map
-        tc::tma_store_2d(&tmH, BKH, tile * BM, sH + CHUNK_BYTES);
+        tc::tma_store_2d(&tmH, 0, tile * BM, sHc(0));         // rows >= N clipped by the map
+        tc::tma_store_2d(&tmH, BKH, tile * BM, sHc(1));
         tc::tma_store_commit();
         tc::tma_store_wait_read();
         tc::mbar_arrive(bar(BAR_H_EMPTY));                    // h tile may be refilled
@@ -697,8 +793,29 @@ static int realloc_h(ggnn_ctx* ctx, void*& p, size_t n_halves) {
   return GGNN_OK;
 }
 
+// folded word-order weights of one slot (needs the slot's edge weights and the GRU cell)
+static int fold_slot(ggnn_ctx* ctx, int slot, cudaStream_t st) {
+  ggnn_edge_weights& ew = ctx->edge[slot];
+  ew.fold_ok = false;
+  if (ctx->two_e < 2 || ctx->two_e % 2 || !ctx->Wg || !ctx->Wc || !ew.W) return GGNN_OK;
+  GGNN_TRY(realloc_h(ctx, ew.fold_f16, (size_t)2 * 3 * HP * HP));
+  if (!ew.fold_bias) GGNN_CUDA(ctx, cudaMalloc(&ew.fold_bias, 9 * HP * sizeof(float)));
+  fold_kernel<<<2 * 3 * HP, HP, 0, st>>>(ew.W, ctx->Wg, ctx->Wc, reinterpret_cast<__half*>(ew.fold_f16), ctx->two_e, ctx->h);
+  GGNN_LAUNCHED(ctx);
+  fold_bias_kernel<<<3, HP, 0, st>>>(ew.B, ctx->Wg, ctx->Wc, ctx->bg, ctx->bc, ew.fold_bias, ctx->two_e, ctx->h);
+  GGNN_LAUNCHED(ctx);
+  GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ew.tm_fold, ew.fold_f16, 2 * 3 * HP, HP, BKH, HP));
+  ew.fold_ok = true;
+  return GGNN_OK;
+}
+
+bool ggnn_f16_word_fold_ready(const ggnn_ctx* ctx, int slot) {
+  static const bool off = getenv("GGNN_NO_WORD_FOLD") != nullptr;      // A-B switch
+  return !off && ggnn_f16_supported(ctx) && ctx->edge[slot].fold_ok;
+}
+
 int ggnn_f16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st) {
-  if (!ggnn_f16_supported(ctx)) return GGNN_OK;
+  if (!ggnn_f16_supported(ctx)) { ctx->edge[slot].fold_ok = false; return GGNN_OK; }
   const int h = ctx->h, two_e = ctx->two_e;
   ggnn_edge_weights& ew = ctx->edge[slot];
   ew.absmax_w = -1.f;
@@ -716,7 +833,10 @@ int ggnn_f16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t s
     GGNN_LAUNCHED(ctx);
     GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wg16, ctx->Wgt_f16, 2 * HP, 2 * HP, BKH, HP));
     GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16, ctx->Wct_f16, HP, 2 * HP, BKH, HP));
+    for (int s2 = 0; s2 < GGNN_MAX_SLOTS; ++s2)          // a new GRU cell re-folds every slot that is already set
+      if (s2 != slot && ctx->edge[s2].set) GGNN_TRY(fold_slot(ctx, s2, st));
   }
+  GGNN_TRY(fold_slot(ctx, slot, st));
   return GGNN_OK;
 }
 
@@ -764,10 +884,14 @@ int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
   gru16::params g{};
   g.msg = reinterpret_cast<const __half*>(msg16); g.tptr = plan.tptr; g.tmsg = plan.tmsg;
   g.h_out = last_step ? h_out : nullptr; g.bg_pad = ctx->bg_pad; g.bc = ctx->bc;
+  g.regular = plan.tile_regular;                       // non-null only when the plan left the word-order rows out
+  g.fold_bias = plan.tile_regular ? ew.fold_bias : nullptr;
+  if (plan.tile_regular && !ew.fold_ok) GGNN_FAIL(ctx, GGNN_E_STATE, "internal: word-order plan without folded weights");
   g.N = plan.N; g.h = ctx->h; g.n_tiles = (int)ceil_div64(plan.N, BM);
   const int grid = g.n_tiles < ctx->sm_count ? g.n_tiles : ctx->sm_count;
   prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
-  gru16::gru_f16_kernel<<<grid, gru16::NTHREADS, gru16::SMEM_BYTES, st>>>(g, tmH, ctx->tm_Wg16, ctx->tm_Wc16);
+  gru16::gru_f16_kernel<<<grid, gru16::NTHREADS, gru16::SMEM_BYTES, st>>>(g, tmH, ctx->tm_Wg16, ctx->tm_Wc16,
+                                                                          ew.fold_ok ? ew.tm_fold : ctx->tm_Wc16);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

@@ -4,6 +4,8 @@
 #include "plan.cuh"
 
 bool ggnn_f16_supported(const ggnn_ctx* ctx);
+// the plan may leave the word-order rows of regular graphs to the GRU kernel (folded weights are packed, not switched off)
+bool ggnn_f16_word_fold_ready(const ggnn_ctx* ctx, int slot);
 // pack the weights of `slot` (and the GRU cell) into K-major FP16 tiles + TMA maps
 int ggnn_f16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st);
 // state16 [N, 128] FP16 = h [N, h] FP32 rounded to nearest, columns >= h zero; max|h| is

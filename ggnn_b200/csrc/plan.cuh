@@ -16,6 +16,10 @@ struct ggnn_plan {
   int32_t* tile_type = nullptr; // [max_tiles]     edge channel of a tile
   int32_t* tptr = nullptr;      // [N+1]           CSR by target node ...
   int32_t* tmsg = nullptr;      // [nnz]           ... of message-row ids, ascending (channel, source)
+  // GGNN_PREC_F16, h <= 128, dense route, v == 128: [N/128] 1 = the graph's word-order channels E-1 / 2E-1 are
+  // exactly t-1 -> t and t+1 -> t; their edges are NOT in msg_src / tmsg / nnz, the GRU kernel forms them from the
+  // resident h tile.  nullptr = every edge is a message row.
+  int32_t* tile_regular = nullptr;
 };
 
 // Builders take their arrays from the bump allocator in a fixed order.  With dry=true

@@ -46,17 +46,34 @@ __device__ __forceinline__ int row_popc(const uint32_t* __restrict__ bits, int64
 __global__ void __launch_bounds__(MAX_THREADS)
 graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int v,
                    uint16_t* __restrict__ rowcnt, int32_t* __restrict__ seglenT,
-                   int32_t* __restrict__ tcnt) {
+                   int32_t* __restrict__ tcnt, int word_fold, int32_t* __restrict__ regular) {
   extern __shared__ int part[];
   const int64_t g = blockIdx.x;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
+  // word-order graph (v == 128 = blockDim.x): row t of channel E-1 is exactly {t-1}, of channel 2E-1 exactly {t+1}
+  const int cp = two_e / 2 - 1, cn = two_e - 1;
+  int reg = 0;
+  if (word_fold) {
+    const uint4 mp = __ldg(reinterpret_cast<const uint4*>(bits) + ((g * two_e + cp) * v + t));   // 128 bits = one row
+    const uint4 mn = __ldg(reinterpret_cast<const uint4*>(bits) + ((g * two_e + cn) * v + t));
+    const uint32_t wp[4] = {mp.x, mp.y, mp.z, mp.w}, wn[4] = {mn.x, mn.y, mn.z, mn.w};
+    bool ok = true;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t ep = (t >= 1 && ((t - 1) >> 5) == q) ? 1u << ((t - 1) & 31) : 0u;
+      const uint32_t en = (t <= 126 && ((t + 1) >> 5) == q) ? 1u << ((t + 1) & 31) : 0u;
+      ok = ok && wp[q] == ep && wn[q] == en;
+    }
+    reg = __syncthreads_and(ok ? 1 : 0);
+    if (t == 0) regular[g] = reg;
+  }
   int deg = 0;
 #pragma unroll 4
   for (int e = 0; e < two_e; ++e) {
     const int64_t r = (g * two_e + e) * v + t;
     int c = 0;
     if (t < v) {
-      c = row_popc(bits, r * v, v);
+      c = (reg && (e == cp || e == cn)) ? 0 : row_popc(bits, r * v, v);
       rowcnt[r] = (uint16_t)c;
     }
     deg += c;
@@ -181,16 +198,19 @@ void ggnn_plan_bits_take_pre(ws_alloc& a, int64_t b, int two_e, int v, ggnn_plan
   pre->rowcnt = a.take<uint16_t>((size_t)rows + 2);
   pre->segposT = a.take<int32_t>((size_t)nseg + 1);
   pre->tptr = a.take<int32_t>((size_t)N + 1);
+  pre->regular = a.take<int32_t>((size_t)b + 1);
   pre->scan_elems = ggnn_scan_tmp_elems((nseg > N ? nseg : N) + 1);
   pre->scan_tmp = a.take<int32_t>(pre->scan_elems);
 }
 
-int ggnn_plan_bits_count(ggnn_ctx* ctx, const ggnn_plan_bits_pre& pre, int64_t b, int two_e, int v,
+int ggnn_plan_bits_count(ggnn_ctx* ctx, const ggnn_plan_bits_pre& pre, int64_t b, int two_e, int v, bool word_fold,
                          int64_t* nnz_out_dev, cudaStream_t st) {
   prof_scope ps(ctx, GGNN_STAGE_COMPACT_REST, st);
   const int vt = threads_for(v);
+  if (word_fold && (v != GGNN_TILE_M || two_e < 2 || two_e % 2)) GGNN_FAIL(ctx, GGNN_E_ARG, "internal: word_fold needs v == 128 and an even channel count");
   graph_count_kernel<<<(unsigned)b, vt, (size_t)(vt / 32) * two_e * 4, st>>>(pre.bits, b, two_e, v, pre.rowcnt,
-                                                                            pre.segposT, pre.tptr);
+                                                                            pre.segposT, pre.tptr, word_fold ? 1 : 0,
+                                                                            pre.regular);
   GGNN_LAUNCHED(ctx);
   GGNN_TRY(ggnn_exclusive_scan_i32(ctx, pre.segposT, pre.segposT, b * two_e + 1, nullptr, pre.scan_tmp, pre.scan_elems, st));
   GGNN_TRY(ggnn_exclusive_scan_i32(ctx, pre.tptr, pre.tptr, b * v + 1, nnz_out_dev, pre.scan_tmp, pre.scan_elems, st));

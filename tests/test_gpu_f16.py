@@ -199,3 +199,45 @@ def test_large_batch_properties(precision):
     assert torch.equal(permuted, big[sub])
     ref = O.propagate_dense(h0[pick[:2]].cpu().numpy(), adj[pick[:2]].cpu().numpy(), O.make_weights(2 * E, h, 0), T)
     assert O.normwise_err(small[:2].cpu().numpy(), ref) <= (1e-5 if precision == "fp32" else TOL)
+
+
+def test_word_order_channels_folded_into_the_gru_kernel(monkeypatch):
+    """v = 128 graphs whose channels E-1 / 2E-1 are exactly t-1 -> t / t+1 -> t (what graph_to_adj_mat_bd builds for a
+    127-word sentence, chem_tensorflow_dense.py:76-80) never send those messages through HBM: the GRU kernel forms them
+    from the resident h tile.  Mixed batch: full-length trees (folded), shorter trees and a tree with one word-order
+    edge removed / one extra edge on channel E-1 (not folded) -- all against the FP64 oracle, and against the
+    edge-list route, which gathers every message."""
+    b, v, E, h, T = 12, 128, 7, 128, 8
+    lengths = torch.tensor([127, 127, 60, 127, 1, 127, 126, 127, 127, 100, 127, 127])
+    tri = synth.random_trees(b, v - 1, E, seed=21, lengths=lengths)
+    adj = synth.dense_adjacency(tri, v, E)
+    adj[3, E - 1, 50, 49] = 0.0                         # graph 3: one word-order edge missing
+    adj[5, E - 1, 10, 3] = 1.0                          # graph 5: an extra edge on the channel
+    adj[7, 2 * E - 1, 127, 0] = 1.0                     # graph 7: the last node receives on channel 2E-1
+    w = O.make_weights(2 * E, h, 4)
+    h0 = _h0(b, v, h, seed=9)
+    ref = O.propagate_dense(h0, adj.numpy(), w, T)
+    prop = Propagator(W.from_dict(w), "cuda:0")
+    d_h0, d_adj = torch.from_numpy(h0).cuda(), adj.cuda()
+    out = prop.propagate_dense(d_h0, d_adj, num_timesteps=T, precision="f16")
+    assert O.normwise_err(out.cpu().numpy(), ref) <= TOL
+    # (the tolerance is defined on the whole output; per graph the maximum over fewer elements has a heavier tail)
+    per_graph = [O.normwise_err(out[g].cpu().numpy(), ref[g]) for g in range(b)]
+    assert max(per_graph) <= 1.5 * TOL, per_graph
+    assert torch.equal(out, prop.propagate_dense(d_h0, d_adj, num_timesteps=T, precision="f16"))
+    edges = torch.from_numpy(O.dense_to_edges(adj.numpy())).cuda()
+    sp = prop.propagate_edges(d_h0.view(-1, h), edges, num_timesteps=T, precision="f16").view(b, v, h)
+    not_folded = [2, 3, 4, 5, 6, 7, 9]                  # identical plans on both routes -> identical bits
+    assert torch.equal(out[not_folded], sp[not_folded])
+    assert O.normwise_err(out.cpu().numpy(), sp.cpu().numpy()) <= TOL       # two results inside the tolerance of the truth
+    # a graph computed alone equals the same graph inside the batch, folded or not
+    for g in (0, 3, 11):
+        one = prop.propagate_dense(d_h0[g:g + 1].contiguous(), d_adj[g:g + 1].contiguous(), num_timesteps=T, precision="f16")
+        assert torch.equal(one[0], out[g])
+    # no bias, fixed_ts weights, h < 128
+    w2 = O.make_weights(2 * E, 100, 6)
+    w2.pop("edge_biases")
+    h2 = _h0(4, v, 100, seed=3)
+    a2 = synth.dense_adjacency(synth.random_trees(4, v - 1, E, seed=2), v, E).numpy()
+    o2 = ggnn_b200.compute_final_node_representations(h2, a2, weights=w2, num_timesteps=3, precision="f16")
+    assert O.normwise_err(o2, O.propagate_dense(h2, a2, w2, 3, use_bias=False)) <= TOL
