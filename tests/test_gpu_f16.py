@@ -241,3 +241,26 @@ def test_word_order_channels_folded_into_the_gru_kernel(monkeypatch):
     a2 = synth.dense_adjacency(synth.random_trees(4, v - 1, E, seed=2), v, E).numpy()
     o2 = ggnn_b200.compute_final_node_representations(h2, a2, weights=w2, num_timesteps=3, precision="f16")
     assert O.normwise_err(o2, O.propagate_dense(h2, a2, w2, 3, use_bias=False)) <= TOL
+
+
+_C4_REF = {}
+
+
+@pytest.mark.parametrize("precision", ["f16", "tf32", "fp32"])
+def test_c4_full_size_parity(precision):
+    """BASELINE config 4 at FULL size -- v = 4096 nodes, 8 channels, nnz = 65 536, h = 256, T = 8 -- on the inputs
+    bench.py times for it (edge weights x 0.25, bench.C4_WEIGHT_SCALE): two graphs through the edge-list path
+    against the FP64 oracle."""
+    n, nodes, base, types, h, T = 2, 4096, 32768, 4, 256, 8
+    w = O.make_weights(2 * types, h, 0)
+    w["edge_weights"] = w["edge_weights"] * np.float32(0.25)
+    edges = synth.random_multigraph(n, nodes, base, types, seed=1000)
+    h0 = np.random.default_rng(3).uniform(-0.1, 0.1, (n * nodes, h)).astype(np.float32)
+    out = ggnn_b200.compute_final_node_representations_sparse(h0, edges.numpy(), weights=w, num_timesteps=T,
+                                                              precision=precision)
+    if "ref" not in _C4_REF:                                   # one FP64 oracle run serves the three modes
+        _C4_REF["ref"] = O.propagate_edges(h0, edges.numpy(), w, T)
+    ref = _C4_REF["ref"]
+    err = O.normwise_err(out, ref)
+    print(f"C4 full size, {precision}: norm-wise error {err:.3e}")
+    assert err <= (1e-5 if precision == "fp32" else TOL)
