@@ -30,6 +30,7 @@ SIGNATURES = {
     "ggnn_version": (_i, []),
     "ggnn_set_weights": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ggnn_compact_adjacency": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i64, _vp, _vp]),
+    "ggnn_compact_adjacency_static": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i64, _vp, _vp]),
     "ggnn_propagate_dense": (_i, [_vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _u, _vp, _vp]),
     "ggnn_dense_prefetch": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "ggnn_propagate_csr": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _u, _vp, _vp]),

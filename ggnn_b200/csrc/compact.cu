@@ -11,6 +11,7 @@
 //   P4  per-row bit iteration -> col
 #include "common.cuh"
 #include <stdlib.h>
+#include <mutex>
 
 namespace {
 
@@ -443,4 +444,77 @@ int ggnn_compact_fill(ggnn_ctx* ctx, int64_t rows, int v, const int32_t* rowptr,
     GGNN_LAUNCHED(ctx);
   }
   return GGNN_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// ggnn_compact_adjacency_static: the same compaction with its scratch (bitmask + scan partials) in a file-scope
+// device array instead of the ctx's cudaMalloc-ed arena, for callers that must not allocate (CUDA graph capture,
+// tight serving loops).  No counterpart in the reference.
+// Limits: b*two_e*v*v <= GGNN_STATIC_MAX_ELEMS adjacency elements and b*two_e*v <= GGNN_STATIC_MAX_ROWS rows.
+// Every GPU that loads the library holds the array (2 MB + 4 KB) until the process exits.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int64_t STATIC_MAX_ELEMS = GGNN_STATIC_MAX_ELEMS;       // 16 777 216 -> 2 MB of bitmask
+constexpr int64_t STATIC_MAX_ROWS = GGNN_STATIC_MAX_ROWS;         //  1 048 576 -> 1.5 KB of scan partials
+constexpr size_t STATIC_SCRATCH_BYTES = (size_t)(STATIC_MAX_ELEMS / 32) * 4 + 4096;
+
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, NOT a device address: the address each device
+// gives the array is asked for once per device, with that device current, and handed to the kernels as a pointer.
+std::mutex g_scratch_mu;
+char* g_scratch_ptr[64] = {nullptr};
+
+}  // namespace
+
+extern "C" int ggnn_compact_adjacency_static(ggnn_ctx* ctx, const void* adj, int adj_dtype, int b, int two_e, int v,
+                                             int32_t* rowptr, int32_t* col, int64_t col_capacity,
+                                             int64_t* nnz_out_dev, void* stream) {
+  if (!ctx) return GGNN_E_ARG;
+  if (b < 0 || two_e <= 0 || v <= 0) GGNN_FAIL(ctx, GGNN_E_ARG, "compact_static: bad sizes b=%d two_e=%d v=%d", b, two_e, v);
+  if ((b > 0 && !adj) || !rowptr || !nnz_out_dev || (col_capacity > 0 && !col) || col_capacity < 0)
+    GGNN_FAIL(ctx, GGNN_E_ARG, "compact_static: null pointer");
+  if (adj_dtype != GGNN_ADJ_F32 && adj_dtype != GGNN_ADJ_U8) GGNN_FAIL(ctx, GGNN_E_ARG, "compact_static: bad adj_dtype %d", adj_dtype);
+  const int64_t rows = (int64_t)b * two_e * v;
+  const int64_t total = rows * (int64_t)v;
+  if (total > STATIC_MAX_ELEMS || rows > STATIC_MAX_ROWS || ggnn_compact_tmp_bytes(total, rows) > STATIC_SCRATCH_BYTES)
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED,
+              "compact_static: %lld adjacency elements / %lld rows exceed the static scratch (at most %lld elements and "
+              "%lld rows per call); split the batch or use ggnn_compact_adjacency",
+              (long long)total, (long long)rows, (long long)STATIC_MAX_ELEMS, (long long)STATIC_MAX_ROWS);
+  if (ctx->device < 0 || ctx->device >= 64) GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "compact_static: device index %d", ctx->device);
+  int prev = -1;
+  GGNN_CUDA(ctx, cudaGetDevice(&prev));
+  if (prev != ctx->device) GGNN_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = GGNN_OK;
+  char* tmp = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    if (!g_scratch_ptr[ctx->device]) {            // set-up, once per device, that device current
+      void* ptr = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+      if (e != cudaSuccess || !ptr) {
+        snprintf(ctx->err, sizeof(ctx->err), "compact_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        rc = GGNN_E_CUDA;
+      } else {
+        g_scratch_ptr[ctx->device] = static_cast<char*>(ptr);
+      }
+    }
+    tmp = g_scratch_ptr[ctx->device];
+  }
+  if (rc == GGNN_OK) {
+    // Nothing here allocates: kernel launches and one cudaMemsetAsync.  (The per-stage profiler creates CUDA events on
+    // first use, so it is held off for the duration of the call.)  Every scratch word this call reads it has written
+    // itself first -- the bitmask pass covers every word, the scan writes its partials before reading them -- so the
+    // previous call's contents need no clearing.
+    const bool prof = ctx->prof_on;
+    ctx->prof_on = false;
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = ggnn_compact_count(ctx, adj, adj_dtype, rows, v, rowptr, nnz_out_dev, tmp, st);
+    if (rc == GGNN_OK) rc = ggnn_compact_fill(ctx, rows, v, rowptr, col, col_capacity, tmp, st);
+    ctx->prof_on = prof;
+  }
+  if (prev != ctx->device) cudaSetDevice(prev);
+  return rc;
 }

@@ -109,6 +109,24 @@ int ggnn_compact_adjacency(ggnn_ctx* ctx, const void* adj, int adj_dtype,
                            int32_t* rowptr, int32_t* col, int64_t col_capacity,
                            int64_t* nnz_out_dev, void* stream);
 
+/* The same compaction for callers that may not allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, results and conventions as ggnn_compact_adjacency, but the scratch
+ * (bitmask + scan partials) is a fixed device array inside the library (2 MB + 4 KB, held by every GPU that
+ * loads the library until the process exits) instead of the ctx's grow-only arena: the call performs no
+ * cudaMalloc / cudaFree and no other allocating call.
+ *   - limits: b*two_e*v*v <= GGNN_STATIC_MAX_ELEMS and b*two_e*v <= GGNN_STATIC_MAX_ROWS; larger batches return
+ *     GGNN_E_UNSUPPORTED (split them, or use ggnn_compact_adjacency);
+ *   - ALL calls on a device share the one array, from every ctx and stream: calls whose GPU work can overlap
+ *     race on it -- keep them on one stream or order them with events.  It keeps the previous call's contents;
+ *     none of them is read before it is rewritten, so nothing needs clearing between calls. */
+#define GGNN_STATIC_MAX_ELEMS  16777216   /* adjacency elements per call */
+#define GGNN_STATIC_MAX_ROWS    1048576   /* (graph, channel, target) rows per call */
+int ggnn_compact_adjacency_static(ggnn_ctx* ctx, const void* adj, int adj_dtype,
+                                  int b, int two_e, int v,
+                                  int32_t* rowptr, int32_t* col, int64_t col_capacity,
+                                  int64_t* nnz_out_dev, void* stream);
+
 /* A2..A6: propagation ----------------------------------------------------------
  * h0, h_out: float32 [b, v, h] (h_out may alias h0).  T = number of timesteps.
  * Every row is updated, padded or not (the reference never reads node_mask inside
