@@ -150,6 +150,7 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
     free_dev(c, c->edge[s].W);
     free_dev(c, c->edge[s].B);
     free_dev(c, c->edge[s].Wt_tf32);
+    free_dev(c, c->edge[s].Wt_tf32_lo);
     if (c->edge[s].Wt_f16) { cudaFree(c->edge[s].Wt_f16); c->edge[s].Wt_f16 = nullptr; }
     free_dev(c, c->edge[s].B_pad16);
     if (c->edge[s].fold_f16) { cudaFree(c->edge[s].fold_f16); c->edge[s].fold_f16 = nullptr; }
@@ -158,7 +159,7 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
   free_dev(c, c->Wg); free_dev(c, c->bg); free_dev(c, c->Wc); free_dev(c, c->bc);
   if (c->Wgt_f16) cudaFree(c->Wgt_f16);
   if (c->Wct_f16) cudaFree(c->Wct_f16);
-  free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
+  free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->Wgt_tf32_lo); free_dev(c, c->Wct_tf32_lo); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
   free_dev(c, c->bg_w16); free_dev(c, c->bc_w16);
   if (c->ws) {
     ctx_ext* e = ext_of(c);
@@ -436,8 +437,10 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
   }
   if (precision == GGNN_PREC_TF32 && T > 0)   // state is kept TF32-rounded between steps
     GGNN_TRY(ggnn_tf32_round_copy(ctx, h_state, h_state, plan.N * ctx->h, st));
+  const bool strict_tc = precision == GGNN_PREC_FP32 && ggnn_fp32_tc_enabled(ctx);
   for (int t = 0; t < T; ++t) {
     if (precision == GGNN_PREC_TF32) GGNN_TRY(ggnn_step_tf32(ctx, slot, plan, sb, h_state, t == T - 1, st));
+    else if (strict_tc) GGNN_TRY(ggnn_step_fp32_tc(ctx, slot, plan, sb, h_state, st));
     else GGNN_TRY(ggnn_step_fp32(ctx, slot, plan, sb, h_state, st));
   }
   return GGNN_OK;

@@ -17,6 +17,8 @@ struct ggnn_edge_weights {
   float* W = nullptr;      // [two_e, h, h]  FP32, reference layout (K rows, N cols)
   float* B = nullptr;      // [two_e, h] or nullptr
   float* Wt_tf32 = nullptr;// [two_e, hp, hp] TF32-rounded, transposed ([n][k]), zero padded to hp
+  float* Wt_tf32_lo = nullptr; // same layout, tf32(W - tf32(W)): the residual pack of the strict (3xTF32) mode
+  CUtensorMap tm_Wt_lo;
   void*  Wt_f16 = nullptr; // [two_e, P, P] FP16, transposed ([n][k]), zero padded; P = 128 (hp == 128) or hw16 (h > 128)
   CUtensorMap tm_Wt16;     // TMA view of Wt_f16 as [two_e*128 rows, 128 cols], box 64 x 128
   float* B_pad16 = nullptr;// [two_e, hw16] FP32 zero-padded biases (wide16.cu, h > 128)
@@ -49,6 +51,8 @@ struct ggnn_ctx {
   float* bc = nullptr;     // [h]
   float* Wgt_tf32 = nullptr; // [2hp, 2hp] transposed + padded + TF32-rounded
   float* Wct_tf32 = nullptr; // [hp, 2hp]
+  float* Wgt_tf32_lo = nullptr, *Wct_tf32_lo = nullptr;   // residual packs (strict mode)
+  CUtensorMap tm_Wg_lo, tm_Wc_lo, tm_Wg_half;   // (tm_Wg_lo / tm_Wg_half: boxes of hp rows)
   void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
   void* Wct_f16 = nullptr;   // [128, 256]
   CUtensorMap tm_Wg16, tm_Wc16;
@@ -84,7 +88,7 @@ struct ggnn_ctx {
 
 // cudaFuncSetAttribute is per device: remember per ctx (a process may own one ctx per GPU), not in a static
 enum { GGNN_ATTR_TF32_GEMM0 = 0 /* + mode 0..3 */, GGNN_ATTR_GRU_FUSED = 4, GGNN_ATTR_MSG_TC = 5, GGNN_ATTR_F16 = 6,
-       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */, GGNN_ATTR_BMQ = 13 };
+       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */, GGNN_ATTR_BMQ = 13, GGNN_ATTR_STRICT_TC = 14 };
 #define GGNN_ENSURE_SMEM(ctx, bit, kernel, bytes)                                                          \
   do {                                                                                                     \
     if (!((ctx)->attr_mask & (1u << (bit)))) {                                                             \

@@ -277,28 +277,33 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
 
 // ---- weight packing -------------------------------------------------------------------
 // dst[e][n][k] (n, k < hp) = tf32(src[e][k][n]) for k, n < h, else 0
+// lo != 0: the residual pack of the 3xTF32 split (strict_tc.cu), tf32(w - tf32(w))
+__device__ __forceinline__ float pack_val(float w, int lo) {
+  const float hi = tc::to_tf32(w);
+  return lo ? tc::to_tf32(w - hi) : hi;
+}
 __global__ void pack_edge_kernel(const float* __restrict__ W, float* __restrict__ Wt, int two_e,
-                                 int h, int hp) {
+                                 int h, int hp, int lo) {
   const int64_t total = (int64_t)two_e * hp * hp;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int k = (int)(i % hp), n = (int)((i / hp) % hp);
     const int64_t e = i / ((int64_t)hp * hp);
-    Wt[i] = (k < h && n < h) ? tc::to_tf32(W[(e * h + k) * h + n]) : 0.f;
+    Wt[i] = (k < h && n < h) ? pack_val(W[(e * h + k) * h + n], lo) : 0.f;
   }
 }
 
 // GRU kernels: src [2h, ncols*h] (rows: x part then h part; column blocks of width h)
 // dst [ncols*hp, 2hp]: dst[nb*hp + n][kb*hp + k] = tf32(src[kb*h + k][nb*h + n])
 __global__ void pack_gru_kernel(const float* __restrict__ src, float* __restrict__ dst, int ncols,
-                                int h, int hp) {
+                                int h, int hp, int lo) {
   const int Kp = 2 * hp, Np = ncols * hp;
   const int64_t total = (int64_t)Np * Kp;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int kk = (int)(i % Kp), nn = (int)(i / Kp);
     const int kb = kk / hp, k = kk % hp, nb = nn / hp, n = nn % hp;
-    dst[i] = (k < h && n < h) ? tc::to_tf32(src[(size_t)(kb * h + k) * (ncols * h) + nb * h + n]) : 0.f;
+    dst[i] = (k < h && n < h) ? pack_val(src[(size_t)(kb * h + k) * (ncols * h) + nb * h + n], lo) : 0.f;
   }
 }
 
@@ -456,7 +461,7 @@ int ggnn_tf32_nt(ggnn_ctx* ctx, const float* A1, const float* A2, int lda, const
 // edge weights of `slot` re-packed from W_src (dropout: this step's effective weights; null = the slot's own)
 int ggnn_tf32_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st) {
   ggnn_edge_weights& ew = ctx->edge[slot];
-  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src ? W_src : ew.W, ew.Wt_tf32, ctx->two_e, ctx->h, ctx->hp);
+  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src ? W_src : ew.W, ew.Wt_tf32, ctx->two_e, ctx->h, ctx->hp, 0);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
@@ -477,18 +482,39 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
   const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
   ggnn_edge_weights& ew = ctx->edge[slot];
   GGNN_TRY(realloc_f(ctx, ew.Wt_tf32, (size_t)two_e * hp * hp));
-  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32, two_e, h, hp);
+  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32, two_e, h, hp, 0);
   GGNN_LAUNCHED(ctx);
   GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt, ew.Wt_tf32, (int64_t)two_e * hp, hp, &ew.tm_rows, hp));
+  const bool strict_tc = hp <= 128;      // residual packs of the strict (3xTF32) mode, strict_tc.cu
+  if (strict_tc) {
+    GGNN_TRY(realloc_f(ctx, ew.Wt_tf32_lo, (size_t)two_e * hp * hp));
+    pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32_lo, two_e, h, hp, 1);
+    GGNN_LAUNCHED(ctx);
+    int rows_lo;
+    GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt_lo, ew.Wt_tf32_lo, (int64_t)two_e * hp, hp, &rows_lo, hp));
+  }
   if (with_gru) {
     GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32, (size_t)4 * hp * hp));
     GGNN_TRY(realloc_f(ctx, ctx->Wct_tf32, (size_t)2 * hp * hp));
     GGNN_TRY(realloc_f(ctx, ctx->bg_pad, (size_t)2 * hp));
     GGNN_TRY(realloc_f(ctx, ctx->bc_pad, (size_t)hp));
-    pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, ctx->Wgt_tf32, 2, h, hp);
+    pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, ctx->Wgt_tf32, 2, h, hp, 0);
     GGNN_LAUNCHED(ctx);
-    pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, ctx->Wct_tf32, 1, h, hp);
+    pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, ctx->Wct_tf32, 1, h, hp, 0);
     GGNN_LAUNCHED(ctx);
+    if (strict_tc) {
+      GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32_lo, (size_t)4 * hp * hp));
+      GGNN_TRY(realloc_f(ctx, ctx->Wct_tf32_lo, (size_t)2 * hp * hp));
+      pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, ctx->Wgt_tf32_lo, 2, h, hp, 1);
+      GGNN_LAUNCHED(ctx);
+      pack_gru_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, ctx->Wct_tf32_lo, 1, h, hp, 1);
+      GGNN_LAUNCHED(ctx);
+      int r_;
+      // strict_tc.cu runs the gate contraction as two N = hp halves: boxes of hp rows
+      GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg_lo, ctx->Wgt_tf32_lo, 2 * hp, 2 * hp, hp));
+      GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg_half, ctx->Wgt_tf32, 2 * hp, 2 * hp, hp));
+      GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wc_lo, ctx->Wct_tf32_lo, hp, 2 * hp, &r_, hp));
+    }
     pack_bias_kernel<<<(2 * hp + 255) / 256, 256, 0, st>>>(ctx->bg, ctx->bg_pad, 2, h, hp);
     GGNN_LAUNCHED(ctx);
     pack_bias_kernel<<<(hp + 255) / 256, 256, 0, st>>>(ctx->bc, ctx->bc_pad, 1, h, hp);

@@ -57,3 +57,9 @@ int ggnn_tf32_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStrea
 int ggnn_tf32_tn(ggnn_ctx* ctx, const float* X, int ldx, const int32_t* x_rowmap, int K1, const float* D, int ldd,
                  const int32_t* d_rowmap, int N, int64_t R, int rows_per_cta, float* C, int ldc,
                  const int32_t* tile_type, const int32_t* n_tiles, int64_t c_type_stride, cudaStream_t st);
+
+// GGNN_PREC_FP32 on the tensor cores (3xTF32 split, strict_tc.cu), hidden sizes up to 128; GGNN_FP32_FFMA=1 keeps the FFMA
+// kernels of step_fp32.cu
+bool ggnn_fp32_tc_enabled(const ggnn_ctx* ctx);
+int ggnn_step_fp32_tc(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bufs& bufs, float* h_state,
+                      cudaStream_t st);

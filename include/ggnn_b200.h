@@ -53,7 +53,9 @@ extern "C" {
 #define GGNN_ADJ_U8   1
 
 /* arithmetic mode of the message / GRU contractions */
-#define GGNN_PREC_FP32  0   /* strict: FP32 FFMA, <= 1e-5 norm-wise vs the FP64 oracle  */
+#define GGNN_PREC_FP32  0   /* strict, <= 1e-5 norm-wise vs the FP64 oracle.  Hidden sizes up to 128: tcgen05 with every
+                             * operand split in two TF32 halves (3 MMAs per product, FP32 accumulate; ~3e-6 at T = 8);
+                             * above 128, and with GGNN_FP32_FFMA=1 in the environment: FP32 FFMA (~6e-7)           */
 #define GGNN_PREC_TF32  1   /* tcgen05 kind::tf32, FP32 accumulate, <= 2e-3 norm-wise   */
 #define GGNN_PREC_F16   2   /* tcgen05 kind::f16: operands rounded to FP16 (the same 11-bit significand
                              * as TF32) and held in 16-bit containers, FP32 accumulate, FP32 gate math,

@@ -72,14 +72,26 @@ def test_random_trees(precision, b, v, E, h, T):
     assert O.normwise_err(out, ref) <= TOL[precision]
 
 
-def test_fp32_is_well_inside_tolerance_and_reproducible():
+def test_fp32_is_well_inside_tolerance_and_reproducible(monkeypatch):
+    """Strict mode, h <= 128: the 3xTF32 tensor-core kernels (strict_tc.cu) -- their error is set by the tensor core's
+    truncating accumulation (measured 3.3e-6 at C3 shape, T = 8) -- and, behind GGNN_FP32_FFMA=1, the FFMA kernels they
+    replaced, which stay as the second opinion (IEEE FP32 throughout: ~5e-7, like the oracle's own FP32)."""
     _, adj = _trees(8, 32, 10, seed=0)
     w = _weights(20, 128, 0)
     h0 = _h0(8, 32, 128)
     out, ref = _run_both(w, h0, adj, 8, "fp32")
-    assert O.normwise_err(out, ref) <= 2e-6            # oracle's own FP32 is at ~5e-7
+    assert O.normwise_err(out, ref) <= 5e-6
     out2, _ = _run_both(w, h0, adj, 8, "fp32")
     assert np.array_equal(out, out2)                   # no float atomics: bit-reproducible
+    monkeypatch.setenv("GGNN_FP32_FFMA", "1")
+    ffma, _ = _run_both(w, h0, adj, 8, "fp32")
+    assert O.normwise_err(ffma, ref) <= 2e-6
+    assert O.normwise_err(out, ffma) <= 5e-6
+    monkeypatch.delenv("GGNN_FP32_FFMA")
+    # hidden sizes above 128 stay on the FFMA kernels (the split's accumulation error grows with the reduction length)
+    w4 = _weights(20, 160, 1)
+    out4, ref4 = _run_both(w4, _h0(8, 32, 160), adj, 4, "fp32")
+    assert O.normwise_err(out4, ref4) <= 2e-6
 
 
 def test_ragged_lengths_and_padded_rows():
