@@ -316,7 +316,7 @@ int f16_prologue(ggnn_ctx* ctx, int slot, const float* h0, int64_t N, cudaStream
   GGNN_CUDA(ctx, cudaMemsetAsync(ctx->d_mail + 4, 0, 3 * sizeof(int64_t), st));
   ggnn_edge_weights& ew = ctx->edge[slot];
   if (ew.absmax_w < 0.f) {
-    GGNN_TRY(ggnn_absmax(ctx, ew.W, (int64_t)ctx->two_e * ctx->h * ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 4), st));
+    GGNN_TRY(ggnn_colnorm_max(ctx, ew.W, ctx->two_e, ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 4), st));
     if (ew.B) GGNN_TRY(ggnn_absmax(ctx, ew.B, (int64_t)ctx->two_e * ctx->h, reinterpret_cast<unsigned*>(ctx->d_mail + 5), st));
   }
   if (wide) return ggnn_w16_state_in(ctx, h0, ext_of(ctx)->ar[4].p, N, reinterpret_cast<unsigned*>(ctx->d_mail + 6), st);
@@ -329,10 +329,11 @@ int f16_check(ggnn_ctx* ctx, int slot) {
   ggnn_edge_weights& ew = ctx->edge[slot];
   if (ew.absmax_w < 0.f) { ew.absmax_w = f(4); ew.absmax_b = f(5); }
   const float hmax = f(6);
-  const float bound = ctx->h * ew.absmax_w * (hmax > 1.f ? hmax : 1.f) + ew.absmax_b;
+  // |h @ W_e + b_e| <= (largest column L1 norm of any W_e) * max|h| + max|B|; states stay within max(max|h0|, 1)
+  const float bound = ew.absmax_w * (hmax > 1.f ? hmax : 1.f) + ew.absmax_b;
   if (!(bound < 64.f))
-    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "F16 mode: h*max|W|*max(max|h0|,1)+max|B| = %g >= 64 (max|W|=%g max|h0|=%g): values may leave the FP16 range; use GGNN_PREC_TF32",
-              bound, ew.absmax_w, hmax);
+    GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "F16 mode: max column L1 norm of W (%g) * max(max|h0|,1) (max|h0|=%g) + max|B| = %g >= 64: values may leave the FP16 range; use GGNN_PREC_TF32",
+              ew.absmax_w, hmax, bound);
   return GGNN_OK;
 }
 

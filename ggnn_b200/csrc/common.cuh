@@ -27,7 +27,7 @@ struct ggnn_edge_weights {
   float* fold_bias = nullptr;  // [3][384] scaled biases of a word-order tile
   CUtensorMap tm_fold;
   bool   fold_ok = false;
-  float  absmax_w = -1.f;  // max|W|, max|B| of this slot (host copy, < 0 = not computed yet)
+  float  absmax_w = -1.f;  // largest column L1 norm of any W_e, max|B| of this slot (host copy, < 0 = not computed yet)
   float  absmax_b = 0.f;
   CUtensorMap tm_Wt;       // TMA view of Wt_tf32 as [two_e*hp rows, hp cols], box 32 x tm_rows
   int    tm_rows = 0;

@@ -849,6 +849,31 @@ int ggnn_f16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, u
   return GGNN_OK;
 }
 
+// max over (e, n) of sum_k |W[e][k][n]|: the largest L1 norm of a column of any edge weight matrix.  |h @ W_e| <=
+// colnorm * max|h| element-wise, which is what the FP16 range guard needs -- h * max|W| is the same bound with every
+// |W| replaced by the largest one.  One thread per (e, n), coalesced over n; fixed order, no float atomics on the sum.
+__global__ void colnorm_kernel(const float* __restrict__ W, int two_e, int h, unsigned* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float s = 0.f;
+  if (i < (int64_t)two_e * h) {
+    const int64_t e = i / h;
+    const int n = (int)(i % h);
+    const float* p = W + e * h * h + n;
+    for (int k = 0; k < h; ++k) s += fabsf(p[(size_t)k * h]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, o));
+  if ((threadIdx.x & 31) == 0 && s > 0.f) atomicMax(out, __float_as_uint(s));     // NaN fails the `> 0`; Inf propagates
+}
+
+int ggnn_colnorm_max(ggnn_ctx* ctx, const float* W, int two_e, int h, unsigned* out_bits, cudaStream_t st) {
+  const int64_t n = (int64_t)two_e * h;
+  if (n <= 0) return GGNN_OK;
+  colnorm_kernel<<<(unsigned)ceil_div64(n, 128), 128, 0, st>>>(W, two_e, h, out_bits);
+  GGNN_LAUNCHED(ctx);
+  return GGNN_OK;
+}
+
 int ggnn_absmax(ggnn_ctx* ctx, const float* x, int64_t n, unsigned* out_bits, cudaStream_t st) {
   if (n <= 0) return GGNN_OK;
   absmax_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(x, n, out_bits);

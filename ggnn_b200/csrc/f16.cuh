@@ -14,6 +14,8 @@ int ggnn_f16_state_in(ggnn_ctx* ctx, const float* h, void* state16, int64_t N, u
                       cudaStream_t st);
 // max|x| over n floats, accumulated into *out_bits (float bits, atomicMax; caller zeroes)
 int ggnn_absmax(ggnn_ctx* ctx, const float* x, int64_t n, unsigned* out_bits, cudaStream_t st);
+// max over edge types and output columns of the column's L1 norm sum_k |W[e][k][n]| (float bits, atomicMax; caller zeroes)
+int ggnn_colnorm_max(ggnn_ctx* ctx, const float* W, int two_e, int h, unsigned* out_bits, cudaStream_t st);
 // one timestep: msg16 [max_tiles*128, 128] FP16 scratch; state16 in/out; on the last step the
 // unrounded FP32 state is also written to h_out [N, h]
 int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16,

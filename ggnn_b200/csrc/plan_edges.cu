@@ -82,7 +82,11 @@ __global__ void edge_assign_kernel(const int32_t* __restrict__ edges, int64_t nn
   tval[pos] = mrow;
 }
 
-// one thread per node: insertion sort of its (key, val) segment, then emit tmsg
+// one thread per node: insertion sort of its (key, val) segment by (channel, source), then emit tmsg.  Slots inside a
+// segment were handed out with atomicAdd, so edges with EQUAL keys (duplicate (src, channel, dst) triples) end up in
+// arbitrary relative order -- harmless: their message values are identical, so the sum does not depend on it.
+// O(d^2) per node: fine for the in-degrees of the configurations (<= ~130); a hub with 1e5 in-edges would want a
+// segmented sort instead.
 __global__ void target_sort_kernel(const int32_t* __restrict__ tptr, int64_t N,
                                    unsigned long long* __restrict__ tkey,
                                    int32_t* __restrict__ tval) {

@@ -60,8 +60,9 @@ extern "C" {
 #define GGNN_PREC_F16   2   /* tcgen05 kind::f16: operands rounded to FP16 (the same 11-bit significand
                              * as TF32) and held in 16-bit containers, FP32 accumulate, FP32 gate math,
                              * FP32 result; <= 2e-3 norm-wise.  Hidden size in (96, 512].  Needs
-                             * h*max|W|*max(max|h0|,1) + max|B| < 64 so nothing leaves the FP16 range;
-                             * otherwise the call returns GGNN_E_UNSUPPORTED (use GGNN_PREC_TF32).    */
+                             * max_(e,n) sum_k |W[e][k][n]| * max(max|h0|,1) + max|B| < 64 (largest column L1 norm
+                             * of any edge weight matrix) so nothing leaves the FP16 range; otherwise the call
+                             * returns GGNN_E_UNSUPPORTED (use GGNN_PREC_TF32).    */
 
 /* weight slot: 0 = edge_weights / edge_biases (chem_tensorflow_dense.py:202-206),
  *              1 = edge_weights_fixed / edge_biases_fixed (:208-212), used when the
@@ -161,7 +162,7 @@ int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0,
 /* Edge-list form (A9): h0/h_out float32 [N, h]; edges int32 [nnz, 3] rows
  * (src, channel, dst), channel 0-based in [0, two_e), node ids global in [0, N).
  * acts[dst] = sum over edges (h[src] @ W[channel] + B[channel]); messages into one
- * node are summed in ascending (channel, src) order, edge-list order for ties. */
+ * node are summed in ascending (channel, src) order (duplicate triples, whose messages are identical, in any order). */
 int ggnn_propagate_edges(ggnn_ctx* ctx, int slot, const float* h0,
                          const int32_t* edges, int64_t nnz, int64_t N,
                          int T, int precision, unsigned flags,

@@ -171,6 +171,22 @@ def test_range_guard_and_unsupported_hidden_size():
         ggnn_b200.compute_final_node_representations(big, adj, weights=w, num_timesteps=2, precision="f16")
     out = ggnn_b200.compute_final_node_representations(big, adj, weights=w, num_timesteps=2, precision="tf32")
     assert np.isfinite(out).all()
+    # the guard is the largest COLUMN L1 NORM of any W_e, not h * max|W|: a checkpoint with a few large weights
+    # (max|W| = 0.3 at h = 400: the old worst-case bound 120 >= 64 refused it) stays on the F16 path ...
+    w4 = O.make_weights(6, 400, 3)
+    w4["edge_weights"] = (w4["edge_weights"] * 0.4).astype(np.float32)
+    w4["edge_weights"][:, ::37, ::41] = 0.3
+    col = np.abs(w4["edge_weights"]).sum(axis=1).max()
+    assert np.abs(w4["edge_weights"]).max() == np.float32(0.3) and 400 * 0.3 >= 64 and col < 40
+    _, adj4 = _trees(3, 16, 3, seed=1)
+    h4 = _h0(3, 16, 400)
+    o4 = ggnn_b200.compute_final_node_representations(h4, adj4, weights=w4, num_timesteps=2, precision="f16")
+    assert O.normwise_err(o4, O.propagate_dense(h4, adj4, w4, 2)) <= TOL
+    # ... and one whose column norms really are too large is still refused
+    w5 = O.make_weights(6, 400, 3)
+    w5["edge_weights"][2, :, 7] = 0.2                   # one column: 400 * 0.2 = 80
+    with pytest.raises(RuntimeError, match="FP16 range"):
+        ggnn_b200.compute_final_node_representations(h4, adj4, weights=w5, num_timesteps=2, precision="f16")
     w64 = O.make_weights(6, 64, 0)
     with pytest.raises(RuntimeError, match="hidden size"):
         ggnn_b200.compute_final_node_representations(_h0(2, 8, 64), adj, weights=w64, num_timesteps=2, precision="f16")
