@@ -419,13 +419,37 @@ def measure_c3(args, env):
         barrier()
         rms = max_over_ranks(f0.elapsed_time(f1), dev, world) / args.steps
         tot = lambda x: sum_over_ranks(float(x), dev, world)
+        # the same sentences as ONE packed edge list (CSR straight from the triples, rows = bucket size):
+        # one ggnn_propagate_edges call instead of one dense call per bucket
+        tri_all = synth.random_trees(ng, int(lengths.max()), E, seed=4000 + rank, lengths=lengths)
+        edges_p, off_p = synth.packed_edge_list(tri_all, bsz, E)
+        edges_p = edges_p.to(dev)
+        hp_ = (torch.rand(int(off_p[-1]), H, device=dev, generator=gen) - 0.5) * 0.2
+        outp = torch.empty_like(hp_)
+        for _ in range(max(1, args.warmup)):
+            prop.propagate_edges(hp_, edges_p, num_timesteps=T, precision=precision, out=outp)
+        barrier()
+        f0.record()
+        for _ in range(args.steps):
+            prop.propagate_edges(hp_, edges_p, num_timesteps=T, precision=precision, out=outp)
+        f1.record()
+        barrier()
+        pms = max_over_ranks(f0.elapsed_time(f1), dev, world) / args.steps
         ragged = {"value": tot(ng) / (rms * 1e-3), "unit": "graphs/s", "ms_per_step": rms, "graphs_per_step": int(tot(ng)),
                   "buckets": len(groups), "mean_words": float(lengths.float().mean()),
                   "node_updates_per_s_padded_rows": tot(padded_nodes) * T / (rms * 1e-3),
                   "node_updates_per_s_real_nodes": tot(real_nodes) * T / (rms * 1e-3),
                   "adjacency_bytes_per_step": int(tot(sum(a.numel() * 4 for a, _ in groups))),
                   "note": "C2 sentence-length distribution, even bucket sizes 4..128, one dense FP32 batch per bucket "
-                          "(v < 128: generic gather route, no word-order fold)"}
+                          "(v < 128: generic gather route, no word-order fold)",
+                  "as_one_packed_edge_list": {
+                      "value": tot(ng) / (pms * 1e-3), "unit": "graphs/s", "ms_per_step": pms,
+                      "node_updates_per_s_padded_rows": tot(padded_nodes) * T / (pms * 1e-3),
+                      "node_updates_per_s_real_nodes": tot(real_nodes) * T / (pms * 1e-3),
+                      "edges_per_step": int(tot(edges_p.shape[0])),
+                      "note": "same length distribution, rows padded to the bucket size like the dense batches, handed over as "
+                              "(src, channel, dst) triples in ONE ggnn_propagate_edges call (no dense adjacency, no per-bucket launches)"}}
+        del edges_p, hp_, outp
         del groups
 
     if rank == 0:
