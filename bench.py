@@ -51,9 +51,13 @@ def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops"]),
-                "bf16_tflops_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
-                "source": "measured (MEASURED_PEAKS.json)"}
+        out = {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops"]),
+               "bf16_tflops_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+               "source": "measured (MEASURED_PEAKS.json)"}
+        t = os.path.join(ROOT, "profiles", "r2_tf32_peak.json")     # same protocol, TF32 (scripts/measure_tf32_peak.py)
+        if os.path.exists(t):
+            out["tf32_tflops_sustained"] = float(json.load(open(t))["tf32_tflops_sustained"])
+        return out
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0,
             "source": "fallback (B200_PROFILING.md)"}
 
@@ -456,7 +460,8 @@ def measure_c3(args, env):
         steps_g = stage_steps * graphs_rank                # graph passes in the per-stage pass on this rank
         st_ms = {k: v[0] for k, v in stages.items()}
         st_ln = {k: v[1] for k, v in stages.items()}
-        tf32_peak = peaks["bf16_tflops_sustained"] / (1.0 if precision == "f16" else 2.0)   # kind::f16 runs at the BF16 rate
+        tf32_peak = peaks["bf16_tflops_sustained"] if precision == "f16" else \
+            peaks.get("tf32_tflops_sustained", peaks["bf16_tflops_sustained"] / 2.0)            # kind::f16 runs at the BF16 rate
         cand = {
             "compact_mask": ("hbm", steps_g * BYTES_COMPACT_PER_GRAPH / 1e9, "GB/s", peaks["hbm_gbs"]),
             "agg": ("hbm", steps_g * T * BYTES_AGG_PER_GRAPH_STEP / 1e9, "GB/s", peaks["hbm_gbs"]),
@@ -535,6 +540,81 @@ def measure_c3(args, env):
             line["cpu_baseline"] = cpu_baseline()
         return line
     return None
+
+
+# ---------------------------------------------------------------------------------------
+# secondary workload: BASELINE config 2 (WSJ-shaped evaluation: embed -> propagate -> heads -> decode -> LAS/UAS)
+# ---------------------------------------------------------------------------------------
+def measure_c2(args, env):
+    import ggnn_b200
+    from ggnn_b200 import parser_eval as PE, synth
+    world, rank, local, dev = env
+    n_sent, Hc, Ec, E_out, Tc = args.c2_sentences, 400, 46, 45, 4
+    rng = np.random.default_rng(0)
+    r = lambda *s_: (np.sqrt(6.0 / (s_[-2] + s_[-1])) * rng.uniform(-1, 1, s_)).astype(np.float32)
+    wd = synth.make_weights(2 * Ec, Hc, 0)
+    w = ggnn_b200.from_dict(wd, {"num_timesteps": Tc, "hidden_size": Hc})
+    heads = PE.ParserHeads(loc_embeddings=r(150, 80), pos_embeddings=r(48, 50), word_embeddings=r(20000, 100),
+                           head_W=r(2 * Hc, 150) * 4, head_b=np.zeros(150, np.float32),
+                           label_W=r(2 * Hc, E_out) * 4, label_b=np.zeros(E_out, np.float32))
+    recs = synth.wsj_like_corpus(n_sent, Ec, E_out, pos_size=48, vocab=20000, seed=rank)
+    ev = PE.ParserEvaluator(w, heads, dev, num_timesteps=Tc)
+
+    def timed(precision, batch):
+        ev.evaluate(recs[:64], batch_size=batch, precision=precision)        # warm-up
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res, per = ev.evaluate(recs, batch_size=batch, precision=precision)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0, dev, world)
+        return {"value": n_sent * world / dt, "unit": "sentences/s", "seconds": dt, "LAS": res["LAS"], "UAS": res["UAS"]}, per
+
+    runs = {}
+    strict20, per_strict = timed("fp32", 20)
+    runs["fp32_batch20"] = strict20
+    runs["f16_batch20"], per_f16 = timed("f16", 20)
+    runs["f16_batch512"], per_f16b = timed("f16", 512)
+    runs["fp32_batch512"], per_strictb = timed("fp32", 512)
+    if rank != 0:
+        return None
+    line = {"metric": "WSJ-shaped evaluation sentences/sec (embed -> propagate T=4 -> heads -> decode -> LAS/UAS)",
+            "value": runs["f16_batch512"]["value"], "unit": "sentences/s", "n_gpus": world, "higher_is_better": True,
+            "scaling": "weak", "data": "synthetic",
+            "config": {"workload": "C2 synthetic WSJ twin (SURVEY 8(d)): lognormal lengths, 45 labels, 2E=92, h=400, T=4, "
+                                   "buckets of even sizes like the reference; edges fed as triples (N3); host decode + scorer",
+                       "sentences_per_gpu": n_sent, "note": "WSJ data / pickle not present (LDC-licensed, SURVEY F6)"},
+            "runs": runs,
+            "f16_sentences_scoring_differently_from_strict": int((np.abs(per_f16 - per_strict).max(axis=1) > 0).sum()),
+            "batch_size_changes_any_score": bool(not np.array_equal(np.sort(per_strictb, 0), np.sort(per_strict, 0)))}
+    if world == 1 and not args.no_cpu:
+        # the oracle pipeline (CPU, NumPy FP64 propagation) on a small sample: CPU baseline AND the identity check
+        from oracle import ggnn_oracle as O
+        from oracle import parser_oracle as P
+        n = 40
+        sample = recs[:n]
+        t0 = time.perf_counter()
+        per = []
+        for v, items in PE.make_batches(sample, 20):
+            idx, edges, n_active, _ = PE.batch_arrays(v, items, Ec)
+            h0 = P.initial_node_representation(idx, heads.loc_embeddings, heads.pos_embeddings, heads.word_embeddings, Hc)
+            adj = np.stack([O.graph_to_adj_mat_bd(rr["graph"], v, Ec) for rr in items])
+            hT = O.propagate_dense(h0, adj, wd, Tc)
+            ph, pe = P.heads(hT, h0, heads.head_W, heads.head_b, heads.label_W, heads.label_b)
+            masks = np.stack([P.get_mask(int(k), v, E_out, PE.OUTPUT_SIZE) for k in n_active])
+            masks_e = np.stack([P.get_mask(int(k), v, E_out, PE.OUTPUT_SIZE, is_edge=True) for k in n_active])
+            labels = [P.target_to_adj_mat(rr["targets"], v, E_out, v) for rr in items]
+            sc, _ = P.score_batch(P.target_values(labels, PE.OUTPUT_SIZE), ph, masks, P.target_values_edges(labels), pe,
+                                  masks_e, v, E_out, PE.OUTPUT_SIZE)
+            per.append(sc)
+        dt = time.perf_counter() - t0
+        ref = np.concatenate(per)
+        _, got = ev.evaluate(sample, batch_size=20, precision="fp32")
+        _, got16 = ev.evaluate(sample, batch_size=20, precision="f16")
+        line["cpu_baseline"] = {"value": n / dt, "unit": "sentences/s", "cores": os.cpu_count(), "kind": "port",
+                                "sample": f"{n} sentences through the oracle pipeline (NumPy FP64 propagation + the reference's decode / scorer restated)"}
+        line["per_sentence_scores_identical_to_oracle"] = {"fp32": bool(np.array_equal(ref, got)), "f16": bool(np.array_equal(ref, got16)),
+                                                           "sentences": n}
+    return line
 
 
 # ---------------------------------------------------------------------------------------
@@ -759,7 +839,7 @@ def measure_c4(args, env, precision=None):
         peaks = load_peaks()
         sm = line["stages_ms_per_step"]
         gsteps = per_gpu * Tc
-        tpeak = peaks["bf16_tflops_sustained"] * (0.5 if prec == "tf32" else 1.0)
+        tpeak = peaks["bf16_tflops_sustained"] if prec != "tf32" else peaks.get("tf32_tflops_sustained", peaks["bf16_tflops_sustained"] / 2.0)
         def tens(ms, flop):
             a = flop * gsteps / (ms * 1e-3) / 1e12
             return {"bound": "tensor", "ms_per_step": ms, "achieved": a, "unit": "TFLOP/s", "peak": tpeak, "frac": a / tpeak}
@@ -819,7 +899,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-prefetch", action="store_true", help="c3: do not announce the next call's adjacency (A-B switch)")
     ap.add_argument("--no-fp32", action="store_true", help="skip the passes in the other arithmetic modes (c3 workload)")
-    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
+    ap.add_argument("--c2-sentences", type=int, default=2416, help="sentences per GPU of the c2 sub-record (WSJ test set size)")
+    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5"],
                     help="c3 = the headline forward benchmark; c5 = training step (secondary line)")
     ap.add_argument("--c4-graphs", type=int, default=64, help="graphs per GPU of the c4 workload")
     ap.add_argument("--c5-graphs", type=int, default=2048, help="graphs per GPU of the c5 workload")
@@ -831,7 +912,9 @@ def main():
     import torch.distributed as dist
     env = init_env()
     world, rank = env[0], env[1]
-    if args.workload == "c5":
+    if args.workload == "c2":
+        line = measure_c2(args, env)
+    elif args.workload == "c5":
         line = measure_c5(args, env)
     elif args.workload == "c4":
         line = measure_c4(args, env)
@@ -844,8 +927,10 @@ def main():
             c4 = measure_c4(args, env, precision="f16")
             torch.cuda.empty_cache()
             c5 = measure_c5(args, env, precision="f16")
+            torch.cuda.empty_cache()
+            c2 = measure_c2(args, env)
             if rank == 0:
-                line["c4"], line["c5"] = c4, c5
+                line["c2"], line["c4"], line["c5"] = c2, c4, c5
                 line["gpu_launches"] += c4["gpu_launches"] + c5["gpu_launches"]
     if rank == 0:
         print(json.dumps(line), flush=True)
