@@ -160,6 +160,7 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
   if (c->Wgt_f16) cudaFree(c->Wgt_f16);
   if (c->Wct_f16) cudaFree(c->Wct_f16);
   free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->Wgt_tf32_lo); free_dev(c, c->Wct_tf32_lo); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
+  if (c->btab16) cudaFree(c->btab16);
   free_dev(c, c->bg_w16); free_dev(c, c->bc_w16);
   if (c->ws) {
     ctx_ext* e = ext_of(c);
@@ -239,6 +240,7 @@ extern "C" int ggnn_set_weights(ggnn_ctx* ctx, int slot, int two_e, int h, const
         free_dev(ctx, ctx->edge[s2].B_pad16);
       }
       if (ctx->Wgt_f16) { cudaFree(ctx->Wgt_f16); ctx->Wgt_f16 = nullptr; }
+      ctx->pair_ok = false;
       if (ctx->Wct_f16) { cudaFree(ctx->Wct_f16); ctx->Wct_f16 = nullptr; }
       free_dev(ctx, ctx->bg_w16); free_dev(ctx, ctx->bc_w16);
     }

@@ -21,6 +21,7 @@ struct ggnn_edge_weights {
   CUtensorMap tm_Wt_lo;
   void*  Wt_f16 = nullptr; // [two_e, P, P] FP16, transposed ([n][k]), zero padded; P = 128 (hp == 128) or hw16 (h > 128)
   CUtensorMap tm_Wt16;     // TMA view of Wt_f16 as [two_e*128 rows, 128 cols], box 64 x 128
+  CUtensorMap tm_Wt16q;    // same, box 64 x 64 rows (gru_pair.cu: half of a matrix's output columns per CTA)
   float* B_pad16 = nullptr;// [two_e, hw16] FP32 zero-padded biases (wide16.cu, h > 128)
   // word-order channels E-1 / 2E-1 folded through the GRU input weights (f16.cu, hp == 128, two_e even)
   void*  fold_f16 = nullptr;   // [2][384][128] FP16, K-major
@@ -56,6 +57,10 @@ struct ggnn_ctx {
   void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
   void* Wct_f16 = nullptr;   // [128, 256]
   CUtensorMap tm_Wg16, tm_Wc16;
+  CUtensorMap tm_Wc16q;      // box 64 x 64 rows (gru_pair.cu)
+  float* btab16 = nullptr;   // [slots][640] gru_pair.cu's bias table (gp::bias_tab)
+  bool   btab_ok[GGNN_MAX_SLOTS] = {false, false};
+  bool   pair_ok = false;    // tm_Wc16q is current
   CUtensorMap tm_Wg16h, tm_Wc16h;   // same, boxes of hw16 / 2 rows (CTA pairs)
   CUtensorMap tm_Wg16f, tm_Wc16f;   // wide16.cu fused GRU kernel (hw16 <= 256): boxes of hw16 rows
   float* bg_w16 = nullptr;   // [2*hw16], [hw16] zero-padded GRU biases (wide16.cu)
@@ -88,7 +93,8 @@ struct ggnn_ctx {
 
 // cudaFuncSetAttribute is per device: remember per ctx (a process may own one ctx per GPU), not in a static
 enum { GGNN_ATTR_TF32_GEMM0 = 0 /* + mode 0..3 */, GGNN_ATTR_GRU_FUSED = 4, GGNN_ATTR_MSG_TC = 5, GGNN_ATTR_F16 = 6,
-       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */, GGNN_ATTR_BMQ = 13, GGNN_ATTR_STRICT_TC = 14 };
+       GGNN_ATTR_TN = 7, GGNN_ATTR_W16_0 = 8 /* + mode 0..2, 3 = fused GRU, 4 = fused GRU on CTA pairs */, GGNN_ATTR_BMQ = 13, GGNN_ATTR_STRICT_TC = 14,
+       GGNN_ATTR_GRU_PAIR = 15 };
 #define GGNN_ENSURE_SMEM(ctx, bit, kernel, bytes)                                                          \
   do {                                                                                                     \
     if (!((ctx)->attr_mask & (1u << (bit)))) {                                                             \

@@ -837,6 +837,7 @@ int ggnn_f16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t s
       if (s2 != slot && ctx->edge[s2].set) GGNN_TRY(fold_slot(ctx, s2, st));
   }
   GGNN_TRY(fold_slot(ctx, slot, st));
+  GGNN_TRY(ggnn_gru_pair_pack(ctx, slot, with_gru, st));
   return GGNN_OK;
 }
 
@@ -903,6 +904,10 @@ int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     prof_scope ps(ctx, GGNN_STAGE_MSG, st);
     msg16::msg_f16_kernel<<<grid, msg16::NTHREADS, msg16::SMEM_BYTES, st>>>(p, ew.tm_Wt16, tmOut);
     GGNN_LAUNCHED(ctx);
+  }
+  if (ggnn_gru_pair_enabled(ctx, slot)) {                // CTA pairs, resident weights (gru_pair.cu)
+    prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+    return ggnn_gru_pair_launch(ctx, slot, plan, msg16, state16, last_step ? h_out : nullptr, st);
   }
   CUtensorMap tmH;
   GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &tmH, state16, plan.N, HP, BKH, BM));
