@@ -57,10 +57,11 @@ struct ggnn_ctx {
   void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
   void* Wct_f16 = nullptr;   // [128, 256]
   CUtensorMap tm_Wg16, tm_Wc16;
-  CUtensorMap tm_Wc16q;      // box 64 x 64 rows (gru_pair.cu)
+  CUtensorMap tm_Wc16q, tm_Wg16q;   // boxes of 64 x 64 rows (gru_pair.cu)
   float* btab16 = nullptr;   // [slots][640] gru_pair.cu's bias table (gp::bias_tab)
   bool   btab_ok[GGNN_MAX_SLOTS] = {false, false};
-  bool   pair_ok = false;    // tm_Wc16q is current
+  bool   pair_ok = false;    // tm_Wc16q / tm_Wg16q are current
+  int    pair_fit = -1;      // a CTA pair of gru_pair_kernel can be resident on this device: 1 / 0, -1 = not asked yet
   CUtensorMap tm_Wg16h, tm_Wc16h;   // same, boxes of hw16 / 2 rows (CTA pairs)
   CUtensorMap tm_Wg16f, tm_Wc16f;   // wide16.cu fused GRU kernel (hw16 <= 256): boxes of hw16 rows
   float* bg_w16 = nullptr;   // [2*hw16], [hw16] zero-padded GRU biases (wide16.cu)

@@ -21,8 +21,8 @@ int ggnn_colnorm_max(ggnn_ctx* ctx, const float* W, int two_e, int h, unsigned* 
 int ggnn_step_f16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16,
                   float* h_out, bool last_step, cudaStream_t st);
 
-// ---- gru_pair.cu: the GRU kernel of the h <= 128 timestep on CTA pairs with resident weights (GGNN_GRU_PAIR=0: off) ----
-bool ggnn_gru_pair_enabled(const ggnn_ctx* ctx, int slot);
+// ---- gru_pair.cu: the GRU kernel of the h <= 128 timestep on CTA pairs with resident weights (the default; GGNN_GRU_PAIR=0: gru_f16_kernel) ----
+bool ggnn_gru_pair_enabled(ggnn_ctx* ctx, int slot);
 int ggnn_gru_pair_pack(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st);   // after ggnn_f16_pack_weights' packs
 int ggnn_gru_pair_launch(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const void* msg16, void* state16, float* h_out,
                          cudaStream_t st);

@@ -4,22 +4,34 @@
 // Why: gru16::gru_f16_kernel (f16.cu) re-streams 256-384 KB of weights from L2 for every 128-node tile and is bound by
 // the latency of that stream (scripts/experiments/README.md).  A CTA pair working on two adjacent tiles as one 256-row
 // MMA tile needs only HALF of every weight matrix's output columns per CTA:
-//     [x,h] -> r|u  (N = 256: the even CTA holds the r columns, the odd CTA the u columns)   64 KB per CTA
+//     [x,h] -> r, u  (N = 128 each: 64 columns of r and 64 of u per CTA)                      64 KB per CTA
 //     [x,r*h] -> cand (N = 128: 64 columns each)                                             32 KB
 //     W[E-1], W[2E-1] (the two word-order channels, N = 128 each: 64 columns each)           32 KB
 // = 128 KB, loaded once.  What moves per tile is the state tile (32 KB in, 32 KB out) and the message rows.
 //
 // Per pair of tiles `it` (both CTAs run the same roles on their own tile; the even CTA's thread issues all MMAs):
-//   TMA warp     h tile -> H[it & 1] (two tiles deep); after the epilogue: TMA store of h' from the same buffer, reload
+//   TMA warp     lane 0: h tile -> H[it & 1] (two tiles deep); after the epilogue the TMA store of h' from the same buffer,
+//                then its refill.  Lanes 1-31: L2 prefetch of the message rows three tiles ahead.
+//   agg warps    x = sum of the tile's FP16 message rows (24 rows per warp in flight through registers, branch-free
+//                summation) -> x tile.  The x tile is free again as soon as the MMAs reading it have retired (r*h does NOT
+//                go there), so the gather of tile it+1 runs under the whole epilogue of tile it.
 //   MMA          word-order messages of a regular tile: Zp = h[t-1] @ W[E-1], Zn = h[t+1] @ W[2E-1] (row-shifted A
-//                descriptors on the resident h tile, scripts/micro/desc_shift.cu) into the idle r accumulator and the
-//                spare 128 TMEM columns -- issued one tile AHEAD, under the previous tile's candidate
-//   agg warps    x = sum of the tile's FP16 message rows (gathered through registers), then x += Zp + b[E-1] (rows >= 1)
-//                + Zn + b[2E-1] (rows <= 126) for a regular tile
-//   MMA          r|u = [x,h] @ Wg (one N = 256 instruction stream), cand = x @ Wc[:h]
-//   epilogue     r -> f16(r*h) over x;  u -> TMEM;  MMA cand += (r*h) @ Wc[h:];  h' = c + u (h - c) over the h tile
+//                descriptors on the resident h tile, scripts/micro/desc_shift.cu) into the r accumulator columns and the
+//                spare 128 TMEM columns -- issued one tile AHEAD, right after the previous tile's candidate
+//   epilogue     (after its last pass on tile it-1) z = Zp + b[E-1] (rows >= 1) + Zn + b[2E-1] (rows <= 126), split into
+//                FP16 hi + lo and written back to TMEM in the tensor core's A-operand form (complete_z)
+//   MMA          r = x @ Wr_x + h @ Wr_h + z @ Wr_x   (z: A operand FROM TENSOR MEMORY, same weights as x: the word-order
+//                messages are part of x in the reference, but never pass through x's FP16 rounding here), h @ Wu_h;
+//                then u's x and z parts, cand = (x + z) @ Wc_x
+//   epilogue     1a: r -> f16(r*h) over h in the h tile (h stays in registers);  1b: u (16-bit fixed point) | h -> u's TMEM
+//                word;  MMA cand += (r*h) @ Wc_h;  2: h' = c + u (h - c) over r*h in the h tile -> TMA store
 // The row that falls off a shifted tile reads whatever lies next to the h tile in shared memory; that row of Zp / Zn is
-// never used (row 0 has no t-1, row 127 no t+1), so no zeroed gaps are needed.
+// masked out in complete_z (row 0 has no t-1, row 127 no t+1), so no zeroed gaps are needed.
+//
+// Shared memory: x 32 KB | h 2 x 32 KB | weights 128 KB | barriers, the two edge biases: 230 656 B -- one background CTA
+// of compact.cu's bitmask queue still fits next to it.  The GRU biases live in registers (6 per epilogue lane, broadcast by
+// shuffle): no shared memory is left for them and both L1 and the constant bank cost a cache round trip per 16 columns.
+// Phase trace: scripts/gpu_pair_trace.py (GP_TRACE).
 #include "f16.cuh"
 #include "tf32.cuh"
 #include "tc.cuh"
@@ -42,8 +54,8 @@ constexpr int NTHREADS = (WARP_AGG0 + N_AGG) * 32;   // 512: 4 warps per schedul
 constexpr int OFF_X = 0;                          // x tile, later f16(r*h)
 constexpr int OFF_H = TILE;                       // two h tiles
 constexpr int OFF_W = 3 * TILE;
-constexpr int W_RUX = 0;                          // [128 n x 128 k] as two K chunks of 16 KB: x -> r (even CTA) / u (odd)
-constexpr int W_RUH = W_RUX + TILE;               // h -> r / u
+constexpr int W_RUX = 0;                          // two K chunks of 16 KB, each [64 n of r | 64 n of u] x 64 k: x -> r, u
+constexpr int W_RUH = W_RUX + TILE;               // h -> r, u
 constexpr int W_CX = W_RUH + TILE;                // [64 n x 128 k] as two K chunks of 8 KB: x -> cand
 constexpr int W_CRH = W_CX + TILE / 2;            // r*h -> cand
 constexpr int W_ZP = W_CRH + TILE / 2;            // W[E-1]
@@ -60,7 +72,8 @@ enum {
   BAR_H_STORE = BAR_H_FULL + 2,   // [2] local: the 8 epilogue warps have written h' into the h tile
   BAR_Z_DONE = BAR_H_STORE + 2,   // multicast commit: Zp / Zn of the tile are in TMEM
   BAR_X_FULL,           // even CTA: 2 x 4 completion warps: x tiles final
-  BAR_RU_DONE,          // multicast commit
+  BAR_R_DONE,           // multicast commit: reset gate complete (it goes first: r*h is on the critical path)
+  BAR_U_DONE,           // multicast commit: update gate complete
   BAR_X_READ,           // multicast commit: every MMA reading x has retired: the buffer may take the next tile's sums
   BAR_RH_FULL,          // even CTA: 16 epilogue warps
   BAR_CAND_DONE,        // multicast commit: candidate complete
@@ -136,42 +149,57 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return v;
 }
 
-// x += Zp + b[E-1] (rows >= 1) + Zn + b[2E-1] (rows <= 126): one warp per TMEM lane quarter, thread = row.
-__device__ __forceinline__ void complete_x(uint8_t* xtile, uint32_t tmem_base, int q4, int lane, const float* s_eb,
-                                           uint32_t zbar, uint32_t parity, unsigned long long* trc) {
-  const int r = q4 * 32 + lane;        // TMEM lane quarter of this warp, row of this thread
+// The word-order messages of a regular tile, z = Zp + b[E-1] (rows >= 1) + Zn + b[2E-1] (rows <= 126), become a SECOND A
+// operand of the gate MMAs instead of being added to the FP16 x tile (that sum, rounded to FP16, doubled the mode's error on
+// word-order graphs): z is split into FP16 hi + lo (22 significant bits) and written back into the Zn columns in the tensor
+// core's A-operand form -- K-group c (16 columns of z) = 8 columns of hi at 16c, 8 columns of lo at 16c + 8, exactly the
+// columns this iteration has just read.  Done by the EPILOGUE warps (two per TMEM lane quarter, 64 columns each, thread =
+// row) for the NEXT tile, right after the current tile's last pass: its accumulators are long complete by then and the
+// aggregation warps are left alone.  reg = false (the other tile of the pair is the regular one): zeros.
+__device__ __forceinline__ void complete_z(uint32_t tmem_base, int q4, int lane, int c_begin, const float* s_eb, bool reg,
+                                           uint32_t zbar, uint32_t parity) {
+  const int r = q4 * 32 + lane;
   const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
   // row 0 has no t-1, row 127 no t+1: masks instead of branches (what sits in those accumulator rows may be NaN)
-  const uint32_t mp = r >= 1 ? 0xffffffffu : 0u, mn = r <= BM - 2 ? 0xffffffffu : 0u;
-  const float fp = r >= 1 ? 1.f : 0.f, fn = r <= BM - 2 ? 1.f : 0.f;
+  const uint32_t mp = (reg && r >= 1) ? 0xffffffffu : 0u, mn = (reg && r <= BM - 2) ? 0xffffffffu : 0u;
+  const float fp = (reg && r >= 1) ? 1.f : 0.f, fn = (reg && r <= BM - 2) ? 1.f : 0.f;
   tc::mbar_wait(zbar, parity);
   tc::fence_after_sync();
-  if (trc) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); trc[21] = t_; }
-#pragma unroll 1
-  for (int c = 0; c < 8; ++c) {
-    if (trc && c == 1) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); trc[22] = t_; }
-    const int col0 = c * 16;
-    uint32_t zp[16], zn[16];
-    tc::tmem_ld16(t_lane + col0, zp);
-    tc::tmem_ld16(t_lane + 384 + col0, zn);
-    uint8_t* xr = xtile + (c >> 2) * CHUNK;
-    uint4* s0 = reinterpret_cast<uint4*>(xr + sw_off(r, 2 * (c & 3)));
-    uint4* s1 = reinterpret_cast<uint4*>(xr + sw_off(r, 2 * (c & 3) + 1));
-    float t0[8], t1[8];
-    unpack8(*s0, t0); unpack8(*s1, t1);
-    if (trc && c == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); trc[23] = t_; }
-    tc::tmem_ld_wait();
-    if (trc && c == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); trc[25] = t_; }
+  uint32_t zpv[2][16], znv[2][16];
+  tc::tmem_ld16(t_lane + c_begin * 16, zpv[0]);
+  tc::tmem_ld16(t_lane + 384 + c_begin * 16, znv[0]);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const float add = (__uint_as_float(zp[i] & mp) + __uint_as_float(zn[i] & mn)) + fmaf(fp, s_eb[col0 + i], fn * s_eb[HP + col0 + i]);
-      if (i < 8) t0[i] += add; else t1[i - 8] += add;
+  for (int cc = 0; cc < 4; ++cc) {                        // this warp's 64 columns of z; the next group's loads go first
+    const int col0 = (c_begin + cc) * 16;
+    uint32_t (&zp)[16] = zpv[cc & 1];
+    uint32_t (&zn)[16] = znv[cc & 1];
+    tc::tmem_ld_wait();
+    if (cc < 3) {
+      tc::tmem_ld16(t_lane + col0 + 16, zpv[(cc + 1) & 1]);
+      tc::tmem_ld16(t_lane + 384 + col0 + 16, znv[(cc + 1) & 1]);
     }
-    if (trc && c == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); trc[26] = t_; }
-    *s0 = pack8(t0);
-    *s1 = pack8(t1);
+    uint32_t wh[8], wl[8];
+#pragma unroll
+    for (int i = 0; i < 16; i += 4) {
+      const float4 bp = *reinterpret_cast<const float4*>(s_eb + col0 + i);
+      const float4 bn = *reinterpret_cast<const float4*>(s_eb + HP + col0 + i);
+      const float bb[4] = {fmaf(fp, bp.x, fn * bn.x), fmaf(fp, bp.y, fn * bn.y), fmaf(fp, bp.z, fn * bn.z), fmaf(fp, bp.w, fn * bn.w)};
+#pragma unroll
+      for (int j = 0; j < 4; j += 2) {
+      const float za = (__uint_as_float(zp[i + j] & mp) + __uint_as_float(zn[i + j] & mn)) + bb[j];
+      const float zb = (__uint_as_float(zp[i + j + 1] & mp) + __uint_as_float(zn[i + j + 1] & mn)) + bb[j + 1];
+      const __half2 hi = __floats2half2_rn(za, zb);
+      const float2 hf = __half22float2(hi);
+      const __half2 lo = __floats2half2_rn(za - hf.x, zb - hf.y);
+      wh[(i + j) >> 1] = *reinterpret_cast<const uint32_t*>(&hi);
+      wl[(i + j) >> 1] = *reinterpret_cast<const uint32_t*>(&lo);
+      }
+    }
+    tc::tmem_st8(t_lane + 384 + col0, wh);
+    tc::tmem_st8(t_lane + 384 + col0 + 8, wl);
   }
-  tc::fence_before_sync();                            // TMEM reads done before the accumulators are overwritten
+  tc::tmem_st_wait();
+  tc::fence_before_sync();                            // TMEM traffic done before the MMAs read / overwrite these columns
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __maxnreg__(96)
@@ -200,8 +228,9 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
       tc::mbar_init(bar(BAR_H_STORE + s), N_EPI);
     }
     tc::mbar_init(bar(BAR_Z_DONE), 1);
-    tc::mbar_init(bar(BAR_X_FULL), 8);
-    tc::mbar_init(bar(BAR_RU_DONE), 1);
+    tc::mbar_init(bar(BAR_X_FULL), 2 * N_AGG);
+    tc::mbar_init(bar(BAR_R_DONE), 1);
+    tc::mbar_init(bar(BAR_U_DONE), 1);
     tc::mbar_init(bar(BAR_X_READ), 1);
     tc::mbar_init(bar(BAR_RH_FULL), 2 * N_EPI);
     tc::mbar_init(bar(BAR_CAND_DONE), 1);
@@ -300,19 +329,11 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
           load32(cur, pb + AB);
         }
       }
-      // ---- completion: the gathered sums of the whole tile are in place once the six warps meet
       tc::fence_proxy_async();                                // every writer: its rows -> visible to the tensor core
       if (warp == WARP_AGG0 && lane == 0) GP_TRACE(18);
-      tc::named_bar_sync(2, N_AGG * 32);
-      if (warp == 12 && lane == 0) GP_TRACE(19);
-      if (warp >= 12) {
-        if (is_reg(tile)) complete_x(xtile, tmem_base, warp & 3, lane, s_eb, bar(BAR_Z_DONE), it & 1,
-                                     (p.dbg && blockIdx.x < 2 && it < 12 && warp == 12 && lane == 0) ? p.dbg + (blockIdx.x * 12 + it) * 32 : nullptr);
-        tc::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive_cta0(bar(BAR_X_FULL));
-        if (warp == 12 && lane == 0) GP_TRACE(20);
-      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive_cta0(bar(BAR_X_FULL));
+      if (warp == WARP_AGG0 && lane == 0) GP_TRACE(20);
       my_ptr = nxt_ptr;
     }
   }
@@ -320,10 +341,12 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
     // =============================== TMA: resident weights, h tiles in, h' tiles out ===============================
     if (lane == 0) {
       if (lead) tc::mbar_arrive_expect_tx(bar(BAR_W_READY), 2u * W_BYTES);
-      const int r128 = (int)rank * 128, r64 = (int)rank * 64;
+      const int r64 = (int)rank * 64;
       for (int kc = 0; kc < 2; ++kc) {
-        tc::tma_load_2d_pair(sW + W_RUX + kc * CHUNK, &tmWg, kc * BKH, r128, bar(BAR_W_READY));
-        tc::tma_load_2d_pair(sW + W_RUH + kc * CHUNK, &tmWg, HP + kc * BKH, r128, bar(BAR_W_READY));
+        tc::tma_load_2d_pair(sW + W_RUX + kc * CHUNK, &tmWg, kc * BKH, r64, bar(BAR_W_READY));                          // r
+        tc::tma_load_2d_pair(sW + W_RUX + kc * CHUNK + CHUNK / 2, &tmWg, kc * BKH, HP + r64, bar(BAR_W_READY));         // u
+        tc::tma_load_2d_pair(sW + W_RUH + kc * CHUNK, &tmWg, HP + kc * BKH, r64, bar(BAR_W_READY));
+        tc::tma_load_2d_pair(sW + W_RUH + kc * CHUNK + CHUNK / 2, &tmWg, HP + kc * BKH, HP + r64, bar(BAR_W_READY));
         tc::tma_load_2d_pair(sW + W_CX + kc * (CHUNK / 2), &tmWcq, kc * BKH, r64, bar(BAR_W_READY));
         tc::tma_load_2d_pair(sW + W_CRH + kc * (CHUNK / 2), &tmWcq, HP + kc * BKH, r64, bar(BAR_W_READY));
         tc::tma_load_2d_pair(sW + W_ZP + kc * (CHUNK / 2), &tmWeq, kc * BKH, p.zp_row + r64, bar(BAR_W_READY));
@@ -377,9 +400,8 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
   } else if (warp == WARP_MMA) {
     // =============================== MMA issuer (even CTA) ===============================
     if (lead && lane == 0) {
-      const uint32_t idesc256 = tc::umma_idesc(0 /*F16*/, 2 * BM, 256);
       const uint32_t idesc128 = tc::umma_idesc(0 /*F16*/, 2 * BM, 128);
-      const uint32_t d_ru = tmem_base, d_cand = tmem_base + 256, d_zp = tmem_base, d_zn = tmem_base + 384;
+      const uint32_t d_r = tmem_base, d_u = tmem_base + 128, d_cand = tmem_base + 256, d_zp = tmem_base, d_zn = tmem_base + 384;
       // D (+)= A tile [256 x 128] @ W^T, both K chunks; wstride = bytes between the two K chunks of this CTA's W half
       auto tile_mma = [&](uint32_t d, uint32_t a0, uint32_t w0, uint32_t wstride, uint32_t idesc, bool first) {
 #pragma unroll
@@ -388,6 +410,15 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
           for (int k = 0; k < 4; ++k)
             tc::umma_f16_pair(d, tc::umma_desc_sw128(a0 + kc * CHUNK + k * 32), tc::umma_desc_sw128(w0 + kc * wstride + k * 32),
                               idesc, (first && kc == 0 && k == 0) ? 0u : 1u);
+      };
+      // D += z @ W^T with z as the A operand in tensor memory (complete_z's layout): the same weights as x
+      auto z_mma = [&](uint32_t d, uint32_t w0, uint32_t wstride, uint32_t idesc) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const uint64_t bd = tc::umma_desc_sw128(w0 + (c >> 2) * wstride + (c & 3) * 32);
+          tc::umma_f16_pair_ts(d, tmem_base + 384 + 16 * c, bd, idesc, 1u);
+          tc::umma_f16_pair_ts(d, tmem_base + 384 + 16 * c + 8, bd, idesc, 1u);
+        }
       };
       auto z_phase = [&](int it, int t0) {                    // word-order messages of pair `it` (its h tiles must be in)
         const int hb = it & 1;
@@ -405,15 +436,22 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
       int it = 0;
       for (int tile = tile0; live(tile); tile += gridDim.x, ++it) {
         const uint32_t h0 = sH(it & 1);
-        if (it > 0) tc::mbar_wait_cluster(bar(BAR_TMEM_FREE), (it - 1) & 1);       // u and cand of the previous pair consumed
+        tc::mbar_wait_cluster(bar(BAR_TMEM_FREE), it & 1);        // u, cand of the previous pair consumed; z of this one in place
         GP_TRACE(0);
         tc::mbar_wait_cluster(bar(BAR_X_FULL), it & 1);                            // x final in both CTAs, Zp / Zn consumed
         tc::fence_after_sync();
         GP_TRACE(1);
-        tile_mma(d_ru, sX, sW + W_RUX, CHUNK, idesc256, true);                      // x -> r | u
-        tile_mma(d_ru, h0, sW + W_RUH, CHUNK, idesc256, false);                     // h -> r | u
-        tc::umma_commit_pair(bar(BAR_RU_DONE));
+        const bool preg = is_reg(tile) || is_reg(tile + 1);
+        tile_mma(d_r, sX, sW + W_RUX, CHUNK, idesc128, true);                       // x -> r
+        tile_mma(d_r, h0, sW + W_RUH, CHUNK, idesc128, false);                      // h -> r
+        if (preg) z_mma(d_r, sW + W_RUX, CHUNK, idesc128);                          // z (hi, lo) -> r
+        tile_mma(d_u, h0, sW + W_RUH + CHUNK / 2, CHUNK, idesc128, true);           // h -> u (h's last reader: r*h will replace h)
+        tc::umma_commit_pair(bar(BAR_R_DONE));
+        tile_mma(d_u, sX, sW + W_RUX + CHUNK / 2, CHUNK, idesc128, false);          // x -> u
+        if (preg) z_mma(d_u, sW + W_RUX + CHUNK / 2, CHUNK, idesc128);              // z (hi, lo) -> u
+        tc::umma_commit_pair(bar(BAR_U_DONE));
         tile_mma(d_cand, sX, sW + W_CX, CHUNK / 2, idesc128, true);                 // x -> cand
+        if (preg) z_mma(d_cand, sW + W_CX, CHUNK / 2, idesc128);                    // z (hi, lo) -> cand
         tc::umma_commit_pair(bar(BAR_X_READ));                                      // the x buffers may take the next tile's sums
         GP_TRACE(2);
         tc::mbar_wait_cluster(bar(BAR_RH_FULL), it & 1);                            // r drained, f16(r*h) in both x buffers
@@ -438,67 +476,100 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
     const float* bt = p.btab + chalf * 64 + lane;
     const float br0 = __ldg(bt), br1 = __ldg(bt + 32), bu0 = __ldg(bt + HP), bu1 = __ldg(bt + HP + 32);
     const float bc0 = __ldg(bt + 2 * HP), bc1 = __ldg(bt + 2 * HP + 32);
+    auto z_ready = [&](int it, int tile) {                    // z of pair `it` -> A operand form; then "TMEM free" phase `it`
+      if (is_reg(tile) || is_reg(tile ^ 1))
+        complete_z(tmem_base, ew, lane, chalf * 4, s_eb, is_reg(tile), bar(BAR_Z_DONE), it & 1);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive_cta0(bar(BAR_TMEM_FREE));
+    };
+    if (live(tile0)) z_ready(0, tile0);
     int it = 0;
     for (int tile = tile0; live(tile); tile += gridDim.x, ++it) {
       const int hb = it & 1;
       uint8_t* hrow = smem_al + OFF_H + hb * TILE + chalf * CHUNK;      // + sw_off(r, slot): this thread's h row, its 64 columns
-      // ---- pass 1: both gates.  f16(r*h) replaces h in the h tile (every MMA reading h has retired with r|u; the x
-      //      buffer is already being refilled for the next tile); u (FP16) and the h it displaces go into u's TMEM word
-      tc::mbar_wait(bar(BAR_RU_DONE), it & 1);
+      // ---- pass 1a: reset gate.  f16(r*h) replaces h in the h tile (every MMA reading h has retired with r; the x
+      //      buffer is already being refilled for the next tile); the h it displaces stays in registers for pass 1b
+      tc::mbar_wait(bar(BAR_R_DONE), it & 1);
       tc::fence_after_sync();
       if (tid == 0) GP_TRACE(8);
-#pragma unroll 1
+      // (all passes: the TMEM loads of group c16 + 1 are issued before the math of group c16 -- a load takes ~0.3 us)
+      uint32_t hkeep[4][8];
+      uint32_t av[2][16];
+      tc::tmem_ld16(t_lane + chalf * 64, av[0]);
+#pragma unroll
       for (int c16 = 0; c16 < 4; ++c16) {
-        const int col0 = chalf * 64 + c16 * 16;
-        uint32_t ar[16], au[16];
-        tc::tmem_ld16(t_lane + col0, ar);
-        tc::tmem_ld16(t_lane + 128 + col0, au);
+        uint32_t (&ar)[16] = av[c16 & 1];
         uint4* s0 = reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16));
         uint4* s1 = reinterpret_cast<uint4*>(hrow + sw_off(r, 2 * c16 + 1));
         const uint4 h0 = *s0, h1 = *s1;
-        const uint32_t hbits[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-        const float brs = c16 < 2 ? br0 : br1, bus = c16 < 2 ? bu0 : bu1;
+        hkeep[c16][0] = h0.x; hkeep[c16][1] = h0.y; hkeep[c16][2] = h0.z; hkeep[c16][3] = h0.w;
+        hkeep[c16][4] = h1.x; hkeep[c16][5] = h1.y; hkeep[c16][6] = h1.z; hkeep[c16][7] = h1.w;
+        const float brs = c16 < 2 ? br0 : br1;
         const int l0 = (c16 & 1) * 16;
         tc::tmem_ld_wait();
+        if (c16 < 3) tc::tmem_ld16(t_lane + chalf * 64 + (c16 + 1) * 16, av[(c16 + 1) & 1]);
         uint32_t rh[8];
 #pragma unroll
         for (int i = 0; i < 16; i += 2) {
-          const float2 hv = __half22float2(*reinterpret_cast<const __half2*>(&hbits[i >> 1]));
+          const float2 hv = __half22float2(*reinterpret_cast<const __half2*>(&hkeep[c16][i >> 1]));
           const float ra = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(ar[i]), -kLog2e, __shfl_sync(0xffffffffu, brs, l0 + i))));
           const float rb = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(ar[i + 1]), -kLog2e, __shfl_sync(0xffffffffu, brs, l0 + i + 1))));
           const __half2 pr = __floats2half2_rn(ra * hv.x, rb * hv.y);
           rh[i >> 1] = *reinterpret_cast<const uint32_t*>(&pr);
-          const float ua = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(au[i]), -kLog2e, __shfl_sync(0xffffffffu, bus, l0 + i))));
-          const float ub = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(au[i + 1]), -kLog2e, __shfl_sync(0xffffffffu, bus, l0 + i + 1))));
-          // u in (0, 1) as 16-bit fixed point (|error| <= 2^-17; FP16 would lose up to 2^-12): 2^23 + 65535 u, low 16 bits
-          au[i] = (__float_as_uint(fmaf(ua, 65535.0f, 8388608.0f)) & 0xffffu) | (hbits[i >> 1] << 16);
-          au[i + 1] = (__float_as_uint(fmaf(ub, 65535.0f, 8388608.0f)) & 0xffffu) | (hbits[i >> 1] & 0xffff0000u);
         }
         *s0 = make_uint4(rh[0], rh[1], rh[2], rh[3]);
         *s1 = make_uint4(rh[4], rh[5], rh[6], rh[7]);
-        tc::tmem_st16(t_lane + 128 + col0, au);
       }
-      tc::tmem_st_wait();
       tc::fence_before_sync();                                // r has been read: the next pair's Zp may land there
       tc::fence_proxy_async();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive_cta0(bar(BAR_RH_FULL));
       if (tid == 0) GP_TRACE(9);
+      // ---- pass 1b (under the r*h MMAs): update gate; u (16-bit fixed point) and h go into u's TMEM word
+      tc::mbar_wait(bar(BAR_U_DONE), it & 1);
+      tc::fence_after_sync();
+      tc::tmem_ld16(t_lane + 128 + chalf * 64, av[0]);
+#pragma unroll
+      for (int c16 = 0; c16 < 4; ++c16) {
+        const int col0 = chalf * 64 + c16 * 16;
+        uint32_t (&au)[16] = av[c16 & 1];
+        const float bus = c16 < 2 ? bu0 : bu1;
+        const int l0 = (c16 & 1) * 16;
+        tc::tmem_ld_wait();
+        if (c16 < 3) tc::tmem_ld16(t_lane + 128 + col0 + 16, av[(c16 + 1) & 1]);
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+          const float ua = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(au[i]), -kLog2e, __shfl_sync(0xffffffffu, bus, l0 + i))));
+          const float ub = tc::rcp_approx(1.0f + tc::ex2_approx(fmaf(__uint_as_float(au[i + 1]), -kLog2e, __shfl_sync(0xffffffffu, bus, l0 + i + 1))));
+          // u in (0, 1) as 16-bit fixed point (|error| <= 2^-17; FP16 would lose up to 2^-12): 2^23 + 65535 u, low 16 bits
+          au[i] = (__float_as_uint(fmaf(ua, 65535.0f, 8388608.0f)) & 0xffffu) | (hkeep[c16][i >> 1] << 16);
+          au[i + 1] = (__float_as_uint(fmaf(ub, 65535.0f, 8388608.0f)) & 0xffffu) | (hkeep[c16][i >> 1] & 0xffff0000u);
+        }
+        tc::tmem_st16(t_lane + 128 + col0, au);
+      }
+      tc::tmem_st_wait();
+      if (tid == 0) GP_TRACE(10);
       // ---- pass 2: candidate and new state h' = c + u (h - c): FP16 over r*h in the h tile (the MMAs reading it have
       //      retired) for the TMA store; the unrounded FP32 straight to h_out on the last step
       tc::mbar_wait(bar(BAR_CAND_DONE), it & 1);
       tc::fence_after_sync();
       if (tid == 0) GP_TRACE(11);
       const int64_t grow = (int64_t)tile * BM + r;
-#pragma unroll 1
+      uint32_t uv[2][16];
+      tc::tmem_ld16(t_lane + 256 + chalf * 64, av[0]);
+      tc::tmem_ld16(t_lane + 128 + chalf * 64, uv[0]);
+#pragma unroll
       for (int c16 = 0; c16 < 4; ++c16) {
         const int col0 = chalf * 64 + c16 * 16;
-        uint32_t ac[16], uu[16];
-        tc::tmem_ld16(t_lane + 256 + col0, ac);
-        tc::tmem_ld16(t_lane + 128 + col0, uu);
+        uint32_t (&ac)[16] = av[c16 & 1];
+        uint32_t (&uu)[16] = uv[c16 & 1];
         const float bcs = c16 < 2 ? bc0 : bc1;
         const int l0 = (c16 & 1) * 16;
         tc::tmem_ld_wait();
+        if (c16 < 3) {
+          tc::tmem_ld16(t_lane + 256 + col0 + 16, av[(c16 + 1) & 1]);
+          tc::tmem_ld16(t_lane + 128 + col0 + 16, uv[(c16 + 1) & 1]);
+        }
         float o0[8], o1[8];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -525,11 +596,10 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
       tc::fence_before_sync();                                // TMEM reads done
       tc::fence_proxy_async();                                // h' -> visible to the TMA unit
       __syncwarp();
-      if (lane == 0) {
-        tc::mbar_arrive_cta0(bar(BAR_TMEM_FREE));
-        tc::mbar_arrive(bar(BAR_H_STORE + hb));
-      }
+      if (lane == 0) tc::mbar_arrive(bar(BAR_H_STORE + hb));
       if (tid == 0) GP_TRACE(12);
+      if (live(tile + gridDim.x)) z_ready(it + 1, tile + gridDim.x);          // (nobody waits for a phase after the last pair)
+      if (tid == 0) GP_TRACE(19);
     }
   }
 
@@ -555,11 +625,31 @@ static_assert(sizeof(bias_tab) == 5 * HP * sizeof(float), "bias_tab layout");
 }  // namespace gp
 
 // =========================================================================================
-bool ggnn_gru_pair_enabled(const ggnn_ctx* ctx, int slot) {
-  const char* e = getenv("GGNN_GRU_PAIR");                   // opt-in while under development; read per call
-  if (!e || e[0] != '1') return false;
+// can a 2-CTA cluster of this kernel be resident at all (asked once per ctx; no: gru16::gru_f16_kernel serves the step)
+static bool pair_fits(ggnn_ctx* ctx) {
+  if (ctx->pair_fit < 0) {
+    ctx->pair_fit = 0;
+    if (cudaFuncSetAttribute(gp::gru_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gp::SMEM_BYTES) == cudaSuccess) {
+      ctx->attr_mask |= 1u << GGNN_ATTR_GRU_PAIR;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(2, 1, 1); cfg.blockDim = dim3(gp::NTHREADS, 1, 1); cfg.dynamicSmemBytes = gp::SMEM_BYTES;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, gp::gru_pair_kernel, &cfg) == cudaSuccess && n > 0) ctx->pair_fit = 1;
+    }
+    cudaGetLastError();                                      // a refusal is an answer, not an error of the call
+  }
+  return ctx->pair_fit == 1;
+}
+
+bool ggnn_gru_pair_enabled(ggnn_ctx* ctx, int slot) {
+  const char* e = getenv("GGNN_GRU_PAIR");                   // A-B switch, read per call (tests flip it): 0 = off
+  if (e && e[0] == '0') return false;
   return ggnn_f16_supported(ctx) && ctx->pair_ok && ctx->edge[slot].Wt_f16 && ctx->edge[slot].B_pad16 &&
-         ctx->two_e >= 2 && ctx->two_e % 2 == 0 && ctx->sm_count >= 2;
+         ctx->two_e >= 2 && ctx->two_e % 2 == 0 && ctx->sm_count >= 2 && pair_fits(ctx);
 }
 
 int ggnn_gru_pair_pack(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st) {
@@ -571,6 +661,7 @@ int ggnn_gru_pair_pack(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t st) 
     ctx->pair_ok = false;
     for (int s2 = 0; s2 < GGNN_MAX_SLOTS; ++s2) ctx->btab_ok[s2] = false;
     GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wc16q, ctx->Wct_f16, HP, 2 * HP, BKH, HP / 2));
+    GGNN_TRY(ggnn_make_tmap_2d_f16(ctx, &ctx->tm_Wg16q, ctx->Wgt_f16, 2 * HP, 2 * HP, BKH, HP / 2));
     ctx->pair_ok = true;
   }
   return GGNN_OK;
@@ -600,10 +691,10 @@ int ggnn_gru_pair_launch(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const v
   g.h_out = h_out;
   g.N = plan.N; g.h = ctx->h; g.n_tiles = (int)((plan.N + BM - 1) / BM);
   g.zp_row = e_prev * HP; g.zn_row = e_next * HP;
-  g.dbg = ctx->dbg_trace;
+  g.dbg = h_out ? nullptr : ctx->dbg_trace;               // trace a step that is not the last one (no FP32 output)
   const int n_pairs = (g.n_tiles + 1) / 2;
   const int clusters = n_pairs < ctx->sm_count / 2 ? n_pairs : ctx->sm_count / 2;
-  gru_pair_kernel<<<2 * clusters, NTHREADS, SMEM_BYTES, st>>>(g, tmH, ctx->tm_Wg16, ctx->tm_Wc16q, ew.tm_Wt16q);
+  gru_pair_kernel<<<2 * clusters, NTHREADS, SMEM_BYTES, st>>>(g, tmH, ctx->tm_Wg16q, ctx->tm_Wc16q, ew.tm_Wt16q);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }

@@ -217,12 +217,16 @@ def test_large_batch_properties(precision):
     assert O.normwise_err(small[:2].cpu().numpy(), ref) <= (1e-5 if precision == "fp32" else TOL)
 
 
-def test_word_order_channels_folded_into_the_gru_kernel(monkeypatch):
+@pytest.mark.parametrize("pair", ["1", "0"])
+def test_word_order_channels_folded_into_the_gru_kernel(monkeypatch, pair):
     """v = 128 graphs whose channels E-1 / 2E-1 are exactly t-1 -> t / t+1 -> t (what graph_to_adj_mat_bd builds for a
     127-word sentence, chem_tensorflow_dense.py:76-80) never send those messages through HBM: the GRU kernel forms them
     from the resident h tile.  Mixed batch: full-length trees (folded), shorter trees and a tree with one word-order
     edge removed / one extra edge on channel E-1 (not folded) -- all against the FP64 oracle, and against the
-    edge-list route, which gathers every message."""
+    edge-list route, which gathers every message.  Both GRU kernels: gru_pair_kernel (CTA pairs, resident weights, the
+    word-order messages as a second A operand from tensor memory; the default) and, behind GGNN_GRU_PAIR=0,
+    gru_f16_kernel (one CTA per tile, streamed weights, folded word-order weights)."""
+    monkeypatch.setenv("GGNN_GRU_PAIR", pair)
     b, v, E, h, T = 12, 128, 7, 128, 8
     lengths = torch.tensor([127, 127, 60, 127, 1, 127, 126, 127, 127, 100, 127, 127])
     tri = synth.random_trees(b, v - 1, E, seed=21, lengths=lengths)
