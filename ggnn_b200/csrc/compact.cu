@@ -186,7 +186,7 @@ constexpr int64_t Q_SLICE = 12288;   // work items (32-byte groups) per slice = 
 template <bool U8>
 __global__ void __maxnreg__(40)      // (not combinable with __launch_bounds__; always launched with P1_THREADS)
 bitmask_queue_kernel(const void* __restrict__ adj_v, int64_t n_items, uint32_t* __restrict__ bits,
-                     unsigned* __restrict__ ctl, int one_per_sm) {
+                     unsigned* __restrict__ ctl, int one_per_sm, int l2pf) {
   __shared__ unsigned s_next;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -210,6 +210,19 @@ bitmask_queue_kernel(const void* __restrict__ adj_v, int64_t n_items, uint32_t* 
     const int nthr = blockDim.x;                               // 256 or 384: Q_SLICE is a multiple of 4 * nthr
 #pragma unroll 1
     for (int off = 0; off < (int)Q_SLICE; off += nthr * P1_UNROLL) {
+      // One piece (nthr x 4 loads) AHEAD of the CTA's own loads, thread 0 pulls the next piece -- of this slice, then the
+      // first of the next one -- into L2 (no registers, no shared memory).  A CTA of this footprint holds only 32-48 KB in
+      // flight; with its loads hitting L2 that is enough for the full HBM rate (scripts/micro/bg_stream.cu: 384 threads
+      // 6.1 -> 6.9 TB/s, 256 threads 4.9 -> 6.1; farther ahead than one piece is erratic).
+      if (l2pf && threadIdx.x == 0) {
+        const int noff = off + nthr * P1_UNROLL;
+        const int64_t it0 = noff < (int)Q_SLICE ? (int64_t)cur * Q_SLICE + noff : (int64_t)nxt * Q_SLICE;
+        if (it0 < n_items) {
+          const int64_t left = n_items - it0;
+          const uint32_t bytes = (uint32_t)(left < nthr * P1_UNROLL ? left : nthr * P1_UNROLL) * 32u;
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(reinterpret_cast<const char*>(adj_v) + it0 * 32), "r"(bytes) : "memory");
+        }
+      }
       const int64_t i0 = g0 + off;
       f32x8 x[P1_UNROLL];
 #pragma unroll
@@ -408,10 +421,12 @@ int ggnn_bitmask_queue_launch(ggnn_ctx* ctx, const void* adj, int adj_dtype, int
   // background CTA: 12 warps x 32 x 40 registers = 3 warps per scheduler partition, what the 16-warp GRU kernel leaves free
   static const int bg_threads = getenv("GGNN_BMQ_THREADS") ? atoi(getenv("GGNN_BMQ_THREADS")) : 384;
   const int threads = background && (bg_threads == 256 || bg_threads == 384) ? bg_threads : P1_THREADS;
+  static const int l2pf_env = getenv("GGNN_BMQ_L2PF") ? atoi(getenv("GGNN_BMQ_L2PF")) : 1;    // A-B switch: 0 off, 1 background, 2 drain too
+  const int l2pf = background ? l2pf_env >= 1 : l2pf_env >= 2;
   if (adj_dtype == GGNN_ADJ_F32)
-    bitmask_queue_kernel<false><<<(unsigned)grid, threads, 0, st>>>(adj, n_items, bits, ctl, background ? 1 : 0);
+    bitmask_queue_kernel<false><<<(unsigned)grid, threads, 0, st>>>(adj, n_items, bits, ctl, background ? 1 : 0, l2pf);
   else
-    bitmask_queue_kernel<true><<<(unsigned)grid, threads, 0, st>>>(adj, n_items, bits, ctl, background ? 1 : 0);
+    bitmask_queue_kernel<true><<<(unsigned)grid, threads, 0, st>>>(adj, n_items, bits, ctl, background ? 1 : 0, l2pf);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
