@@ -235,7 +235,7 @@ def measure_c3(args, env):
     out = torch.empty_like(h0)
 
     chunks = [(c, min(pool, graphs_rank - c)) for c in range(0, graphs_rank, pool)]
-    prefetch = (not args.no_prefetch) and precision == "f16"
+    prefetch = (not args.no_prefetch) and precision in ("f16", "fp32")
 
     def step(last=False, pf=None):
         """One pass over this rank's graphs.  With prefetch, every call announces the next call's adjacency
@@ -354,9 +354,10 @@ def measure_c3(args, env):
     # the other arithmetic modes and the uint8 adjacency on the same workload, timed exactly like the headline
     # (same --steps / --warmup, same prefetch pipeline)
     def timed_variant(mode, adj_t, steps, warmup):
-        # the background pass is sized to sit next to the F16 kernels (16 warps x 96 registers); the TF32 / FP32
-        # kernels fill the register file, so a prefetch would only serialise behind them: not used there
-        prefetch = (not args.no_prefetch) and mode == "f16"
+        # the background pass is sized to sit next to the F16 kernels (16 warps x 96 registers) and, since round 2b, next
+        # to the strict mode's tensor-core kernels (strict_tc.cu: 9 warps capped at 128 registers, h <= 128); the TF32
+        # kernels (20 warps x 96) fill the register file, so a prefetch would only serialise behind them: not used there
+        prefetch = (not args.no_prefetch) and mode in ("f16", "fp32")
 
         def one(last):
             for i, (c, n) in enumerate(chunks):

@@ -74,7 +74,7 @@ __device__ __forceinline__ float stc_sigmoid(float x) { return tc::fast_sigmoid(
 __device__ __forceinline__ float stc_tanh(float x) { return tc::fast_tanh(x); }
 
 template <int MODE>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __maxnreg__(128)   // 3 warps x 32 x 128 registers in the fullest scheduler partition: a background bitmask-queue CTA (3 x 32 x 40) fits beside it
 split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, const __grid_constant__ CUtensorMap tmLo) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;

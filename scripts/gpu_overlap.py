@@ -5,6 +5,7 @@ import torch
 import ggnn_b200
 from ggnn_b200 import synth
 b = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+PREC = sys.argv[2] if len(sys.argv) > 2 else "f16"
 E, v, h, T = 46, 128, 128, 8
 prop = ggnn_b200.Propagator(ggnn_b200.from_dict(synth.make_weights(2 * E, h, 0)), "cuda:0")
 tri = synth.random_trees(b, v - 1, E, seed=1).cuda()
@@ -22,10 +23,10 @@ def timed(f, n=5):
     sync()
     return (time.perf_counter() - t0) / n * 1e3
 
-def plain(): prop.propagate_dense(h0, adj, num_timesteps=T, precision="f16", out=out)
+def plain(): prop.propagate_dense(h0, adj, num_timesteps=T, precision=PREC, out=out)
 def bg_only(): prop.prefetch_dense(adj); sync()
 def piped():
-    prop.propagate_dense(h0, adj, num_timesteps=T, precision="f16", out=out)
+    prop.propagate_dense(h0, adj, num_timesteps=T, precision=PREC, out=out)
     prop.prefetch_dense(adj)
 t_plain = timed(plain)
 t_bg = timed(bg_only)
