@@ -562,7 +562,7 @@ def measure_c2(args, env):
     ev = PE.ParserEvaluator(w, heads, dev, num_timesteps=Tc)
 
     def timed(precision, batch):
-        ev.evaluate(recs[:64], batch_size=batch, precision=precision)        # warm-up
+        ev.evaluate(recs, batch_size=batch, precision=precision)             # warm-up: the same pass (arenas grow to their final size)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         res, per = ev.evaluate(recs, batch_size=batch, precision=precision)
