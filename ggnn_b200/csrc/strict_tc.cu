@@ -66,7 +66,16 @@ struct params {
   int b_bytes;              // bytes one TMA box of the weight maps delivers per K chunk
   int dbg;                  // timing experiments (GGNN_STC_DBG): 1 = epilogue touches no global memory, 2 = no split math,
                             // 4 = one MMA per K step instead of three
+  unsigned long long* trace;// development aid (ggnn_debug_trace): %globaltimer of CTA 0's roles, MODE_GATES launches only
 };
+#define STC_TRACE(slot, idx)                                                                     \
+  do {                                                                                           \
+    if (MODE == MODE_GATES && p.trace && blockIdx.x == 0 && (idx) < 64) {                        \
+      unsigned long long t_;                                                                     \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                     \
+      p.trace[(slot) * 64 + (idx)] = t_;                                                         \
+    }                                                                                            \
+  } while (0)
 
 // gate math: ex2.approx / rcp.approx forms (~2e-7 relative).  Measured: accurate expf / tanhf change the end-to-end
 // error by < 2 % (it is set by the tensor core's accumulation, see the header) and cost 3 ms per 4 096-graph chunk.
@@ -166,32 +175,31 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
     };
     for (long long g = 0; g < RAW - 1; ++g) issue(g);
     int item = t_begin, kc = 0;
-    int b_row = 0;
     for (long long c = 0; c < total; ++c) {
+      if (tid == 0) STC_TRACE(0, c);
       issue(c + RAW - 1);
       asm volatile("cp.async.wait_group %0;" ::"n"(RAW - 1) : "memory");      // raw chunk c has landed (this thread's pieces)
-      if (kc == 0)
-        b_row = MODE == MODE_MSG ? __ldg(p.tile_type + item) * p.Np : (MODE == MODE_GATES ? (item & 1) * p.Np : 0);
+      if (tid == 0) STC_TRACE(1, c);
       const uint8_t* raw = smem + (sRaw - base) + (size_t)(c % RAW) * A_BYTES + raw_off;
       float4 x[RPT];
 #pragma unroll
       for (int j = 0; j < RPT; ++j) x[j] = *reinterpret_cast<const float4*>(raw + j * (RSTEP * 128));
       const int s = (int)(c % NST);
       if (c >= NST) tc::mbar_wait(bar(BAR_EMPTY + s), (uint32_t)((c / NST) - 1) & 1);
+      if (tid == 0) STC_TRACE(2, c);
       const uint32_t st0 = base + (uint32_t)s * st_bytes;
-      if (tid == 0) {                                 // weights: hi and lo boxes [Np rows x 32 k], swizzled by the TMA unit
-        tc::mbar_arrive_expect_tx(bar(BAR_FULL + s), 2u * (uint32_t)p.b_bytes);
-        tc::tma_load_2d(st0 + 2 * A_BYTES, &tmHi, kc * BKF, b_row, bar(BAR_FULL + s));
-        tc::tma_load_2d(st0 + 2 * A_BYTES + b_alloc, &tmLo, kc * BKF, b_row, bar(BAR_FULL + s));
-      }
+      // (the weight boxes of this stage are requested by the MMA thread, one chunk ahead: a producer thread that also
+      //  issued the two TMA loads made its whole warp -- and so every stage -- ~0.3 us late)
       uint8_t* a_hi = smem + (st0 - base);
 #pragma unroll
       for (int j = 0; j < RPT; ++j) {
         float4 hi, lo;
         if (p.dbg & 2) { hi = x[j]; lo = x[j]; } else {
-        hi.x = tc::to_tf32(x[j].x); hi.y = tc::to_tf32(x[j].y); hi.z = tc::to_tf32(x[j].z); hi.w = tc::to_tf32(x[j].w);
-        lo.x = tc::to_tf32(x[j].x - hi.x); lo.y = tc::to_tf32(x[j].y - hi.y);
-        lo.z = tc::to_tf32(x[j].z - hi.z); lo.w = tc::to_tf32(x[j].w - hi.w); }
+        // round-half-up in two integer ops (tc::to_tf32_fast) instead of cvt.rna (a conversion-unit instruction, 16 per
+        // clock per SM): x - hi is exact either way and lo only has to be SOME TF32 number within 2^-11 of it
+        hi.x = tc::to_tf32_fast(x[j].x); hi.y = tc::to_tf32_fast(x[j].y); hi.z = tc::to_tf32_fast(x[j].z); hi.w = tc::to_tf32_fast(x[j].w);
+        lo.x = tc::to_tf32_fast(x[j].x - hi.x); lo.y = tc::to_tf32_fast(x[j].y - hi.y);
+        lo.z = tc::to_tf32_fast(x[j].z - hi.z); lo.w = tc::to_tf32_fast(x[j].w - hi.w); }
         *reinterpret_cast<float4*>(a_hi + a_off[j]) = hi;
         *reinterpret_cast<float4*>(a_hi + A_BYTES + a_off[j]) = lo;
       }
@@ -199,11 +207,26 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
       tc::mbar_arrive(bar(BAR_FULL + s));
       if (++kc == KC) { kc = 0; ++item; }
     }
+    (void)item;
   } else if (warp == WARP_MMA) {
     // =============================== MMA issuer ===============================
     if (lane == 0) {
       const uint32_t idesc = tc::umma_idesc(/*TF32*/ 2, BM, p.Np);
       long long c = 0;
+      const long long total = (long long)(t_end - t_begin) * KC;
+      // weights of chunk cc = K chunk kcw of item itw: hi and lo boxes [Np rows x 32 k], swizzled by the TMA unit
+      int itw = t_begin, kcw = 0;
+      auto issue_w = [&](long long cc) {
+        const int s = (int)(cc % NST);
+        if (cc >= NST) tc::mbar_wait(bar(BAR_EMPTY + s), (uint32_t)((cc / NST) - 1) & 1);      // its last reader has retired
+        const int b_row = MODE == MODE_MSG ? __ldg(p.tile_type + itw) * p.Np : (MODE == MODE_GATES ? (itw & 1) * p.Np : 0);
+        const uint32_t st0 = base + (uint32_t)s * st_bytes;
+        tc::mbar_arrive_expect_tx(bar(BAR_FULL + s), 2u * (uint32_t)p.b_bytes);
+        tc::tma_load_2d(st0 + 2 * A_BYTES, &tmHi, kcw * BKF, b_row, bar(BAR_FULL + s));
+        tc::tma_load_2d(st0 + 2 * A_BYTES + b_alloc, &tmLo, kcw * BKF, b_row, bar(BAR_FULL + s));
+        if (++kcw == KC) { kcw = 0; ++itw; }
+      };
+      if (total > 0) issue_w(0);
       for (int tile = t_begin, i = 0; tile < t_end; ++tile, ++i) {
         const int buf = i & 1;
         if (i >= 2) tc::mbar_wait(bar(BAR_ACC_EMPTY + buf), (uint32_t)((i >> 1) - 1) & 1);
@@ -211,8 +234,10 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
         const uint32_t d = tmem_base + buf * 256, dx = d + 128;      // main | cross-term accumulator
         for (int kc = 0; kc < KC; ++kc, ++c) {
           const int s = (int)(c % NST);
+          if (c + 1 < total) issue_w(c + 1);
           tc::mbar_wait(bar(BAR_FULL + s), (uint32_t)(c / NST) & 1);
           tc::fence_after_sync();
+          STC_TRACE(3, c);
           const uint32_t a0 = base + (uint32_t)s * st_bytes, b0 = a0 + 2 * A_BYTES;
 #pragma unroll
           for (int k = 0; k < BKF / 8; ++k) {         // UMMA K = 8 for TF32 (32 bytes)
@@ -255,8 +280,10 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
       const float* bias = p.bias;
       if (MODE == MODE_MSG && bias) bias += (size_t)__ldg(p.tile_type + tile) * p.h;
       if (MODE == MODE_GATES) bias += half * p.hp;
+      if (etid == 0) STC_TRACE(4, i);
       tc::mbar_wait(bar(BAR_ACC_FULL + buf), (uint32_t)(i >> 1) & 1);
       tc::fence_after_sync();
+      if (etid == 0) STC_TRACE(5, i);
       const int ngroups = p.Np / 32;
       for (int cc = 0; cc < ngroups; ++cc, ++grp) {
         uint32_t acc[32], accx[32];
@@ -347,6 +374,7 @@ int launch(ggnn_ctx* ctx, const params& p, const CUtensorMap& hi, const CUtensor
   static const int dbg = getenv("GGNN_STC_DBG") ? atoi(getenv("GGNN_STC_DBG")) : 0;
   params pd = p;
   pd.dbg = dbg;
+  pd.trace = ctx->dbg_trace;
   split_gemm_kernel<MODE><<<grid, NTHREADS, SMEM_BYTES, st>>>(pd, hi, lo);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
