@@ -290,32 +290,56 @@ def measure_c3(args, env):
     ne = min(args.e2e_graphs, pool)
     h0_host = h0[:ne].cpu().pin_memory()
     adj_host = adj[:ne].cpu().pin_memory()
-    res = None
-    for _ in range(max(3, args.warmup)):   # results are held like in the timed loop, so the pinned-host allocator
-        res = ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,   # caches both blocks
-                                                           num_timesteps=T, precision=precision)
-    barrier()
-    t0 = time.perf_counter()
-    per_call = []
-    for _ in range(args.steps):
-        tc0 = time.perf_counter()
-        res = ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,
-                                                           num_timesteps=T, precision=precision)
-        per_call.append(time.perf_counter() - tc0)     # the call returns host data: it has synchronised
-    torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / args.steps
-    if os.environ.get("GGNN_BENCH_DEBUG"):
-        print("e2e per call ms:", [round(x * 1e3, 2) for x in per_call], file=sys.stderr)
-    if world > 1:
-        te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e_s = float(te.item())
+    from ggnn_b200 import api as _api
+
+    def time_e2e(host_pack):
+        """The public drop-in on HOST tensors, copies inside the timed region.  host_pack: the dense adjacency is reduced
+        to its bitmask on the host cores before it crosses the bus (the default for host inputs, api.py); False: the FP32
+        tensor itself travels (round 1 / 2a behaviour, GGNN_HOST_PACK=0)."""
+        saved = _api._HOST_PACK
+        _api._HOST_PACK = host_pack
+        try:
+            r = None
+            for _ in range(max(3, args.warmup)):   # results are held like in the timed loop, so the pinned-host allocator
+                r = ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,   # caches both blocks
+                                                                 num_timesteps=T, precision=precision)
+            barrier()
+            t0 = time.perf_counter()
+            per_call = []
+            for _ in range(args.steps):
+                tc0 = time.perf_counter()
+                r = ggnn_b200.compute_final_node_representations(h0_host, adj_host, weights=prop,
+                                                                 num_timesteps=T, precision=precision)
+                per_call.append(time.perf_counter() - tc0)     # the call returns host data: it has synchronised
+            torch.cuda.synchronize()
+            sec = (time.perf_counter() - t0) / args.steps
+        finally:
+            _api._HOST_PACK = saved
+        if os.environ.get("GGNN_BENCH_DEBUG"):
+            print("e2e per call ms:", [round(x * 1e3, 2) for x in per_call], file=sys.stderr)
+        return max_over_ranks(sec, dev, world), r
+
+    pack_threads = max(1, (os.cpu_count() or 2) // world - 1)  # the ranks of one box share its host cores; one is left to the caller
+    _api._HOST_PACK_THREADS = pack_threads
+    packed = _api._HOST_PACK and _api._bits_route_ok(2 * E, V)
+    e2e_s, res = time_e2e(packed)
     assert res.shape == h0_host.shape
+    adj_bus_bytes = adj_host.numel() // 8 if packed else adj_host.numel() * 4
     e2e = {"value": ne * world / e2e_s, "unit": "graphs/s",
-           "h2d_bytes_per_step": int(adj_host.numel() * 4 + h0_host.numel() * 4),
+           "h2d_bytes_per_step": int(adj_bus_bytes + h0_host.numel() * 4),
            "d2h_bytes_per_step": int(res.numel() * 4), "graphs_per_step": ne * world,
-           "note": "ggnn_b200.compute_final_node_representations on pinned host tensors: dense "
-                   "FP32 adjacency (6.03 MB/graph, the reference's feed format) + states H2D, result D2H"}
+           "host_bytes_read_per_step": int(adj_host.numel() * 4 + h0_host.numel() * 4),
+           "note": ("ggnn_b200.compute_final_node_representations on pinned host tensors holding the dense FP32 adjacency "
+                    "(6.03 MB/graph, the reference's feed format) and the states; the adjacency is reduced to its bitmask "
+                    "(1 bit per element, the path's own first intermediate) by ggnn_host_pack_adjacency on the host cores, "
+                    "and the bitmask + states go H2D, the result D2H" if packed else
+                    "ggnn_b200.compute_final_node_representations on pinned host tensors: dense "
+                    "FP32 adjacency (6.03 MB/graph, the reference's feed format) + states H2D, result D2H"),
+           "host_pack": bool(packed), "host_pack_threads": (pack_threads if packed else 0)}
+    if packed:      # the same call with the FP32 tensor itself on the bus (what rounds 1 / 2a measured)
+        dense_s, _ = time_e2e(False)
+        e2e["dense_over_the_bus"] = {"value": ne * world / dense_s, "unit": "graphs/s",
+                                     "h2d_bytes_per_step": int(adj_host.numel() * 4 + h0_host.numel() * 4)}
 
     # context for the e2e figure: what a bare pinned-host -> device copy of the same adjacency reaches on this box
     d_tmp = torch.empty_like(adj_host, device=dev)
@@ -329,6 +353,7 @@ def measure_c3(args, env):
     torch.cuda.synchronize()
     e2e["h2d_copy_peak_gbps"] = 3 * adj_host.numel() * 4 / (c0.elapsed_time(c1) * 1e-3) / 1e9
     e2e["achieved_bus_gbps"] = (e2e["h2d_bytes_per_step"] + e2e["d2h_bytes_per_step"]) / e2e_s / 1e9
+    e2e["host_read_gbps"] = e2e["host_bytes_read_per_step"] / e2e_s / 1e9
     del d_tmp
 
     # same graphs handed over as (src, channel, dst) triples: no dense adjacency on the bus

@@ -33,6 +33,8 @@ SIGNATURES = {
     "ggnn_compact_adjacency_static": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _i64, _vp, _vp]),
     "ggnn_propagate_dense": (_i, [_vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _u, _vp, _vp]),
     "ggnn_dense_prefetch": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "ggnn_host_pack_adjacency": (_i, [_vp, _i, _i64, _vp, _i]),
+    "ggnn_propagate_dense_bits": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _i, _u, _vp, _vp]),
     "ggnn_propagate_csr": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _u, _vp, _vp]),
     "ggnn_propagate_edges": (_i, [_vp, _i, _vp, _vp, _i64, _i64, _i, _i, _u, _vp, _vp]),
     "ggnn_grad_floats": (_i64, [_vp]),

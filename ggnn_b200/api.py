@@ -6,12 +6,15 @@
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
 import threading
 from typing import Optional, Union
 
 import numpy as np
 import torch
 
+from . import _lib
 from .engine import Propagator
 from .weights import GGNNWeights, as_weights
 
@@ -133,6 +136,127 @@ def _propagate_dense_from_host(prop: Propagator, h0, adj, num_timesteps, fixed_t
     return out_host
 
 
+_HOST_PACK = os.environ.get("GGNN_HOST_PACK", "1") != "0"      # A-B switch: 0 = ship the dense tensor over the bus
+_HOST_PACK_CHUNK_BYTES = 768 << 20                          # 128 C3 graphs: few calls; the sweep is in scripts/gpu_e2e_pack.py
+# packer threads: all host cores but one (the calling thread drives the GPU and spins in its planning sync)
+_HOST_PACK_THREADS = int(os.environ.get("GGNN_HOST_PACK_THREADS", "0")) or max(1, (os.cpu_count() or 2) - 1)
+
+
+_packer_pool = None
+
+
+def _packer():
+    """One background thread that calls the (multi-threaded, GIL-free) host packer ahead of the GPU calls."""
+    global _packer_pool
+    if _packer_pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _packer_pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="ggnn-pack")
+    return _packer_pool
+
+
+def _bits_route_ok(two_e: int, v: int) -> bool:
+    """Shapes the bitmask -> plan route of the library serves (ggnn_plan_bits_supported, plan_bits.cu)."""
+    vt = (v + 31) // 32 * 32
+    return 1 <= v <= 255 and two_e <= 256 and two_e * vt * 2 <= 48 * 1024 and (vt // 32) * two_e * 4 <= 48 * 1024
+
+
+def _propagate_dense_from_host_packed(prop: Propagator, h0, adj, num_timesteps, fixed_ts, precision):
+    """Host-resident inputs, packed: the path uses one bit per adjacency element (A != 0), so the dense tensor is
+    reduced to its bitmask ON THE HOST CORES (ggnn_host_pack_adjacency: threads + AVX, 29 k C3 graphs/s on the 16
+    cores of the GPU box against 9 k graphs/s for the FP32 tensor over PCIe) and 1/32 of the bytes cross the bus.
+    Chunks of ~768 MB of adjacency, packed by a background thread up to two chunks ahead: packing of chunk k+1 overlaps the GPU's work on chunk k (row counts, plan,
+    messages, GRU steps -- ggnn_propagate_dense_bits) and the D2H of chunk k-1.  The bitmask is the same
+    intermediate the GPU's own first pass produces for device-resident inputs (tests/test_gpu_hostpack.py).
+    Works on pageable memory as it is (no pinned staging copy).  Returns a pinned CPU tensor."""
+    import time as _t0m
+    t_enter = _t0m.perf_counter()
+    dev = prop.device
+    lib = _lib.lib()
+    b, v, h = h0.shape
+    per_graph_elems = adj[0].numel()
+    words_pg = per_graph_elems // 32                              # _bits_route_ok shapes only; checked by the caller
+    cg = int(max(1, min(b, _HOST_PACK_CHUNK_BYTES // max(per_graph_elems * adj.element_size(), 1))))
+    dt = _lib.ADJ_F32 if adj.dtype == torch.float32 else _lib.ADJ_U8
+    key = (threading.get_ident(), dev.index)
+    if key not in _streams:
+        _streams[key] = tuple(torch.cuda.Stream(dev) for _ in range(3))
+    s_in, s_run, s_out = _streams[key]
+    cur = torch.cuda.current_stream(dev)
+    h_bits = [torch.empty(cg * words_pg, dtype=torch.int32, pin_memory=True) for _ in range(2)]
+    d_bits = [torch.empty(cg * words_pg, dtype=torch.int32, device=dev) for _ in range(2)]
+    d_h = torch.empty((b, v, h), dtype=torch.float32, device=dev)
+    out_host = torch.empty((b, v, h), dtype=torch.float32, pin_memory=True)
+    h0p = h0 if h0.is_pinned() else None
+    copied = [torch.cuda.Event() for _ in range(2)]
+    done = [torch.cuda.Event() for _ in range(2)]
+    for st in (s_in, s_run, s_out):
+        st.wait_stream(cur)
+    nchunks = (b + cg - 1) // cg
+    esz = adj.element_size()
+
+    dbg = os.environ.get("GGNN_HOST_PACK_DEBUG")      # development aid: where a call's time goes
+    import time as _t
+    tl = {"pack": 0.0, "wait_pack": 0.0, "propagate": 0.0, "t0": _t.perf_counter()}
+
+    def pack(k):                                      # runs on the packer thread (ctypes releases the GIL)
+        slot, lo, hi = k & 1, k * cg, min(b, (k + 1) * cg)
+        if k >= 2:
+            copied[slot].synchronize()                # the DMA out of this pinned bitmask buffer has finished
+        t0 = _t.perf_counter()
+        try:
+            return _pack_call(k, slot, lo, hi)
+        finally:
+            tl["pack"] += _t.perf_counter() - t0
+
+    def _pack_call(k, slot, lo, hi):
+        rc = lib.ggnn_host_pack_adjacency(C.c_void_p(adj.data_ptr() + lo * per_graph_elems * esz), dt,
+                                          (hi - lo) * per_graph_elems, C.c_void_p(h_bits[slot].data_ptr()),
+                                          _HOST_PACK_THREADS)
+        if rc != _lib.OK:
+            raise RuntimeError(f"ggnn_host_pack_adjacency failed ({rc})")
+
+    def copy_in(k):
+        slot, lo, hi = k & 1, k * cg, min(b, (k + 1) * cg)
+        with torch.cuda.stream(s_in):
+            if k >= 2:
+                s_in.wait_event(done[slot])           # chunk k-2 no longer reads this device buffer
+            d_bits[slot][:(hi - lo) * words_pg].copy_(h_bits[slot][:(hi - lo) * words_pg], non_blocking=True)
+            d_h[lo:hi].copy_((h0p if h0p is not None else h0)[lo:hi], non_blocking=True)
+            copied[slot].record(s_in)
+
+    # the packer runs up to two chunks ahead of the GPU calls (whose planning step waits for the device)
+    packer = _packer()
+    futs = {k: packer.submit(pack, k) for k in range(min(2, nchunks))}
+    for k in range(nchunks):
+        slot, lo, hi = k & 1, k * cg, min(b, (k + 1) * cg)
+        t0 = _t.perf_counter()
+        futs.pop(k).result()
+        tl["wait_pack"] += _t.perf_counter() - t0
+        copy_in(k)
+        if k + 2 < nchunks:
+            futs[k + 2] = packer.submit(pack, k + 2)  # (waits for this chunk's DMA out of the buffer it reuses)
+        t0 = _t.perf_counter()
+        with torch.cuda.stream(s_run):
+            s_run.wait_event(copied[slot])
+            prop.propagate_dense_bits(d_h[lo:hi], d_bits[slot], num_timesteps=num_timesteps, fixed_ts=fixed_ts,
+                                      precision=precision, out=d_h[lo:hi])
+            done[slot].record(s_run)
+        tl["propagate"] += _t.perf_counter() - t0
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(done[slot])
+            out_host[lo:hi].copy_(d_h[lo:hi], non_blocking=True)
+    t0 = _t.perf_counter()
+    s_out.synchronize()
+    if dbg:
+        import sys
+        print(f"host-pack call: {nchunks} chunks of {cg} graphs; setup {(tl['t0'] - t_enter) * 1e3:.2f} ms, pack {tl['pack'] * 1e3:.2f} ms "
+              f"(packer thread), waiting for the packer {tl['wait_pack'] * 1e3:.2f} ms, propagate calls {tl['propagate'] * 1e3:.2f} ms, "
+              f"final sync {(_t.perf_counter() - t0) * 1e3:.2f} ms, total {(_t.perf_counter() - t_enter) * 1e3:.2f} ms", file=sys.stderr)
+    for t in d_bits + [d_h]:                           # the caching allocator must not hand these out too early
+        t.record_stream(s_in); t.record_stream(s_run); t.record_stream(s_out)
+    return out_host
+
+
 def _device_of(*xs):
     for x in xs:
         if isinstance(x, torch.Tensor) and x.device.type == "cuda":
@@ -199,7 +323,10 @@ def compute_final_node_representations(initial_node_representations, adjacency_m
             raise ValueError(f"states {tuple(h0.shape)} {h0.dtype} / adjacency {tuple(adj.shape)} {adj.dtype} do not "
                              f"match [b, v, {prop.weights.hidden_size}] float32 / [b, {prop.weights.two_e}, v, v]")
         if h0.shape[0] > 0:
-            out = _propagate_dense_from_host(prop, h0, adj, num_timesteps, fixed_ts, precision)
+            if _HOST_PACK and _bits_route_ok(prop.weights.two_e, h0.shape[1]) and adj[0].numel() % 32 == 0:
+                out = _propagate_dense_from_host_packed(prop, h0, adj, num_timesteps, fixed_ts, precision)
+            else:
+                out = _propagate_dense_from_host(prop, h0, adj, num_timesteps, fixed_ts, precision)
             return out.numpy() if kind == "numpy" else out
     h0, kind = _to_device(initial_node_representations, dev, np.float32, "initial_node_representations")
     adj, _ = _to_device(adjacency_matrix, dev, None, "adjacency_matrix")

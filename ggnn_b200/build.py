@@ -6,10 +6,10 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libggnn_b200.so")
-SOURCES = ["api.cu", "compact.cu", "scan.cu", "plan.cu", "plan_edges.cu", "step_fp32.cu", "tf32.cu", "gru_fused.cu", "msg_tc.cu", "train_fp32.cu", "train_tf32.cu", "heads.cu", "f16.cu", "wide16.cu", "plan_bits.cu", "strict_tc.cu", "gru_pair.cu"]
+SOURCES = ["api.cu", "compact.cu", "scan.cu", "plan.cu", "plan_edges.cu", "step_fp32.cu", "tf32.cu", "gru_fused.cu", "msg_tc.cu", "train_fp32.cu", "train_tf32.cu", "heads.cu", "f16.cu", "wide16.cu", "plan_bits.cu", "strict_tc.cu", "gru_pair.cu", "host_pack.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "-lcuda",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-pthread", "-shared", "-lcuda",
 ]
 
 

@@ -485,13 +485,14 @@ size_t csr_chunk_bytes(ggnn_ctx* ctx, int64_t bc, int v, int64_t nnz, size_t ext
 
 }  // namespace
 
-extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, const void* adj,
-                                    int adj_dtype, const float* mask_or_null, int b, int v, int T,
-                                    int precision, unsigned flags, float* h_out, void* stream) {
-  (void)mask_or_null;
+// bits_in != null: the adjacency arrives as its bitmask (device memory; word w, bit i <=> element 32 w + i of the dense
+// [b, 2E, v, v] tensor is non-zero) and `adj` is not read -- ggnn_propagate_dense_bits
+static int propagate_dense_impl(ggnn_ctx* ctx, int slot, const float* h0, const void* adj, int adj_dtype,
+                                const uint32_t* bits_in, int b, int v, int T, int precision, unsigned flags,
+                                float* h_out, void* stream) {
   if (!ctx) return GGNN_E_ARG;
   if (b < 0 || v <= 0 || T < 0) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: bad sizes b=%d v=%d T=%d", b, v, T);
-  if (b > 0 && (!h0 || !adj || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: null pointer");
+  if (b > 0 && (!h0 || (!adj && !bits_in) || !h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: null pointer");
   if (misaligned16(h0) || misaligned16(h_out)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: state pointers must be 16-byte aligned");
   if (adj_dtype != GGNN_ADJ_F32 && adj_dtype != GGNN_ADJ_U8) GGNN_FAIL(ctx, GGNN_E_ARG, "bad adj_dtype %d", adj_dtype);
   GGNN_TRY(check_ready(ctx, slot, precision));
@@ -509,10 +510,16 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
   const int64_t rows_per_graph = (int64_t)two_e * v;
   int64_t chunk = dense_chunk(two_e, v);
   if (chunk > b) chunk = b;
+  if (bits_in) {
+    if (!ggnn_plan_bits_supported(two_e, v) || ctx->no_bits_plan)
+      GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "propagate_dense_bits: the bitmask route does not serve 2E=%d, v=%d", two_e, v);
+    if (chunk < b && (chunk * rows_per_graph * v) % 32 != 0)
+      GGNN_FAIL(ctx, GGNN_E_UNSUPPORTED, "propagate_dense_bits: %d graphs need chunks that do not start on a bitmask word; split the batch", b);
+  }
   // a prefetched adjacency (ggnn_dense_prefetch) is consumed by the call it was announced for, and only by that one
   ctx_ext* ex = ext_of(ctx);
   const prefetch_rec pf = ex->pf;
-  const bool use_pf = pf.active && pf.adj == adj && pf.dtype == adj_dtype && pf.b == b && pf.v == v &&
+  const bool use_pf = !bits_in && pf.active && pf.adj == adj && pf.dtype == adj_dtype && pf.b == b && pf.v == v &&
                       pf.two_e == two_e && chunk == b && ggnn_plan_bits_supported(two_e, v) && !ctx->no_bits_plan;
   if (pf.active && !use_pf) prefetch_cancel(ctx);
   ex->pf.active = false;
@@ -535,7 +542,9 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
       ggnn_plan_bits_take_pre(a0, bc, two_e, v, &pre);
       if (precision == GGNN_PREC_F16)
         GGNN_TRY(f16_prologue(ctx, slot, f16_direct ? h0 + (size_t)g0 * v * h : h_chunk, bc * v, st));
-      if (use_pf) {
+      if (bits_in) {
+        pre.bits = const_cast<uint32_t*>(bits_in) + (size_t)g0 * rows_per_graph * v / 32;     // read only from here on
+      } else if (use_pf) {
         // the background pass has been streaming this adjacency since the prefetch call: take the slices that are
         // left at full occupancy, then wait for the background CTAs' last slices
         char* pb = ex->ar[7 + pf.buf].p;
@@ -594,6 +603,21 @@ extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, co
                                  T, precision, flags, col_bytes, st));
   }
   return GGNN_OK;
+}
+
+extern "C" int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0, const void* adj,
+                                    int adj_dtype, const float* mask_or_null, int b, int v, int T,
+                                    int precision, unsigned flags, float* h_out, void* stream) {
+  (void)mask_or_null;
+  if (ctx && b > 0 && !adj) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense: null pointer");
+  return propagate_dense_impl(ctx, slot, h0, adj, adj_dtype, nullptr, b, v, T, precision, flags, h_out, stream);
+}
+
+extern "C" int ggnn_propagate_dense_bits(ggnn_ctx* ctx, int slot, const float* h0, const uint32_t* bits, int b, int v,
+                                         int T, int precision, unsigned flags, float* h_out, void* stream) {
+  if (ctx && b > 0 && !bits) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense_bits: null pointer");
+  if (ctx && (reinterpret_cast<uintptr_t>(bits) & 15u)) GGNN_FAIL(ctx, GGNN_E_ARG, "propagate_dense_bits: the bitmask must be 16-byte aligned");
+  return propagate_dense_impl(ctx, slot, h0, nullptr, GGNN_ADJ_F32, bits, b, v, T, precision, flags, h_out, stream);
 }
 
 // Announce the adjacency of the NEXT ggnn_propagate_dense call: its bitmask pass starts now, on the ctx's own side

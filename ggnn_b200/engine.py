@@ -203,6 +203,27 @@ class Propagator:
         self._check(rc, "ggnn_propagate_dense")
         return out
 
+    def propagate_dense_bits(self, h0: torch.Tensor, bits: torch.Tensor, num_timesteps=None, fixed_ts=None,
+                             precision: str = "fp32", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``propagate_dense`` with the adjacency given as its bitmask (int32 device tensor of ceil(b*2E*v*v / 32)
+        words as ``pack_adjacency_host`` builds it on the host cores): what a host-resident dense adjacency is
+        reduced to before it crosses the bus (include/ggnn_b200.h, ggnn_propagate_dense_bits)."""
+        if precision not in _PREC:
+            raise ValueError(f"precision must be one of {sorted(_PREC)}, got {precision!r}")
+        h0 = self._state(h0, 3)
+        b, v, h = h0.shape
+        words = (b * self.weights.two_e * v * v + 31) // 32
+        if bits.dtype != torch.int32 or bits.device != self.device or bits.numel() < words or not bits.is_contiguous():
+            raise ValueError(f"bits must be a contiguous int32 tensor of >= {words} words on {self.device}")
+        slot, T = self._slot_T(num_timesteps, fixed_ts)
+        if out is None:
+            out = torch.empty_like(h0)
+        with torch.cuda.device(self.device):
+            rc = self._l.ggnn_propagate_dense_bits(self._ctx, slot, _ptr(h0), _ptr(bits), b, v, T, _PREC[precision],
+                                                   _flags(False), _ptr(out), _stream_ptr(self.device))
+        self._check(rc, "ggnn_propagate_dense_bits")
+        return out
+
     def prefetch_dense(self, adj: torch.Tensor, ready_event: Optional[torch.cuda.Event] = None):
         """Announce the adjacency of the NEXT ``propagate_dense`` call: its dense -> bitmask pass starts now in the
         background of the work already queued (the reference's ThreadedIterator prepares the next batch the same

@@ -154,6 +154,24 @@ int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0,
  *     accepted and simply not prefetched.  No synchronisation unless an announcement is dropped. */
 int ggnn_dense_prefetch(ggnn_ctx* ctx, const void* adj, int adj_dtype, int b, int v, void* ready_event_or_null);
 
+/* Host-resident dense adjacency (the reference feeds it from host memory every step: feed_dict,
+ * chem_tensorflow.py:262-268, built by chem_tensorflow_dense.py:566-602).  The path uses ONE BIT per element (A != 0),
+ * and over PCIe the FP32 tensor caps the call at ~9 k C3 graphs/s whatever the GPU does, so for HOST inputs the bit is
+ * formed where the data is and 1/32 of the bytes travel:
+ *   ggnn_host_pack_adjacency   host function, no ctx, no CUDA: bits_host[w] bit i = (element 32 w + i != 0) over the
+ *                              flat tensor (n_elems = b*2E*v*v; the last word zero padded) -- exactly the
+ *                              intermediate the GPU's own first pass produces for device-resident inputs
+ *                              (tests/test_gpu_hostpack.py: bit for bit).  threads <= 0: all host cores.
+ *   ggnn_propagate_dense_bits  ggnn_propagate_dense with that bitmask (DEVICE memory, 16-byte aligned) in place of
+ *                              the dense tensor: row counts, plan, messages and GRU steps on the GPU as usual; same
+ *                              results bit for bit.  GGNN_E_UNSUPPORTED where the bitmask route does not apply
+ *                              (v > 255, 2E > 256): use ggnn_propagate_dense.
+ * Device-resident adjacency keeps the GPU bitmask pass (ggnn_propagate_dense, ggnn_dense_prefetch). */
+int ggnn_host_pack_adjacency(const void* adj_host, int adj_dtype, int64_t n_elems, uint32_t* bits_host, int threads);
+int ggnn_propagate_dense_bits(ggnn_ctx* ctx, int slot, const float* h0, const uint32_t* bits,
+                              int b, int v, int T, int precision, unsigned flags,
+                              float* h_out, void* stream);
+
 int ggnn_propagate_csr(ggnn_ctx* ctx, int slot, const float* h0,
                        const int32_t* rowptr, const int32_t* col,
                        int b, int v, int T, int precision, unsigned flags,

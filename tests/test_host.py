@@ -133,3 +133,23 @@ def test_synth_matches_reference_rules():
     de = O.dense_to_edges(adj)
     assert sorted(map(tuple, el)) == sorted(map(tuple, de))
     assert synth.bucket_size(5) == 6 and synth.bucket_size(4) == 6 and synth.bucket_size(3) == 4
+
+
+def test_host_adjacency_packer_is_bit_exact():
+    """ggnn_host_pack_adjacency is a host function (no GPU): word w, bit i <=> element 32 w + i != 0, for FP32 (with
+    -0.0, NaN and a denormal-range value) and uint8 inputs, any thread count, with a partial last word."""
+    import ctypes as C
+    from ggnn_b200 import _lib
+    l = _lib.lib()
+    rng = np.random.default_rng(0)
+    n = 3 * 10 * 33 * 33 + 5
+    a = (rng.random(n) < 0.03).astype(np.float32)
+    a[3], a[5], a[9] = -0.0, np.nan, 1e-38
+    ref = np.packbits(np.pad(a != 0, (0, (-n) % 32)).astype(np.uint8), bitorder="little").view(np.uint32)
+    for arr, code in ((a, _lib.ADJ_F32), ((a != 0).astype(np.uint8), _lib.ADJ_U8)):
+        for threads in (1, 2, 0):
+            bits = np.full((n + 31) // 32, 0xFFFFFFFF, dtype=np.uint32)
+            assert l.ggnn_host_pack_adjacency(C.c_void_p(arr.ctypes.data), code, n, C.c_void_p(bits.ctypes.data), threads) == _lib.OK
+            assert np.array_equal(bits, ref)
+    assert l.ggnn_host_pack_adjacency(None, _lib.ADJ_F32, 64, None, 0) == _lib.E_ARG
+    assert l.ggnn_host_pack_adjacency(C.c_void_p(a.ctypes.data), 7, 64, C.c_void_p(ref.ctypes.data), 0) == _lib.E_ARG
