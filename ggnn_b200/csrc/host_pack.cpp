@@ -12,6 +12,7 @@
 // Plain C++ (std::thread), AVX2 / AVX-512 picked at run time; no CUDA in this file.
 #include <stdint.h>
 #include <string.h>
+#include <atomic>
 #include <thread>
 #include <vector>
 #include <immintrin.h>
@@ -92,10 +93,18 @@ extern "C" int ggnn_host_pack_adjacency(const void* adj_host, int adj_dtype, int
   const int64_t min_words = 1 << 14;                       // 2 MB of FP32 per thread at least
   if ((int64_t)threads > (words + min_words - 1) / min_words) threads = (int)((words + min_words - 1) / min_words);
   if (threads < 1) threads = 1;
-  auto work = [&](int t) {
-    const int64_t w0 = words * t / threads, w1 = words * (t + 1) / threads;
-    if (adj_dtype == GGNN_ADJ_F32) pack_range(reinterpret_cast<const float*>(adj_host) + w0 * 32, w1 - w0, bits_host + w0);
-    else pack_range(reinterpret_cast<const uint8_t*>(adj_host) + w0 * 32, w1 - w0, bits_host + w0);
+  // blocks of 64 K words (8 MB of FP32) handed out by a counter: a core that is busy with something else (the caller's
+  // own thread, another rank) delays one block, not a fixed 1/threads share of the tensor
+  const int64_t blk = 1 << 16;
+  std::atomic<int64_t> next(0);
+  auto work = [&](int) {
+    for (;;) {
+      const int64_t w0 = next.fetch_add(blk, std::memory_order_relaxed);
+      if (w0 >= words) break;
+      const int64_t w1 = w0 + blk < words ? w0 + blk : words;
+      if (adj_dtype == GGNN_ADJ_F32) pack_range(reinterpret_cast<const float*>(adj_host) + w0 * 32, w1 - w0, bits_host + w0);
+      else pack_range(reinterpret_cast<const uint8_t*>(adj_host) + w0 * 32, w1 - w0, bits_host + w0);
+    }
   };
   if (threads == 1) {
     work(0);
