@@ -257,6 +257,125 @@ def _propagate_dense_from_host_packed(prop: Propagator, h0, adj, num_timesteps, 
     return out_host
 
 
+# opt-in (GGNN_HOST_HYBRID=1): measured 23.5-25.8 k graphs/s against 22.7-23.6 k for the packer alone (scripts/gpu_e2e_pack.py) --
+# the copy engine and the packer read the same host memory, which is the limit either way
+_HOST_HYBRID = os.environ.get("GGNN_HOST_HYBRID", "0") == "1"
+_HYBRID_PACK_GRAPH_BYTES = 384 << 20       # a packed unit: ~64 C3 graphs (about 2.7 ms of the packer)
+_HYBRID_DENSE_GRAPH_BYTES = 96 << 20       # a dense unit: ~16 C3 graphs (about 1.8 ms of the bus)
+
+
+def _propagate_dense_from_host_hybrid(prop: Propagator, h0, adj, num_timesteps, fixed_ts, precision):
+    """Host-resident PINNED inputs: the host packer (memory-bound on the host cores) and the copy engine (bound by the
+    bus) are two independent ways of getting adjacency to the GPU, so both are used at once.  The batch is cut into
+    units that alternate between the two routes -- packed units (bitmask built on the host, ggnn_propagate_dense_bits)
+    and dense units (the FP32 tensor over the bus, ggnn_propagate_dense: the GPU builds the bitmask) -- each route
+    works through its own units in order, two ahead of the GPU calls, which consume the units in batch order.
+    Results are the same bits whichever route a graph takes (tests/test_gpu_hostpack.py)."""
+    dev = prop.device
+    lib = _lib.lib()
+    b, v, h = h0.shape
+    per_graph_elems = adj[0].numel()
+    esz = adj.element_size()
+    per_graph = per_graph_elems * esz
+    words_pg = per_graph_elems // 32
+    gp = int(max(1, _HYBRID_PACK_GRAPH_BYTES // per_graph))
+    gd = int(max(1, _HYBRID_DENSE_GRAPH_BYTES // per_graph))
+    dt = _lib.ADJ_F32 if adj.dtype == torch.float32 else _lib.ADJ_U8
+    units = []                                            # (route, lo, hi); the packer's first unit is ready last: dense first
+    lo, k = 0, 0
+    while lo < b:
+        route = "D" if k % 2 == 0 else "P"
+        hi = min(b, lo + (gd if route == "D" else gp))
+        units.append((route, lo, hi))
+        lo, k = hi, k + 1
+    key = (threading.get_ident(), dev.index)
+    if key not in _streams:
+        _streams[key] = tuple(torch.cuda.Stream(dev) for _ in range(3))
+    s_in, s_run, s_out = _streams[key]
+    cur = torch.cuda.current_stream(dev)
+    DEPTH = 2
+    h_bits = [torch.empty(gp * words_pg, dtype=torch.int32, pin_memory=True) for _ in range(DEPTH)]
+    d_bits = [torch.empty(gp * words_pg, dtype=torch.int32, device=dev) for _ in range(DEPTH)]
+    d_adj = [torch.empty((gd,) + tuple(adj.shape[1:]), dtype=adj.dtype, device=dev) for _ in range(DEPTH)]
+    d_h = torch.empty((b, v, h), dtype=torch.float32, device=dev)
+    out_host = torch.empty((b, v, h), dtype=torch.float32, pin_memory=True)
+    for st in (s_in, s_run, s_out):
+        st.wait_stream(cur)
+    p_units = [i for i, u in enumerate(units) if u[0] == "P"]
+    d_units = [i for i, u in enumerate(units) if u[0] == "D"]
+    p_ord = {i: n for n, i in enumerate(p_units)}         # unit index -> its number on its route (ring slot = n % DEPTH)
+    d_ord = {i: n for n, i in enumerate(d_units)}
+    bits_copied = [torch.cuda.Event() for _ in range(DEPTH)]     # per ring slot: the bitmask DMA has left the pinned buffer
+    consumed_p = [torch.cuda.Event() for _ in range(DEPTH)]      # per ring slot: the GPU call reading d_bits / d_adj is done
+    consumed_d = [torch.cuda.Event() for _ in range(DEPTH)]
+    ready = [torch.cuda.Event() for _ in units]                  # the unit's inputs are on the device
+
+    def pack(i):                                          # packer thread
+        n = p_ord[i]
+        slot, (_, lo, hi) = n % DEPTH, units[i]
+        if n >= DEPTH:
+            bits_copied[slot].synchronize()
+        rc = lib.ggnn_host_pack_adjacency(C.c_void_p(adj.data_ptr() + lo * per_graph), dt, (hi - lo) * per_graph_elems,
+                                          C.c_void_p(h_bits[slot].data_ptr()), _HOST_PACK_THREADS)
+        if rc != _lib.OK:
+            raise RuntimeError(f"ggnn_host_pack_adjacency failed ({rc})")
+
+    def copy_bits(i):                                     # after the unit's pack job: bitmask + states to the device
+        n = p_ord[i]
+        slot, (_, lo, hi) = n % DEPTH, units[i]
+        with torch.cuda.stream(s_in):
+            if n >= DEPTH:
+                s_in.wait_event(consumed_p[slot])         # the call that read this device buffer has run
+            d_bits[slot][:(hi - lo) * words_pg].copy_(h_bits[slot][:(hi - lo) * words_pg], non_blocking=True)
+            d_h[lo:hi].copy_(h0[lo:hi], non_blocking=True)
+            bits_copied[slot].record(s_in)
+            ready[i].record(s_in)
+
+    def copy_dense(i):                                    # the FP32 tensor itself + states to the device
+        n = d_ord[i]
+        slot, (_, lo, hi) = n % DEPTH, units[i]
+        with torch.cuda.stream(s_in):
+            if n >= DEPTH:
+                s_in.wait_event(consumed_d[slot])
+            d_adj[slot][:hi - lo].copy_(adj[lo:hi], non_blocking=True)
+            d_h[lo:hi].copy_(h0[lo:hi], non_blocking=True)
+            ready[i].record(s_in)
+
+    packer = _packer()
+    futs = {i: packer.submit(pack, i) for i in p_units[:DEPTH]}
+    for i in d_units[:DEPTH]:
+        copy_dense(i)
+    for i, (route, lo, hi) in enumerate(units):
+        if route == "P":
+            n = p_ord[i]
+            futs.pop(i).result()
+            copy_bits(i)
+            if n + DEPTH < len(p_units):                  # its pinned buffer is this unit's: free once the DMA above has run
+                j = p_units[n + DEPTH]
+                futs[j] = packer.submit(pack, j)
+        with torch.cuda.stream(s_run):
+            s_run.wait_event(ready[i])
+            if route == "P":
+                prop.propagate_dense_bits(d_h[lo:hi], d_bits[p_ord[i] % DEPTH], num_timesteps=num_timesteps, fixed_ts=fixed_ts,
+                                          precision=precision, out=d_h[lo:hi])
+                consumed_p[p_ord[i] % DEPTH].record(s_run)
+            else:
+                prop.propagate_dense(d_h[lo:hi], d_adj[d_ord[i] % DEPTH][:hi - lo], num_timesteps=num_timesteps,
+                                     fixed_ts=fixed_ts, precision=precision, out=d_h[lo:hi])
+                consumed_d[d_ord[i] % DEPTH].record(s_run)
+            done = torch.cuda.Event()
+            done.record(s_run)
+        if route == "D" and d_ord[i] + DEPTH < len(d_units):
+            copy_dense(d_units[d_ord[i] + DEPTH])
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(done)
+            out_host[lo:hi].copy_(d_h[lo:hi], non_blocking=True)
+    s_out.synchronize()
+    for t in d_bits + d_adj + [d_h]:                      # the caching allocator must not hand these out too early
+        t.record_stream(s_in); t.record_stream(s_run); t.record_stream(s_out)
+    return out_host
+
+
 def _device_of(*xs):
     for x in xs:
         if isinstance(x, torch.Tensor) and x.device.type == "cuda":
@@ -324,7 +443,10 @@ def compute_final_node_representations(initial_node_representations, adjacency_m
                              f"match [b, v, {prop.weights.hidden_size}] float32 / [b, {prop.weights.two_e}, v, v]")
         if h0.shape[0] > 0:
             if _HOST_PACK and _bits_route_ok(prop.weights.two_e, h0.shape[1]) and adj[0].numel() % 32 == 0:
-                out = _propagate_dense_from_host_packed(prop, h0, adj, num_timesteps, fixed_ts, precision)
+                if _HOST_HYBRID and adj.is_pinned() and h0.is_pinned():
+                    out = _propagate_dense_from_host_hybrid(prop, h0, adj, num_timesteps, fixed_ts, precision)
+                else:
+                    out = _propagate_dense_from_host_packed(prop, h0, adj, num_timesteps, fixed_ts, precision)
             else:
                 out = _propagate_dense_from_host(prop, h0, adj, num_timesteps, fixed_ts, precision)
             return out.numpy() if kind == "numpy" else out

@@ -23,3 +23,18 @@ for graphs_per_chunk in (16, 32, 64, 128):
             r = ggnn_b200.compute_final_node_representations(h0, adj, weights=prop, num_timesteps=T, precision="f16")
         dt = (time.perf_counter() - t0) / 5
         print(f"{graphs_per_chunk:4d} graphs per chunk, {threads:2d} packer threads: {dt * 1e3:6.2f} ms per {ne} graphs = {ne / dt:8.0f} graphs/s")
+
+print("hybrid (packer + copy engine at once):")
+api._HOST_PACK_THREADS = 15
+for hyb, pb, db in ((False, 0, 0), (True, 288, 96), (True, 192, 96), (True, 384, 96), (True, 288, 48), (True, 288, 192)):
+    api._HOST_HYBRID = hyb
+    api._HOST_PACK_CHUNK_BYTES = 128 * per_graph
+    if hyb:
+        api._HYBRID_PACK_GRAPH_BYTES, api._HYBRID_DENSE_GRAPH_BYTES = pb << 20, db << 20
+    for _ in range(3):
+        r = ggnn_b200.compute_final_node_representations(h0, adj, weights=prop, num_timesteps=T, precision="f16")
+    t0 = time.perf_counter()
+    for _ in range(5):
+        r = ggnn_b200.compute_final_node_representations(h0, adj, weights=prop, num_timesteps=T, precision="f16")
+    dt = (time.perf_counter() - t0) / 5
+    print(f"hybrid={hyb} packed unit {pb} MB dense unit {db} MB: {dt * 1e3:6.2f} ms per {ne} graphs = {ne / dt:8.0f} graphs/s")

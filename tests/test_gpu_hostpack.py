@@ -68,6 +68,15 @@ def test_packed_host_route_equals_the_device_route(precision, monkeypatch):
         got = ggnn_b200.compute_final_node_representations(s, a, weights=prop, num_timesteps=T, precision=precision)
         got = torch.from_numpy(got) if isinstance(got, np.ndarray) else got
         assert torch.equal(got, ref)
+    # the hybrid route (pinned inputs: packed and dense units alternate), small units so that both kinds occur several times
+    monkeypatch.setattr(api, "_HYBRID_PACK_GRAPH_BYTES", 5 * adj[0].numel() * 4)
+    monkeypatch.setattr(api, "_HYBRID_DENSE_GRAPH_BYTES", 3 * adj[0].numel() * 4)
+    monkeypatch.setattr(api, "_HOST_HYBRID", True)
+    got = ggnn_b200.compute_final_node_representations(h0.pin_memory(), adj.pin_memory(), weights=prop, num_timesteps=T, precision=precision)
+    assert torch.equal(got, ref)
+    monkeypatch.setattr(api, "_HOST_HYBRID", False)
+    got = ggnn_b200.compute_final_node_representations(h0.pin_memory(), adj.pin_memory(), weights=prop, num_timesteps=T, precision=precision)
+    assert torch.equal(got, ref)
     # the dense-over-the-bus pipeline (GGNN_HOST_PACK=0) gives the same bits
     monkeypatch.setattr(api, "_HOST_PACK", False)
     got = ggnn_b200.compute_final_node_representations(h0.numpy(), adj.numpy(), weights=prop, num_timesteps=T, precision=precision)
