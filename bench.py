@@ -321,7 +321,9 @@ def measure_c3(args, env):
 
     pack_threads = max(1, (os.cpu_count() or 2) // world - 1)  # the ranks of one box share its host cores; one is left to the caller
     _api._HOST_PACK_THREADS = pack_threads
-    packed = _api._HOST_PACK and _api._bits_route_ok(2 * E, V)
+    # The packer is bound by host memory bandwidth and needs cores: with fewer than 6 per rank (4 or 8 ranks on a 16-core box) the
+    # copy engines, which need none, move more -- those runs send the FP32 tensor (both routes read the same host memory).
+    packed = _api._HOST_PACK and _api._bits_route_ok(2 * E, V) and pack_threads >= 6
     e2e_s, res = time_e2e(packed)
     assert res.shape == h0_host.shape
     adj_bus_bytes = adj_host.numel() // 8 if packed else adj_host.numel() * 4
