@@ -71,13 +71,13 @@ enum {
   BAR_H_FULL,           // [2] even CTA: both h tiles of the pair
   BAR_H_STORE = BAR_H_FULL + 2,   // [2] local: the 8 epilogue warps have written h' into the h tile
   BAR_Z_DONE = BAR_H_STORE + 2,   // multicast commit: Zp / Zn of the tile are in TMEM
-  BAR_X_FULL,           // even CTA: 2 x 4 completion warps: x tiles final
+  BAR_X_FULL,           // even CTA: 2 x 6 aggregation warps: both x tiles are whole
   BAR_R_DONE,           // multicast commit: reset gate complete (it goes first: r*h is on the critical path)
   BAR_U_DONE,           // multicast commit: update gate complete
   BAR_X_READ,           // multicast commit: every MMA reading x has retired: the buffer may take the next tile's sums
   BAR_RH_FULL,          // even CTA: 16 epilogue warps
   BAR_CAND_DONE,        // multicast commit: candidate complete
-  BAR_TMEM_FREE,        // even CTA: 16 epilogue warps
+  BAR_TMEM_FREE,        // even CTA: 16 epilogue warps: u / cand of the pair consumed AND z of the next pair in A-operand form
   BAR_COUNT
 };
 static_assert(8 * BAR_COUNT + 8 <= 256, "barrier area");
