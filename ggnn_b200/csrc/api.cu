@@ -184,6 +184,7 @@ extern "C" int64_t ggnn_launch_count(const ggnn_ctx* c) { return c ? c->launches
 extern "C" int ggnn_debug_trace(ggnn_ctx* c, unsigned long long* dev_buf) {
   if (!c) return GGNN_E_ARG;
   c->dbg_trace = dev_buf;
+  { const char* e = getenv("GGNN_PAIR_TRACE_WIDE"); c->dbg_trace_wide = (e && e[0] == '1') ? 1 : 0; }
   return GGNN_OK;
 }
 

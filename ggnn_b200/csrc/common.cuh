@@ -68,6 +68,7 @@ struct ggnn_ctx {
   float* bc_w16 = nullptr;
   CUtensorMap tm_Wg, tm_Wc, tm_Wg256;  // TMA views of the packed GRU kernels (256-row box: fused kernel)
   unsigned long long* dbg_trace = nullptr;   // device buffer for kernel phase traces (ggnn_debug_trace)
+  int dbg_trace_wide = 0;                    // env GGNN_PAIR_TRACE_WIDE=1: the buffer also holds gru_pair.cu's whole-grid region
   bool   no_fused = false;   // debugging / A-B switch (GGNN_NO_FUSED=1)
   bool   repack_in_place = false; // optimizer step: shapes unchanged, packed weight buffers are reused
   bool   no_bits_plan = false; // A-B switch (GGNN_NO_BITS_PLAN=1): dense path goes through the canonical CSR

@@ -94,6 +94,8 @@ struct params {
   int n_tiles;
   int zp_row, zn_row;       // first row of W[E-1] / W[2E-1] in the packed edge weights
   unsigned long long* dbg;  // phase trace of cluster 0 (ggnn_debug_trace) or null
+  int dbg_wide;             // the buffer also has the whole-grid region (GP_WIDE)
+  int dbg_cluster;          // the cluster whose phases are traced (env GGNN_PAIR_TRACE_CLUSTER, default 0)
 };
 
 // Every bias the kernel adds.  There is no shared memory left for the GRU biases and reading them through L1 (which the
@@ -110,10 +112,20 @@ struct bias_tab {
 // development aid: event `ev` of iteration `it`, CTA `blockIdx.x` (0 or 1), nanoseconds
 #define GP_TRACE(ev)                                                                            \
   do {                                                                                          \
-    if (p.dbg && blockIdx.x < 2 && it < 12) {                                                   \
+    if (p.dbg && (blockIdx.x >> 1) == p.dbg_cluster && it < 12) {                               \
       unsigned long long t_;                                                                    \
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                    \
-      p.dbg[(blockIdx.x * 12 + it) * 32 + (ev)] = t_;                                           \
+      p.dbg[(((blockIdx.x & 1) * 12 + it) * 32 + (ev))] = t_;                                   \
+    }                                                                                           \
+  } while (0)
+
+// whole-grid trace behind the cluster-0 one: per CTA 48 slots (0 entry, 1 set-up done, 2 weights in, 3 exit, 8 + it: MMAs of pair it start)
+#define GP_WIDE(slot)                                                                           \
+  do {                                                                                          \
+    if (p.dbg && p.dbg_wide) {                                                                  \
+      unsigned long long t_;                                                                    \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                    \
+      p.dbg[2 * 12 * 32 + blockIdx.x * 48 + (slot)] = t_;                                       \
     }                                                                                           \
   } while (0)
 
@@ -218,6 +230,12 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
   // pair j of this cluster = tiles (tile0 - rank) + j * gridDim.x and the one after it; this CTA's is tile0 + j * gridDim.x.
   // A pair exists while its EVEN tile does (the odd one may lie past the end: loaded as zeros, stored clipped).
   const int tile0 = (int)blockIdx.x;                     // = 2 * (blockIdx.x >> 1) + rank
+  if (tid == 0) GP_WIDE(0);
+  if (tid == 0 && p.dbg && p.dbg_wide) {
+    unsigned smid_;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));
+    p.dbg[2 * 12 * 32 + blockIdx.x * 48 + 4] = smid_;
+  }
   auto live = [&](int tile) { return tile - (int)rank < p.n_tiles; };
   auto is_reg = [&](int tile) { return p.regular && tile < p.n_tiles && __ldg(p.regular + tile) != 0; };
 
@@ -251,6 +269,7 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
   tc::cluster_sync_all();                                 // barriers of both CTAs initialised, TMEM allocated
   tc::fence_after_sync();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_al + (tmem_slot - base));
+  if (tid == 0) GP_WIDE(1);
 
   if (warp >= WARP_AGG0) {
     // =============================== aggregation (6 warps), completion (4 of them) ===============================
@@ -432,6 +451,7 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
       };
       tc::mbar_wait_cluster(bar(BAR_W_READY), 0);
       tc::fence_after_sync();
+      GP_WIDE(2);
       if (live(tile0)) z_phase(0, tile0);
       int it = 0;
       for (int tile = tile0; live(tile); tile += gridDim.x, ++it) {
@@ -441,6 +461,7 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
         tc::mbar_wait_cluster(bar(BAR_X_FULL), it & 1);                            // x final in both CTAs, Zp / Zn consumed
         tc::fence_after_sync();
         GP_TRACE(1);
+        if (it < 40) GP_WIDE(8 + it);
         const bool preg = is_reg(tile) || is_reg(tile + 1);
         tile_mma(d_r, sX, sW + W_RUX, CHUNK, idesc128, true);                       // x -> r
         tile_mma(d_r, h0, sW + W_RUH, CHUNK, idesc128, false);                      // h -> r
@@ -606,6 +627,7 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
   tc::fence_before_sync();
   tc::cluster_sync_all();                                     // both CTAs are done with the pair's TMEM, barriers and shared memory
   if (warp == WARP_TMA) tc::tmem_dealloc_pair(tmem_base, 512);
+  if (tid == 0) GP_WIDE(3);
 }
 
 // the bias_tab of one slot, built on the device (the weights may never have been on the host): the epilogue's exponent forms
@@ -691,6 +713,8 @@ int ggnn_gru_pair_launch(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const v
   g.h_out = h_out;
   g.N = plan.N; g.h = ctx->h; g.n_tiles = (int)((plan.N + BM - 1) / BM);
   g.zp_row = e_prev * HP; g.zn_row = e_next * HP;
+  g.dbg_wide = ctx->dbg_trace_wide;
+  { const char* e = getenv("GGNN_PAIR_TRACE_CLUSTER"); g.dbg_cluster = (e && ctx->dbg_trace) ? atoi(e) : 0; }
   g.dbg = h_out ? nullptr : ctx->dbg_trace;               // trace a step that is not the last one (no FP32 output)
   const int n_pairs = (g.n_tiles + 1) / 2;
   const int clusters = n_pairs < ctx->sm_count / 2 ? n_pairs : ctx->sm_count / 2;

@@ -27,7 +27,7 @@ names = {0: "mma:tmem_free", 1: "mma:x_full", 2: "mma:ru+cx_issued", 3: "mma:rh_
          27: "agg:b0_start", 28: "agg:b1_start", 29: "agg:b2_start", 30: "agg:b0_summed", 31: "agg:b1_summed", 24: "tma:h_store", 25: "tma:store_read"}
 for cta in range(2):
     print(f"--- CTA {cta}")
-    for it in range(8):
+    for it in range(int(os.environ.get('TRACE_IT0', 0)), int(os.environ.get('TRACE_IT1', 8))):
         row = t[cta, it]
         ev = sorted((int(row[k] - t0), names[k]) for k in names if row[k])
         print(f"it {it}: " + "  ".join(f"{n}={ts}" for ts, n in ev))
