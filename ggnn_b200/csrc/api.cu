@@ -402,12 +402,14 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
       ggnn_step_bufs tb = sb;
       tb.acts = tape.at(t, TAPE_X); tb.u = tape.at(t, TAPE_U);
       tb.tape_r = tape.at(t, TAPE_R); tb.tape_c = tape.at(t, TAPE_C);
-      if (tape.w_mask) {                   // tf.nn.dropout(W): W * m_t / keep, a fresh mask per unrolled step
+      if (tape.w_mask && f16t) {           // tf.nn.dropout(W): W * m_t / keep, a fresh mask per unrolled step --
+        // formed inside the pack of this step's FP16 operand (the FP32 product is never written)
+        GGNN_TRY(ggnn_w16_repack_edge(ctx, slot, nullptr, tape.w_mask + (size_t)t * wn, 1.0f / tape.keep, st));
+      } else if (tape.w_mask) {
         GGNN_TRY(ggnn_mask_scale(ctx, ctx->edge[slot].W, tape.w_mask + (size_t)t * wn, 1.0f / tape.keep, tape.w_eff,
                                  (int64_t)wn, false, st));
         tb.W_override = tape.w_eff;
         if (tf) GGNN_TRY(ggnn_tf32_repack_edge(ctx, slot, tape.w_eff, st));   // this step's packed operand
-        if (f16t) GGNN_TRY(ggnn_w16_repack_edge(ctx, slot, tape.w_eff, st));
       }
       if (f16t) {
         const ggnn_w16_tape wt{tape.at(t, TAPE_X), tape.at(t, TAPE_R), tape.at(t, TAPE_U), tape.at(t, TAPE_C)};
@@ -427,7 +429,7 @@ int run_steps(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn_step_bu
       }
     }
     if (tf && tape.w_mask) GGNN_TRY(ggnn_tf32_repack_edge(ctx, slot, nullptr, st));   // back to the undropped weights
-    if (f16t && tape.w_mask) GGNN_TRY(ggnn_w16_repack_edge(ctx, slot, nullptr, st));
+    if (f16t && tape.w_mask) GGNN_TRY(ggnn_w16_repack_edge(ctx, slot, nullptr, nullptr, 1.f, st));
     tape.valid = true;
     return GGNN_OK;
   }

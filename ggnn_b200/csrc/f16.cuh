@@ -40,7 +40,7 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
                   void* state16, float* h_out, bool last_step, cudaStream_t st, const ggnn_w16_tape* tape = nullptr);
 int ggnn_w16_state_out(ggnn_ctx* ctx, const void* state16, float* dst, int64_t N, cudaStream_t st);
 int ggnn_w16_state_mask(ggnn_ctx* ctx, void* state16, const float* mask, float scale, int64_t N, cudaStream_t st);
-int ggnn_w16_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st);
+int ggnn_w16_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, const float* mask, float scale, cudaStream_t st);
 // message transform alone through wgemm16_kernel<MSG> (hw = 128 too) and the padded biases it reads
 int ggnn_w16_msg(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, void* state16, int hw, cudaStream_t st);
 int ggnn_w16_pack_bias(ggnn_ctx* ctx, int slot, int hw, cudaStream_t st);

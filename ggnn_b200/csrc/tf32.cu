@@ -14,6 +14,7 @@
 // (a multiple of 32) once in ggnn_set_weights, so the mainloop needs no K/N edge cases.
 #include "tf32.cuh"
 #include "tc.cuh"
+#include "pack_t.cuh"
 #include <cuda_fp16.h>
 
 namespace {
@@ -276,23 +277,12 @@ gemm_tf32_kernel(const tparams p, const __grid_constant__ CUtensorMap tmapB) {
 }
 
 // ---- weight packing -------------------------------------------------------------------
-// dst[e][n][k] (n, k < hp) = tf32(src[e][k][n]) for k, n < h, else 0
+// edge weights: dst[e][n][k] (n, k < hp) = tf32(src[e][k][n]) for k, n < h, else 0 -- packt::edge_t_kernel (pack_t.cuh)
 // lo != 0: the residual pack of the 3xTF32 split (strict_tc.cu), tf32(w - tf32(w))
 __device__ __forceinline__ float pack_val(float w, int lo) {
   const float hi = tc::to_tf32(w);
   return lo ? tc::to_tf32(w - hi) : hi;
 }
-__global__ void pack_edge_kernel(const float* __restrict__ W, float* __restrict__ Wt, int two_e,
-                                 int h, int hp, int lo) {
-  const int64_t total = (int64_t)two_e * hp * hp;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int k = (int)(i % hp), n = (int)((i / hp) % hp);
-    const int64_t e = i / ((int64_t)hp * hp);
-    Wt[i] = (k < h && n < h) ? pack_val(W[(e * h + k) * h + n], lo) : 0.f;
-  }
-}
-
 // GRU kernels: src [2h, ncols*h] (rows: x part then h part; column blocks of width h)
 // dst [ncols*hp, 2hp]: dst[nb*hp + n][kb*hp + k] = tf32(src[kb*h + k][nb*h + n])
 __global__ void pack_gru_kernel(const float* __restrict__ src, float* __restrict__ dst, int ncols,
@@ -345,20 +335,6 @@ __global__ void round_copy_kernel(const float4* __restrict__ src, float4* __rest
     float4 v = src[i];
     v.x = tc::to_tf32(v.x); v.y = tc::to_tf32(v.y); v.z = tc::to_tf32(v.z); v.w = tc::to_tf32(v.w);
     dst[i] = v;
-  }
-}
-
-// backward operands: dst[b][rb*hp + r][cb*hp + c] = tf32(src[b][(rb*h + r) * src_ld + cb*h + c]), zero padding
-__global__ void pack_blocks_kernel(const float* __restrict__ src, int src_ld, float* __restrict__ dst, int nbatch,
-                                   int rblocks, int cblocks, int h, int hp) {
-  const int64_t rows = (int64_t)rblocks * hp, cols = (int64_t)cblocks * hp;
-  const int64_t total = (int64_t)nbatch * rows * cols;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int cc = (int)(i % cols);
-    const int rr = (int)((i / cols) % rows);
-    const int64_t b = i / (rows * cols);
-    const int rb = rr / hp, r = rr % hp, cb = cc / hp, c = cc % hp;
-    dst[i] = (r < h && c < h) ? tc::to_tf32(src[(b * rblocks * h + rb * h + r) * src_ld + cb * h + c]) : 0.f;
   }
 }
 
@@ -427,18 +403,20 @@ void ggnn_tf32_nt_take(ws_alloc& a, const ggnn_ctx* ctx, ggnn_nt_weights* w) {
   w->Wc = a.take<float>(2 * hp * hp);
 }
 
-int ggnn_tf32_pack_nt_edge(ggnn_ctx* ctx, const float* W_src, ggnn_nt_weights* w, cudaStream_t st) {
+// mask != null: this step's effective weights W_src * mask * scale (edge-weight dropout), formed inside the pack
+int ggnn_tf32_pack_nt_edge(ggnn_ctx* ctx, const float* W_src, const float* mask, float scale, ggnn_nt_weights* w,
+                           cudaStream_t st) {
   const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
-  pack_blocks_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src, h, w->We, two_e, 1, 1, h, hp);
+  packt::blocks4_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(W_src, mask, scale, h, w->We, two_e, 1, 1, h, hp);
   GGNN_LAUNCHED(ctx);
   return make_weight_map(ctx, &w->tmE, w->We, (int64_t)two_e * hp, hp, &w->rowsE, hp);
 }
 
 int ggnn_tf32_pack_nt_gru(ggnn_ctx* ctx, ggnn_nt_weights* w, cudaStream_t st) {
   const int h = ctx->h, hp = ctx->hp;
-  pack_blocks_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, 2 * h, w->Wg, 1, 2, 2, h, hp);
+  packt::blocks4_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wg, nullptr, 1.f, 2 * h, w->Wg, 1, 2, 2, h, hp);
   GGNN_LAUNCHED(ctx);
-  pack_blocks_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, h, w->Wc, 1, 2, 1, h, hp);
+  packt::blocks4_kernel<<<ctx->sm_count * 2, 256, 0, st>>>(ctx->Wc, nullptr, 1.f, h, w->Wc, 1, 2, 1, h, hp);
   GGNN_LAUNCHED(ctx);
   GGNN_TRY(make_weight_map(ctx, &w->tmG, w->Wg, 2 * hp, 2 * hp, &w->rowsG, 2 * hp));
   return make_weight_map(ctx, &w->tmC, w->Wc, 2 * hp, hp, &w->rowsC, 2 * hp);
@@ -461,7 +439,7 @@ int ggnn_tf32_nt(ggnn_ctx* ctx, const float* A1, const float* A2, int lda, const
 // edge weights of `slot` re-packed from W_src (dropout: this step's effective weights; null = the slot's own)
 int ggnn_tf32_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st) {
   ggnn_edge_weights& ew = ctx->edge[slot];
-  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src ? W_src : ew.W, ew.Wt_tf32, ctx->two_e, ctx->h, ctx->hp, 0);
+  packt::launch_edge_t<packt::OUT_TF32>(W_src ? W_src : ew.W, nullptr, 1.f, ew.Wt_tf32, ctx->two_e, ctx->h, ctx->hp, st);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
@@ -482,13 +460,13 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
   const int h = ctx->h, hp = ctx->hp, two_e = ctx->two_e;
   ggnn_edge_weights& ew = ctx->edge[slot];
   GGNN_TRY(realloc_f(ctx, ew.Wt_tf32, (size_t)two_e * hp * hp));
-  pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32, two_e, h, hp, 0);
+  packt::launch_edge_t<packt::OUT_TF32>(ew.W, nullptr, 1.f, ew.Wt_tf32, two_e, h, hp, st);
   GGNN_LAUNCHED(ctx);
   GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt, ew.Wt_tf32, (int64_t)two_e * hp, hp, &ew.tm_rows, hp));
   const bool strict_tc = hp <= 128;      // residual packs of the strict (3xTF32) mode, strict_tc.cu
   if (strict_tc) {
     GGNN_TRY(realloc_f(ctx, ew.Wt_tf32_lo, (size_t)two_e * hp * hp));
-    pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, ew.Wt_tf32_lo, two_e, h, hp, 1);
+    packt::launch_edge_t<packt::OUT_TF32_LO>(ew.W, nullptr, 1.f, ew.Wt_tf32_lo, two_e, h, hp, st);
     GGNN_LAUNCHED(ctx);
     int rows_lo;
     GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt_lo, ew.Wt_tf32_lo, (int64_t)two_e * hp, hp, &rows_lo, hp));

@@ -44,7 +44,8 @@ struct ggnn_nt_weights {
 };
 size_t ggnn_tf32_nt_weight_floats(const ggnn_ctx* ctx);
 void ggnn_tf32_nt_take(ws_alloc& a, const ggnn_ctx* ctx, ggnn_nt_weights* w);
-int ggnn_tf32_pack_nt_edge(ggnn_ctx* ctx, const float* W_src, ggnn_nt_weights* w, cudaStream_t st);
+int ggnn_tf32_pack_nt_edge(ggnn_ctx* ctx, const float* W_src, const float* mask, float scale, ggnn_nt_weights* w,
+                           cudaStream_t st);
 int ggnn_tf32_pack_nt_gru(ggnn_ctx* ctx, ggnn_nt_weights* w, cudaStream_t st);
 // out[crow, (n / hp) * h + n % hp] (=|+=) sum_k A[row, k] * Bt[n, k];  A = [A1 | A2] (K segments of hp), rows
 // optionally gathered; crow = row (store) or c_rowmap[row] (atomic add); grouped by tile type when tile_type != null

@@ -457,7 +457,7 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
   ggnn_nt_weights ntw = s.ntw;
   if (tf) {
     GGNN_TRY(ggnn_tf32_pack_nt_gru(ctx, &ntw, st));
-    if (have_msgs && !tape.w_mask) GGNN_TRY(ggnn_tf32_pack_nt_edge(ctx, ew.W, &ntw, st));
+    if (have_msgs && !tape.w_mask) GGNN_TRY(ggnn_tf32_pack_nt_edge(ctx, ew.W, nullptr, 1.f, &ntw, st));
   }
   const int tn_rows = 2048;
   const float* dhn = d_hT;
@@ -471,7 +471,7 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
       dhn = s.dx;            // dx is free until the second pointwise kernel of this step
     }
     const float* Wt = ew.W;
-    if (tape.w_mask) {       // this step's effective weights W * m_t / keep
+    if (tape.w_mask && !tf) {   // this step's effective weights W * m_t / keep (tensor-core path: formed inside the operand pack)
       GGNN_TRY(ggnn_mask_scale(ctx, ew.W, tape.w_mask + (size_t)t * two_e * h * h, inv_keep, tape.w_eff,
                                (int64_t)two_e * h * h, false, st));
       Wt = tape.w_eff;
@@ -479,7 +479,8 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
     gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h, rnd);
     GGNN_LAUNCHED(ctx);
     if (tf) {
-      if (tape.w_mask && have_msgs) GGNN_TRY(ggnn_tf32_pack_nt_edge(ctx, Wt, &ntw, st));
+      if (tape.w_mask && have_msgs)
+        GGNN_TRY(ggnn_tf32_pack_nt_edge(ctx, ew.W, tape.w_mask + (size_t)t * two_e * h * h, inv_keep, &ntw, st));
       GGNN_TRY(ggnn_tf32_nt(ctx, s.dzc, nullptr, h, nullptr, N, mt, ntw.Wc, ntw.tmC, ntw.rowsC, hp, 2 * hp, nullptr,
                             nullptr, s.dxr, 2 * h, nullptr, st));
       for (int part = 0; part < 2; ++part)

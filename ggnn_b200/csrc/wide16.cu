@@ -24,6 +24,7 @@
 #include "f16.cuh"
 #include "tf32.cuh"
 #include "tc.cuh"
+#include "pack_t.cuh"
 #include <cuda_fp16.h>
 
 namespace w16 {
@@ -369,15 +370,7 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
 }
 
 // ---- packing ------------------------------------------------------------------------------
-// dst[e][n][k] (n, k < hw) = f16(src[e][k][n]) for k, n < h, else 0
-__global__ void pack_edge_kernel(const float* __restrict__ W, __half* __restrict__ Wt, int two_e, int h, int hw) {
-  const int64_t total = (int64_t)two_e * hw * hw;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int k = (int)(i % hw), n = (int)((i / hw) % hw);
-    const int64_t e = i / ((int64_t)hw * hw);
-    Wt[i] = __float2half_rn((k < h && n < h) ? W[(e * h + k) * h + n] : 0.f);
-  }
-}
+// edge weights: dst[e][n][k] (n, k < hw) = f16(src[e][k][n]) for k, n < h, else 0 -- packt::edge_t_kernel (pack_t.cuh)
 // src [2h, ncols*h] -> dst [ncols*hw, 2hw]: dst[nb*hw+n][kb*hw+k] = f16(src[kb*h+k][nb*h+n])
 __global__ void pack_gru_kernel(const float* __restrict__ src, __half* __restrict__ dst, int ncols, int h, int hw) {
   const int Kp = 2 * hw, Np = ncols * hw;
@@ -1111,7 +1104,7 @@ int ggnn_w16_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t s
   ggnn_edge_weights& ew = ctx->edge[slot];
   ew.absmax_w = -1.f;
   GGNN_TRY(realloc_bytes(ctx, ew.Wt_f16, (size_t)two_e * hw * hw * 2));
-  w16::pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(ew.W, reinterpret_cast<__half*>(ew.Wt_f16), two_e, h, hw);
+  packt::launch_edge_t<packt::OUT_F16>(ew.W, nullptr, 1.f, ew.Wt_f16, two_e, h, hw, st);
   GGNN_LAUNCHED(ctx);
   void* bp = ew.B_pad16;
   GGNN_TRY(realloc_bytes(ctx, bp, (size_t)two_e * hw * 4));
@@ -1287,11 +1280,11 @@ int ggnn_w16_state_mask(ggnn_ctx* ctx, void* state16, const float* mask, float s
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
-// edge weights of `slot` re-packed from W_src (dropout: this step's effective weights; null = the slot's own)
-int ggnn_w16_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, cudaStream_t st) {
+// edge weights of `slot` re-packed from W_src (null = the slot's own); mask != null: this step's effective weights
+// W_src * mask * scale (edge-weight dropout), formed inside the pack
+int ggnn_w16_repack_edge(ggnn_ctx* ctx, int slot, const float* W_src, const float* mask, float scale, cudaStream_t st) {
   ggnn_edge_weights& ew = ctx->edge[slot];
-  w16::pack_edge_kernel<<<ctx->sm_count * 4, 256, 0, st>>>(W_src ? W_src : ew.W, reinterpret_cast<__half*>(ew.Wt_f16),
-                                                          ctx->two_e, ctx->h, ctx->hw16);
+  packt::launch_edge_t<packt::OUT_F16>(W_src ? W_src : ew.W, mask, scale, ew.Wt_f16, ctx->two_e, ctx->h, ctx->hw16, st);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
