@@ -82,17 +82,24 @@ __global__ void edge_assign_kernel(const int32_t* __restrict__ edges, int64_t nn
   tval[pos] = mrow;
 }
 
-// one thread per node: insertion sort of its (key, val) segment by (channel, source), then emit tmsg.  Slots inside a
-// segment were handed out with atomicAdd, so edges with EQUAL keys (duplicate (src, channel, dst) triples) end up in
-// arbitrary relative order -- harmless: their message values are identical, so the sum does not depend on it.
-// O(d^2) per node: fine for the in-degrees of the configurations (<= ~130); a hub with 1e5 in-edges would want a
-// segmented sort instead.
+// Sorting a node's (key, val) segment by (channel, source).  Slots inside a segment were handed out with atomicAdd, so
+// edges with EQUAL keys (duplicate (src, channel, dst) triples) end up in arbitrary relative order -- harmless: their
+// message values are identical, so the sum does not depend on it.
+// Two kernels: nodes with at most HUB_DEG incoming edges (every node of the BASELINE configurations) are sorted by one
+// thread each (insertion sort, O(d^2)); a hub -- e.g. a ROOT node shared by a packed batch, 1e5 in-edges -- would keep a
+// single thread busy for seconds that way, so hubs are left to target_sort_hub_kernel: a whole CTA per hub, bitonic
+// network in shared memory (d <= HUB_SMEM) or in place in global memory (L2) above that, O(d log^2 d / threads).
+constexpr int HUB_DEG = 64;
+constexpr int HUB_SMEM = 2048;
+constexpr int HUB_THREADS = 512;
+
 __global__ void target_sort_kernel(const int32_t* __restrict__ tptr, int64_t N,
                                    unsigned long long* __restrict__ tkey,
                                    int32_t* __restrict__ tval) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   const int j0 = tptr[n], j1 = tptr[n + 1];
+  if (j1 - j0 > HUB_DEG) return;                      // target_sort_hub_kernel
   for (int i = j0 + 1; i < j1; ++i) {
     unsigned long long k = tkey[i];
     int32_t v = tval[i];
@@ -104,6 +111,62 @@ __global__ void target_sort_kernel(const int32_t* __restrict__ tptr, int64_t N,
     }
     tkey[j + 1] = k;
     tval[j + 1] = v;
+  }
+}
+
+// Bitonic network in its "flip + disperse" form: every compare-exchange moves the smaller key to the LOWER index, so a
+// length that is not a power of two needs no padding -- the missing elements behave as +inf at the top and never move.
+template <typename K, typename V>
+__device__ __forceinline__ void bitonic_block(K* key, V* val, int n) {
+  for (int k = 2; (k >> 1) < n; k <<= 1) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {          // flip: partner inside the block of k elements
+      const int j = i ^ (k - 1);
+      if (j > i && j < n) {
+        const K a = key[i], b = key[j];
+        if (a > b) { key[i] = b; key[j] = a; const V t = val[i]; val[i] = val[j]; val[j] = t; }
+      }
+    }
+    __syncthreads();
+    for (int d = k >> 2; d > 0; d >>= 1) {                        // disperse
+      for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int j = i | d;
+        if ((i & d) == 0 && j < n) {
+          const K a = key[i], b = key[j];
+          if (a > b) { key[i] = b; key[j] = a; const V t = val[i]; val[i] = val[j]; val[j] = t; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(HUB_THREADS)
+target_sort_hub_kernel(const int32_t* __restrict__ tptr, int64_t N, unsigned long long* tkey, int32_t* tval) {
+  __shared__ unsigned long long s_key[HUB_SMEM];
+  __shared__ int32_t s_val[HUB_SMEM];
+  __shared__ int s_hub[HUB_THREADS];
+  __shared__ int s_nhub;
+  for (int64_t span = (int64_t)blockIdx.x * HUB_THREADS; span < N; span += (int64_t)gridDim.x * HUB_THREADS) {
+    if (threadIdx.x == 0) s_nhub = 0;
+    __syncthreads();
+    const int64_t n = span + threadIdx.x;
+    if (n < N && tptr[n + 1] - tptr[n] > HUB_DEG) s_hub[atomicAdd(&s_nhub, 1)] = (int)threadIdx.x;
+    __syncthreads();
+    const int nhub = s_nhub;
+    for (int q = 0; q < nhub; ++q) {                              // (list order is arbitrary; every hub is independent)
+      const int64_t node = span + s_hub[q];
+      const int j0 = tptr[node], d = tptr[node + 1] - j0;
+      if (d <= HUB_SMEM) {
+        for (int i = threadIdx.x; i < d; i += blockDim.x) { s_key[i] = tkey[j0 + i]; s_val[i] = tval[j0 + i]; }
+        __syncthreads();
+        bitonic_block(s_key, s_val, d);
+        for (int i = threadIdx.x; i < d; i += blockDim.x) { tkey[j0 + i] = s_key[i]; tval[j0 + i] = s_val[i]; }
+        __syncthreads();
+      } else {
+        bitonic_block(tkey + j0, tval + j0, d);                   // in place; __syncthreads orders the CTA's global accesses
+      }
+    }
+    __syncthreads();                                              // s_hub / s_nhub are rewritten by the next span
   }
 }
 
@@ -161,6 +224,12 @@ int ggnn_plan_from_edges(ggnn_ctx* ctx, const int32_t* edges, int64_t nnz, int64
     GGNN_LAUNCHED(ctx);
     target_sort_kernel<<<(unsigned)ceil_div64(N, 128), 128, 0, st>>>(plan->tptr, N, tkey, plan->tmsg);
     GGNN_LAUNCHED(ctx);
+    if (nnz > HUB_DEG) {                // a node with more than HUB_DEG incoming edges can exist
+      const int64_t spans = ceil_div64(N, HUB_THREADS);
+      const unsigned hg = (unsigned)(spans < 2 * (int64_t)ctx->sm_count ? spans : 2 * (int64_t)ctx->sm_count);
+      target_sort_hub_kernel<<<hg, HUB_THREADS, 0, st>>>(plan->tptr, N, tkey, plan->tmsg);
+      GGNN_LAUNCHED(ctx);
+    }
   }
   return GGNN_OK;
 }

@@ -170,6 +170,46 @@ def test_csr_edges_and_dense_paths_agree():
     assert np.array_equal(sp2.reshape(b, v, h), dense.cpu().numpy())
 
 
+def test_hub_nodes_in_an_edge_list():
+    """Nodes with thousands of incoming edges (a ROOT shared by a packed batch): their target lists are sorted by
+    plan_edges.cu's CTA-per-hub bitonic kernel (shared memory up to 2 048 edges, in place in global memory above) instead
+    of the one-thread insertion sort.  Same (channel, source) summation order as the CSR route -> bit-identical."""
+    N, types, h, T = 6000, 2, 128, 2
+    two_e = 2 * types
+    rng = np.random.default_rng(5)
+    tri = [(s, s % two_e, 0) for s in range(1, 5001)]                    # 5 000 edges into node 0: global-memory sort
+    tri += [(s, (s * 7) % two_e, 1) for s in range(2, 1502)]             # 1 500 into node 1: shared-memory sort
+    tri += [(s, (s * 3) % two_e, 2) for s in range(3, 103)]              # 100 into node 2: just above the threshold
+    tri += [(int(rng.integers(0, N)), int(rng.integers(0, two_e)), int(d)) for d in rng.integers(3, N, 12000)]
+    edges = np.unique(np.array(tri, dtype=np.int32), axis=0)
+    edges = edges[rng.permutation(len(edges))]
+    w = _weights(two_e, h, 0)
+    w["edge_weights"] = w["edge_weights"] * 0.05                          # 5 000 messages summed into one node stay O(1)
+    prop = Propagator(W.from_dict(w), "cuda:0")
+    h0 = rng.uniform(-0.1, 0.1, (N, h)).astype(np.float32)
+    h0_d = torch.from_numpy(h0).cuda()
+    sp = prop.propagate_edges(h0_d, torch.from_numpy(edges).cuda(), num_timesteps=T)
+    # the same graph as a CSR over (channel, target) rows with ascending sources
+    order = np.lexsort((edges[:, 0], edges[:, 2], edges[:, 1]))
+    e_sorted = edges[order]
+    rows = e_sorted[:, 1].astype(np.int64) * N + e_sorted[:, 2]
+    rowptr = np.zeros(two_e * N + 1, dtype=np.int64)
+    np.cumsum(np.bincount(rows, minlength=two_e * N), out=rowptr[1:])
+    csr = prop.propagate_csr(h0_d.view(1, N, h), torch.from_numpy(rowptr.astype(np.int32)).cuda(),
+                             torch.from_numpy(np.ascontiguousarray(e_sorted[:, 0])).cuda(), num_timesteps=T)
+    assert torch.equal(sp, csr.view(N, h))
+    ref = O.propagate_edges(h0, edges, w, T)
+    # 5 000 messages (with their biases) summed into one node: the strict mode's FP32 sum itself is 6e-5 away from FP64 here
+    assert O.normwise_err(sp.cpu().numpy(), ref) <= 2e-4
+    # (5 000 rounded messages into one node: the 11-bit modes are compared with their own CSR route, not with a tolerance)
+    for precision in ("tf32", "f16"):
+        out = prop.propagate_edges(h0_d, torch.from_numpy(edges).cuda(), num_timesteps=T, precision=precision)
+        csr_p = prop.propagate_csr(h0_d.view(1, N, h), torch.from_numpy(rowptr.astype(np.int32)).cuda(),
+                                   torch.from_numpy(np.ascontiguousarray(e_sorted[:, 0])).cuda(), num_timesteps=T,
+                                   precision=precision)
+        assert torch.equal(out, csr_p.view(N, h)), precision
+
+
 @pytest.mark.parametrize("precision", ["fp32", "tf32"])
 def test_sparse_large_graph_dense_mode(precision):
     """C4 shape scaled down: nnz >= N*2E so every (node, channel) is transformed once."""
