@@ -26,6 +26,8 @@ struct prefetch_rec {
   bool active = false;
   const void* adj = nullptr;
   int dtype = 0, b = 0, v = 0, two_e = 0, buf = 0;
+  bool counted = false;      // the row counts / scans of the plan were run on the side stream too, with ...
+  bool word_fold = false;    // ... this word-order setting (the consuming call re-counts from the bitmask if its own differs)
 };
 
 struct ctx_ext {
@@ -35,6 +37,11 @@ struct ctx_ext {
   cudaEvent_t pf_done[2] = {nullptr, nullptr};
   prefetch_rec pf;
   int pf_last_buf = 1;       // buffer of the last CONSUMED prefetch: the next one goes to the other
+  // the counting half of the plan (plan_bits.cu count + scans) depends on whether the word-order channels are folded
+  // into the GRU kernel, i.e. on the precision / slot / flags of the CONSUMING call, which a prefetch does not know: it
+  // assumes the next call looks like the last one on the bitmask route
+  bool last_known = false, last_word_fold = false;
+  bool pf_count = true;      // GGNN_PF_COUNT=0: prefetch the bitmask only (A-B switch)
   int64_t adam_n = 0;       // floats the moment buffers were sized (and zeroed) for
   int64_t adam_t = 0;       // steps taken
   ggnn_tape tape;
@@ -543,6 +550,12 @@ static int propagate_dense_impl(ggnn_ctx* ctx, int slot, const float* h0, const 
       }
       ws_alloc a0(ext_of(ctx)->ar[0].p);
       ggnn_plan_bits_take_pre(a0, bc, two_e, v, &pre);
+      // GGNN_PREC_F16, h <= 128, v == 128: graphs whose word-order channels are exactly t-1 -> t / t+1 -> t keep those
+      // edges out of the plan; the GRU kernel forms them from the resident h tile (f16.cu)
+      const bool word_fold = precision == GGNN_PREC_F16 && v == GGNN_TILE_M && !(flags & GGNN_FLAG_SAVE_TAPE) &&
+                             ggnn_f16_word_fold_ready(ctx, slot);
+      ex->last_known = true; ex->last_word_fold = word_fold;
+      bool counted = false;
       if (precision == GGNN_PREC_F16)
         GGNN_TRY(f16_prologue(ctx, slot, f16_direct ? h0 + (size_t)g0 * v * h : h_chunk, bc * v, st));
       if (bits_in) {
@@ -550,22 +563,25 @@ static int propagate_dense_impl(ggnn_ctx* ctx, int slot, const float* h0, const 
       } else if (use_pf) {
         // the background pass has been streaming this adjacency since the prefetch call: take the slices that are
         // left at full occupancy, then wait for the background CTAs' last slices
+        // (the plan's per-row arrays live behind the bitmask in the prefetch buffer: the side stream may have filled them)
         char* pb = ex->ar[7 + pf.buf].p;
-        pre.bits = reinterpret_cast<uint32_t*>(pb + 4096);
+        ws_alloc ap(pb + 4096);
+        ggnn_plan_bits_take_pre(ap, bc, two_e, v, &pre);
+        const int64_t* pf_nnz = ap.take<int64_t>(1);
         {
           prof_scope ps(ctx, GGNN_STAGE_COMPACT_MASK, st);
           GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj_c, adj_dtype, rows * v, pre.bits, reinterpret_cast<unsigned*>(pb), false, st));
         }
         GGNN_CUDA(ctx, cudaStreamWaitEvent(st, ex->pf_done[pf.buf], 0));
         ex->pf_last_buf = pf.buf;
+        if (pf.counted && pf.word_fold == word_fold) {      // counts and scans are there already; the edge count joins the mailbox
+          GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->d_mail, pf_nnz, sizeof(int64_t), cudaMemcpyDeviceToDevice, st));
+          counted = true;
+        }
       } else {
         GGNN_TRY(ggnn_compact_bitmask(ctx, adj_c, adj_dtype, rows * v, pre.bits, st));
       }
-      // GGNN_PREC_F16, h <= 128, v == 128: graphs whose word-order channels are exactly t-1 -> t / t+1 -> t keep those
-      // edges out of the plan; the GRU kernel forms them from the resident h tile (f16.cu)
-      const bool word_fold = precision == GGNN_PREC_F16 && v == GGNN_TILE_M && !(flags & GGNN_FLAG_SAVE_TAPE) &&
-                             ggnn_f16_word_fold_ready(ctx, slot);
-      GGNN_TRY(ggnn_plan_bits_count(ctx, pre, bc, two_e, v, word_fold, ctx->d_mail, st));
+      if (!counted) GGNN_TRY(ggnn_plan_bits_count(ctx, pre, bc, two_e, v, word_fold, ctx->d_mail, st));
       int64_t nnz = 0;
       GGNN_TRY(read_i64(ctx, ctx->d_mail, &nnz, st));     // the one planning sync
       if (precision == GGNN_PREC_F16) GGNN_TRY(f16_check(ctx, slot));
@@ -642,19 +658,38 @@ extern "C" int ggnn_dense_prefetch(ggnn_ctx* ctx, const void* adj, int adj_dtype
     return GGNN_OK;
   }
   if (!ex->side) {
-    GGNN_CUDA(ctx, cudaStreamCreateWithFlags(&ex->side, cudaStreamNonBlocking));
+    // lowest priority: the side stream's short count CTAs must not get in front of the caller's persistent kernels
+    int prio_lo = 0, prio_hi = 0;
+    GGNN_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    GGNN_CUDA(ctx, cudaStreamCreateWithPriority(&ex->side, cudaStreamNonBlocking, prio_lo));
+    { const char* e = getenv("GGNN_PF_COUNT"); ex->pf_count = !(e && e[0] == '0'); }
     for (auto& e : ex->pf_done) GGNN_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   int buf = ex->pf_last_buf ^ 1;
   if (ex->pf.active) { buf = ex->pf.buf; prefetch_cancel(ctx); }   // replaced before it was used: same buffer
-  const size_t words = (size_t)(total / 32);
-  GGNN_TRY(arena_reserve(ctx, 7 + buf, 4096 + words * 4 + 256, ex->side));
+  ggnn_plan_bits_pre pre;
+  {
+    ws_alloc dry(nullptr);
+    ggnn_plan_bits_take_pre(dry, b, two_e, v, &pre);
+    dry.take<int64_t>(1);
+    GGNN_TRY(arena_reserve(ctx, 7 + buf, 4096 + dry.off + 256, ex->side));
+  }
   char* pb = ex->ar[7 + buf].p;
+  ws_alloc ap(pb + 4096);
+  ggnn_plan_bits_take_pre(ap, b, two_e, v, &pre);          // pre.bits = pb + 4096
+  int64_t* pf_nnz = ap.take<int64_t>(1);
   GGNN_CUDA(ctx, cudaMemsetAsync(pb, 0, ggnn_bitmask_queue_ctl_bytes(), ex->side));
   if (ready_event) GGNN_CUDA(ctx, cudaStreamWaitEvent(ex->side, (cudaEvent_t)ready_event, 0));
-  GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj, adj_dtype, total, reinterpret_cast<uint32_t*>(pb + 4096),
-                                     reinterpret_cast<unsigned*>(pb), true, ex->side));
+  GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj, adj_dtype, total, pre.bits, reinterpret_cast<unsigned*>(pb), true, ex->side));
+  // The counting half of the plan follows the bitmask on the side stream (the background CTAs finish the queue on their
+  // own; the consuming call's drain launch only helps): 0.22 ms per 4 096 C3 graphs that the consuming call no longer
+  // runs in front of its first timestep.  The buffer is safe to reuse: it alternates, and the call in between has
+  // synchronised the caller's stream (planning sync) after the last reader of this one.
+  const bool fold = ex->last_word_fold && v == GGNN_TILE_M && two_e >= 2 && two_e % 2 == 0;
+  const bool count = ex->pf_count && ex->last_known;
+  if (count) GGNN_TRY(ggnn_plan_bits_count(ctx, pre, b, two_e, v, fold, pf_nnz, ex->side));
   GGNN_CUDA(ctx, cudaEventRecord(ex->pf_done[buf], ex->side));
+  ex->pf.counted = count; ex->pf.word_fold = fold;
   ex->pf.active = true; ex->pf.adj = adj; ex->pf.dtype = adj_dtype; ex->pf.b = b; ex->pf.v = v;
   ex->pf.two_e = two_e; ex->pf.buf = buf;
   return GGNN_OK;

@@ -42,12 +42,14 @@ __device__ __forceinline__ int row_popc(const uint32_t* __restrict__ bits, int64
   return c;
 }
 
-// one CTA per graph, thread t = target node.  smem: int part[nwarps][two_e]
+// one CTA per graph, thread t = target node.  smem: uint16 part[nwarps][two_e] (a warp's 32 rows hold at most 32 * 255
+// edges).  16-bit on purpose: at v = 128 the CTA then needs 736 bytes of shared memory and fits beside a CTA of the
+// 226 KB GRU kernels when the counts of the NEXT call run on the prefetch stream (ggnn_dense_prefetch)
 __global__ void __launch_bounds__(MAX_THREADS)
 graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int v,
                    uint16_t* __restrict__ rowcnt, int32_t* __restrict__ seglenT,
                    int32_t* __restrict__ tcnt, int word_fold, int32_t* __restrict__ regular) {
-  extern __shared__ int part[];
+  extern __shared__ uint16_t part[];
   const int64_t g = blockIdx.x;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
   // word-order graph (v == 128 = blockDim.x): row t of channel E-1 is exactly {t-1}, of channel 2E-1 exactly {t+1}
@@ -68,7 +70,7 @@ graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int 
     if (t == 0) regular[g] = reg;
   }
   int deg = 0;
-#pragma unroll 4
+#pragma unroll 8
   for (int e = 0; e < two_e; ++e) {
     const int64_t r = (g * two_e + e) * v + t;
     int c = 0;
@@ -80,7 +82,7 @@ graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int 
     int s = c;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) part[wid * two_e + e] = s;
+    if (lane == 0) part[wid * two_e + e] = (uint16_t)s;
   }
   if (t < v) tcnt[g * v + t] = deg;
   if (g == b - 1 && t == 0) { tcnt[b * v] = 0; seglenT[b * two_e] = 0; }
@@ -208,7 +210,7 @@ int ggnn_plan_bits_count(ggnn_ctx* ctx, const ggnn_plan_bits_pre& pre, int64_t b
   prof_scope ps(ctx, GGNN_STAGE_COMPACT_REST, st);
   const int vt = threads_for(v);
   if (word_fold && (v != GGNN_TILE_M || two_e < 2 || two_e % 2)) GGNN_FAIL(ctx, GGNN_E_ARG, "internal: word_fold needs v == 128 and an even channel count");
-  graph_count_kernel<<<(unsigned)b, vt, (size_t)(vt / 32) * two_e * 4, st>>>(pre.bits, b, two_e, v, pre.rowcnt,
+  graph_count_kernel<<<(unsigned)b, vt, (size_t)(vt / 32) * two_e * 2, st>>>(pre.bits, b, two_e, v, pre.rowcnt,
                                                                             pre.segposT, pre.tptr, word_fold ? 1 : 0,
                                                                             pre.regular);
   GGNN_LAUNCHED(ctx);

@@ -53,6 +53,25 @@ def test_prefetch_pipeline_over_batches():
         assert torch.equal(out, plain[k]), k
 
 
+def test_background_counts_follow_the_last_calls_setting():
+    """The side stream also runs the counting half of the plan, assuming the next call folds the word-order channels
+    like the last one did (api.cu): v = 128 F16 calls fold them, strict calls do not.  Alternating precisions makes the
+    consuming call reuse the counts (same setting) or re-count from the bitmask (different setting); either way the
+    result is the plain call's."""
+    v, E, h, T = 128, 6, 128, 2
+    prop = Propagator(ggnn_b200.from_dict(synth.make_weights(2 * E, h, 4)), "cuda:0")
+    adj, h0 = _case(192, v, E, h, 30)
+    adj2, h2 = _case(192, v, E, h, 31)
+    adj2[5, E - 1, 7, 9] = 1.0                            # one graph whose word-order channel is not regular
+    want = {(p, i): prop.propagate_dense(hh, aa, num_timesteps=T, precision=p)
+            for p in ("f16", "fp32") for i, (aa, hh) in enumerate(((adj, h0), (adj2, h2)))}
+    order = ["f16", "f16", "fp32", "fp32", "f16", "fp32", "f16", "f16"]
+    for k, p in enumerate(order):
+        aa, hh = ((adj, h0), (adj2, h2))[k & 1]
+        prop.prefetch_dense(aa)
+        assert torch.equal(prop.propagate_dense(hh, aa, num_timesteps=T, precision=p), want[(p, k & 1)]), (k, p)
+
+
 def test_prefetch_dropped_or_replaced_is_harmless():
     b, v, E, h, T = 64, 32, 5, 128, 2
     w = synth.make_weights(2 * E, h, 2)
