@@ -270,7 +270,10 @@ colsum_kernel(const float* __restrict__ D, int ldd, const int32_t* __restrict__ 
 
 // ---- pointwise pieces of the GRU backward -------------------------------------------------
 // dzc = dh'(1-u)(1-c^2);  dzu -> dzg[:, h:];  dh = dh' u;  rh = r*h (recomputed operand of dWc)
-__global__ void gru_bwd_pw1_kernel(const float* __restrict__ dhn, const float* __restrict__ hs,
+// smask != null: dh' arrives w.r.t. the DROPPED state h' * s_t / keep, so it is (dhn * smask) * sscale here (the product
+// ggnn_mask_scale would have materialised, same order of operations)
+__global__ void gru_bwd_pw1_kernel(const float* __restrict__ dhn, const float* __restrict__ smask, float sscale,
+                                   const float* __restrict__ hs,
                                    const float* __restrict__ r, const float* __restrict__ u,
                                    const float* __restrict__ c, float* __restrict__ dzc,
                                    float* __restrict__ dzg, float* __restrict__ dh, float* __restrict__ rh,
@@ -278,7 +281,8 @@ __global__ void gru_bwd_pw1_kernel(const float* __restrict__ dhn, const float* _
   const int64_t total = N * h;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / h; const int k = (int)(i % h);
-    const float g = dhn[i], uu = u[i], cc = c[i], hh = hs[i];
+    const float g = smask ? dhn[i] * smask[i] * sscale : dhn[i];
+    const float uu = u[i], cc = c[i], hh = hs[i];
     float a = g * (1.f - uu) * (1.f - cc * cc), b = g * (hh - cc) * uu * (1.f - uu), q = r[i] * hh;
     if (rnd) { a = tc::to_tf32(a); b = tc::to_tf32(b); q = tc::to_tf32(q); }
     dzc[i] = a;
@@ -466,17 +470,15 @@ int ggnn_backward_fp32(ggnn_ctx* ctx, const ggnn_tape& tape, const ggnn_bwd_scra
     const float *ht = tape.at(t, TAPE_H), *xt = tape.at(t, TAPE_X), *rt = tape.at(t, TAPE_R),
                 *ut = tape.at(t, TAPE_U), *ct = tape.at(t, TAPE_C);
     const float inv_keep = 1.0f / tape.keep;
-    if (tape.state_mask) {   // dhn is w.r.t. the dropped state h' * s_t / keep
-      GGNN_TRY(ggnn_mask_scale(ctx, dhn, tape.state_mask + (size_t)t * nh, inv_keep, s.dx, (int64_t)nh, false, st));
-      dhn = s.dx;            // dx is free until the second pointwise kernel of this step
-    }
+    // (dhn is w.r.t. the dropped state h' * s_t / keep: the first pointwise kernel applies the mask on the way in)
+    const float* smask = tape.state_mask ? tape.state_mask + (size_t)t * nh : nullptr;
     const float* Wt = ew.W;
     if (tape.w_mask && !tf) {   // this step's effective weights W * m_t / keep (tensor-core path: formed inside the operand pack)
       GGNN_TRY(ggnn_mask_scale(ctx, ew.W, tape.w_mask + (size_t)t * two_e * h * h, inv_keep, tape.w_eff,
                                (int64_t)two_e * h * h, false, st));
       Wt = tape.w_eff;
     }
-    gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h, rnd);
+    gru_bwd_pw1_kernel<<<pw_grid, 256, 0, st>>>(dhn, smask, inv_keep, ht, rt, ut, ct, s.dzc, s.dzg, dh, s.rh, N, h, rnd);
     GGNN_LAUNCHED(ctx);
     if (tf) {
       if (tape.w_mask && have_msgs)
