@@ -146,7 +146,9 @@ int ggnn_propagate_dense(ggnn_ctx* ctx, int slot, const float* h0,
  * HBM-bound half of the path) starts at once on a ctx-owned side stream as a small background kernel that
  * shares the SMs with the msg / GRU kernels still running on the caller's stream; the propagate call that
  * follows with the SAME (adj, adj_dtype, b, v) finishes whatever is left of the pass and goes on as usual --
- * same results, bit for bit.  Any other ggnn_propagate_dense call, a second prefetch, or ggnn_set_weights drops
+ * same results, bit for bit.  The plan's counting kernels follow the pass on the side stream, assuming the consuming
+ * call uses the precision / slot / flags of the ctx's last dense call (they decide whether word-order channels are
+ * counted); a consuming call that differs simply counts again.  Any other ggnn_propagate_dense call, a second prefetch, or ggnn_set_weights drops
  * the announcement (after waiting for the background pass).
  *   - `adj` must already hold its final contents when this is called, or `ready_event` (a cudaEvent_t as void*,
  *     else NULL) must mark their completion; it must stay valid until the consuming call's work has finished;
