@@ -14,6 +14,7 @@
 // plan.cu (same tile table, same segment offsets), so results are bit-identical to the CSR route.
 #include "plan.cuh"
 #include "plan_bits.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -94,18 +95,49 @@ graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int 
   }
 }
 
-// one CTA per graph, thread t = target node.  smem: uint16 rank[two_e][vt]
+// one CTA per graph, thread t = target node.  smem: uint16 rank[two_e][vt] (+ uint32 nzmap[vt][nzw] when wide)
+// wide (v % 8 == 0 and the extra 4 * vt * nzw bytes fit): the row counts come in as 16-byte loads -- 8 targets of one
+// channel per load, two_e * v / 8 loads spread over the CTA, all independent -- instead of two_e 2-byte loads per thread
+// issued eight at a time; which channels of a target are non-empty is then collected in shared memory (atomicOr per
+// non-empty row, ~4 per node) instead of in registers.
 __global__ void __launch_bounds__(MAX_THREADS)
 graph_place_kernel(const uint32_t* __restrict__ bits, const uint16_t* __restrict__ rowcnt, int64_t b,
                    int two_e, int v, const int32_t* __restrict__ segposT,
                    const int32_t* __restrict__ tile_base, const int32_t* __restrict__ tptr,
-                   int32_t* __restrict__ msg_src, int32_t* __restrict__ tmsg) {
-  extern __shared__ uint16_t rank[];
+                   int32_t* __restrict__ msg_src, int32_t* __restrict__ tmsg, int wide) {
+  extern __shared__ __align__(16) uint16_t rank[];
   const int64_t g = blockIdx.x;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5, vt = blockDim.x;
   // load this target's row counts (independent loads, several in flight) and remember which channels are
   // non-empty: the emit loop below then visits ~4 rows per node instead of all 2E
   unsigned long long nz[4] = {0ull, 0ull, 0ull, 0ull};          // two_e <= 256
+  if (wide) {
+    const int nzw = (two_e + 31) >> 5;
+    uint32_t* nzmap = reinterpret_cast<uint32_t*>(rank + (size_t)two_e * vt);      // [vt][nzw]
+    for (int i = t; i < vt * nzw; i += vt) nzmap[i] = 0u;
+    if (vt > v)                                                  // padding targets: count 0 in every channel
+      for (int i = t; i < two_e * (vt - v); i += vt) rank[(i / (vt - v)) * vt + v + i % (vt - v)] = 0;
+    __syncthreads();
+    const int v8 = v >> 3, items = two_e * v8;
+#pragma unroll 4
+    for (int i = t; i < items; i += vt) {
+      const int e = i / v8, j = i - e * v8;
+      const uint4 c8 = __ldg(reinterpret_cast<const uint4*>(rowcnt + (g * two_e + e) * v) + j);
+      *reinterpret_cast<uint4*>(rank + e * vt + 8 * j) = c8;
+      const uint32_t w[4] = {c8.x, c8.y, c8.z, c8.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if ((w[k >> 1] >> (16 * (k & 1))) & 0xffffu) atomicOr(nzmap + (8 * j + k) * nzw + (e >> 5), 1u << (e & 31));
+    }
+    __syncthreads();
+    for (int q = 0; q < nzw; ++q) {                              // this target's non-empty channels -> registers
+      const unsigned long long m = nzmap[t * nzw + q];
+      const int q64 = q >> 1;
+      const unsigned long long bitsq = (q & 1) ? m << 32 : m;
+      nz[0] |= q64 == 0 ? bitsq : 0ull; nz[1] |= q64 == 1 ? bitsq : 0ull;
+      nz[2] |= q64 == 2 ? bitsq : 0ull; nz[3] |= q64 == 3 ? bitsq : 0ull;
+    }
+  } else {
 #pragma unroll 8
   for (int e = 0; e < two_e; ++e) {
     const uint16_t c = t < v ? rowcnt[(g * two_e + e) * v + t] : (uint16_t)0;
@@ -114,6 +146,7 @@ graph_place_kernel(const uint32_t* __restrict__ bits, const uint16_t* __restrict
     const int q = e >> 6;                                       // selects keep nz[] in registers
     nz[0] |= q == 0 ? bit : 0ull; nz[1] |= q == 1 ? bit : 0ull;
     nz[2] |= q == 2 ? bit : 0ull; nz[3] |= q == 3 ? bit : 0ull;
+  }
   }
   __syncthreads();
   // exclusive scan of every channel's row counts over the target index (warp per channel)
@@ -238,8 +271,12 @@ int ggnn_plan_bits_place(ggnn_ctx* ctx, const ggnn_plan_bits_pre& pre, int64_t b
   GGNN_LAUNCHED(ctx);
   GGNN_CUDA(ctx, cudaMemsetAsync(plan->msg_src, 0xFF, (size_t)plan->max_tiles * GGNN_TILE_M * sizeof(int32_t), st));
   const int vt = threads_for(v);
-  graph_place_kernel<<<(unsigned)b, vt, (size_t)two_e * vt * 2, st>>>(pre.bits, pre.rowcnt, b, two_e, v, pre.segposT,
-                                                                     tile_base, pre.tptr, plan->msg_src, plan->tmsg);
+  const size_t rank_bytes = (size_t)two_e * vt * 2, nz_bytes = (size_t)vt * ((two_e + 31) / 32) * 4;
+  static const bool no_wide = getenv("GGNN_PLACE_NARROW") != nullptr;       // A-B switch
+  const bool wide = !no_wide && v % 8 == 0 && rank_bytes + nz_bytes <= 48 * 1024;
+  graph_place_kernel<<<(unsigned)b, vt, rank_bytes + (wide ? nz_bytes : 0), st>>>(pre.bits, pre.rowcnt, b, two_e, v,
+                                                                                  pre.segposT, tile_base, pre.tptr,
+                                                                                  plan->msg_src, plan->tmsg, wide ? 1 : 0);
   GGNN_LAUNCHED(ctx);
   return GGNN_OK;
 }
