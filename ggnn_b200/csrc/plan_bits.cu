@@ -178,6 +178,24 @@ graph_place_kernel(const uint32_t* __restrict__ bits, const uint16_t* __restrict
       int mrow = tile_base[e] * GGNN_TILE_M + (segposT[(int64_t)e * b + g] - segposT[(int64_t)e * b]) +
                  rank[e * vt + t];
       const int64_t lo = r * v, hi = lo + v;
+      if ((v & 127) == 0) {                       // rows of whole 128-bit groups: one load per group instead of four
+        const uint4* p4 = reinterpret_cast<const uint4*>(bits + (lo >> 5));
+        for (int q4 = 0; q4 < (v >> 7); ++q4) {
+          const uint4 m4 = __ldg(p4 + q4);
+          const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint32_t m = mw[k];
+            while (m) {
+              const int bpos = __ffs(m) - 1;
+              m &= m - 1;
+              msg_src[mrow] = (int32_t)(g * v + (q4 * 128 + k * 32 + bpos));
+              tmsg[cursor++] = mrow++;
+            }
+          }
+        }
+        continue;
+      }
       for (int64_t w = lo >> 5; w <= (hi - 1) >> 5; ++w) {
         uint32_t m = __ldg(bits + w);
         const int64_t wb = w << 5;
