@@ -80,9 +80,7 @@ graph_count_kernel(const uint32_t* __restrict__ bits, int64_t b, int two_e, int 
       rowcnt[r] = (uint16_t)c;
     }
     deg += c;
-    int s = c;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const int s = (int)__reduce_add_sync(0xffffffffu, (unsigned)c);      // redux.sync: one instruction per channel
     if (lane == 0) part[wid * two_e + e] = (uint16_t)s;
   }
   if (t < v) tcnt[g * v + t] = deg;
