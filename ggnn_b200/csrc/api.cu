@@ -556,22 +556,25 @@ static int propagate_dense_impl(ggnn_ctx* ctx, int slot, const float* h0, const 
                              ggnn_f16_word_fold_ready(ctx, slot);
       ex->last_known = true; ex->last_word_fold = word_fold;
       bool counted = false;
+      const int64_t* pf_nnz = nullptr;
+      if (use_pf) {
+        // the background pass has been streaming this adjacency since the prefetch call: take the slices that are
+        // left at full occupancy -- FIRST, before the state conversion below: co-resident with the previous call's
+        // kernels the background pass ends ~0.1 ms after them, and the side stream's counting kernels wait for it
+        // (the plan's per-row arrays live behind the bitmask in the prefetch buffer: the side stream fills them)
+        char* pb = ex->ar[7 + pf.buf].p;
+        ws_alloc ap(pb + 4096);
+        ggnn_plan_bits_take_pre(ap, bc, two_e, v, &pre);
+        pf_nnz = ap.take<int64_t>(1);
+        prof_scope ps(ctx, GGNN_STAGE_COMPACT_MASK, st);
+        GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj_c, adj_dtype, rows * v, pre.bits, reinterpret_cast<unsigned*>(pb), false, st));
+      }
       if (precision == GGNN_PREC_F16)
         GGNN_TRY(f16_prologue(ctx, slot, f16_direct ? h0 + (size_t)g0 * v * h : h_chunk, bc * v, st));
       if (bits_in) {
         pre.bits = const_cast<uint32_t*>(bits_in) + (size_t)g0 * rows_per_graph * v / 32;     // read only from here on
       } else if (use_pf) {
-        // the background pass has been streaming this adjacency since the prefetch call: take the slices that are
-        // left at full occupancy, then wait for the background CTAs' last slices
-        // (the plan's per-row arrays live behind the bitmask in the prefetch buffer: the side stream may have filled them)
-        char* pb = ex->ar[7 + pf.buf].p;
-        ws_alloc ap(pb + 4096);
-        ggnn_plan_bits_take_pre(ap, bc, two_e, v, &pre);
-        const int64_t* pf_nnz = ap.take<int64_t>(1);
-        {
-          prof_scope ps(ctx, GGNN_STAGE_COMPACT_MASK, st);
-          GGNN_TRY(ggnn_bitmask_queue_launch(ctx, adj_c, adj_dtype, rows * v, pre.bits, reinterpret_cast<unsigned*>(pb), false, st));
-        }
+        // ... then wait for the background CTAs' last slices (and the counts that follow them on the side stream)
         GGNN_CUDA(ctx, cudaStreamWaitEvent(st, ex->pf_done[pf.buf], 0));
         ex->pf_last_buf = pf.buf;
         if (pf.counted && pf.word_fold == word_fold) {      // counts and scans are there already; the edge count joins the mailbox
