@@ -26,6 +26,7 @@
 #include "tc.cuh"
 #include "pack_t.cuh"
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 namespace w16 {
 
@@ -66,6 +67,7 @@ struct params {
   int n_tiles;                // row tiles when n_tiles_dev is null
   int KC, KC1;                // K chunks in total / in the first K segment
   int Ntot, NW, S;            // output columns, slice width, number of slices
+  int NB;                     // row blocks (>= 1): the activation sweeps run block by block, see item_iter
   const float* bias;          // [types][Ntot] zero-padded FP32
   int hw, h;
   int64_t N;                  // GATES / CAND: valid node rows
@@ -92,6 +94,37 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return v;
 }
 
+// This CTA's work items.  An item = (slice of the weights, 128-row tile); the activations are swept once per slice.
+// With ONE sweep order over all rows (slice-major), S > 1 sweeps of activations that do not stay in L2 come from DRAM
+// every time -- at h = 400 (98 MB of [x | h] against an L2 that holds ~60 MB of data every SM reads) ncu counted
+// 700 MB of DRAM reads per CAND launch (7 sweeps) and 656 MB per GATES launch.  So the rows are cut into NB blocks whose
+// activations do fit, blocks outermost; inside a block every CTA takes a contiguous range of the block's (slice, tile)
+// items (slice-major: the resident panel still changes only once or twice per block), and because every CTA owns a share
+// of EVERY block the whole chip works on one block at a time.  NB == 1 is the plain slice-major order.
+struct item_iter {
+  int nb, tb, n_tiles, S, blk, tiles_b;
+  unsigned cta, grid;
+  int64_t j, je;
+  __device__ __forceinline__ item_iter(int nb_, int n_tiles_, int S_, unsigned cta_, unsigned grid_)
+      : nb(nb_), tb((n_tiles_ + nb_ - 1) / nb_), n_tiles(n_tiles_), S(S_), blk(-1), tiles_b(1), cta(cta_), grid(grid_), j(0), je(0) {
+    next_block();
+  }
+  __device__ __forceinline__ void next_block() {
+    for (++blk; blk < nb; ++blk) {
+      tiles_b = min(tb, n_tiles - blk * tb);
+      if (tiles_b <= 0) { blk = nb; break; }
+      const int64_t total = (int64_t)tiles_b * S;
+      j = total * cta / grid;
+      je = total * (cta + 1) / grid;
+      if (j < je) return;
+    }
+  }
+  __device__ __forceinline__ bool valid() const { return blk < nb; }
+  __device__ __forceinline__ void advance() { if (++j >= je) next_block(); }
+  __device__ __forceinline__ int slice() const { return (int)(j / tiles_b); }
+  __device__ __forceinline__ int tile() const { return blk * tb + (int)(j % tiles_b); }
+};
+
 template <int MODE>
 __global__ void __launch_bounds__(NTHREADS, 1)
 wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
@@ -111,9 +144,7 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
 
   const bool a_tma = p.gather == nullptr;
   const int n_tiles = p.n_tiles_dev ? *p.n_tiles_dev : p.n_tiles;
-  const int64_t total = (int64_t)n_tiles * p.S;
-  const int64_t i_begin = total * blockIdx.x / gridDim.x;
-  const int64_t i_end = total * (blockIdx.x + 1) / gridDim.x;
+  const int nb = p.NB > 0 ? p.NB : 1;
 
   if (warp == WARP_MMA && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -146,8 +177,8 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
     uint32_t c = 0;                                       // running chunk counter of this CTA
     if (a_tma) {
       if (tid == 0) {
-        for (int64_t i = i_begin; i < i_end; ++i) {
-          const int t = (int)(i % n_tiles);
+        for (item_iter q(nb, n_tiles, p.S, blockIdx.x, gridDim.x); q.valid(); q.advance()) {
+          const int t = q.tile();
           const int row0 = (MODE == MODE_MSG ? (t % p.tiles_per_type) : t) * BM;
           for (int kc = 0; kc < p.KC; ++kc, ++c) {
             const int s = c % STAGES;
@@ -165,8 +196,8 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
       uint32_t a_off[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) a_off[j] = sw_off(rbase + 16 * j, slot);
-      for (int64_t i = i_begin; i < i_end; ++i) {
-        const int t = (int)(i % n_tiles);
+      for (item_iter q(nb, n_tiles, p.S, blockIdx.x, gridDim.x); q.valid(); q.advance()) {
+        const int t = q.tile();
         int src[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) src[j] = __ldg(p.gather + (size_t)t * BM + rbase + 16 * j);
@@ -192,8 +223,8 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
       uint32_t c = 0;
       int it = 0, cur_key = -1, w_gen = 0;
       const uint32_t panel_chunk = (uint32_t)p.NW * 128u;  // bytes of one K chunk of the panel
-      for (int64_t i = i_begin; i < i_end; ++i, ++it) {
-        const int sl = (int)(i / n_tiles), t = (int)(i % n_tiles);
+      for (item_iter q(nb, n_tiles, p.S, blockIdx.x, gridDim.x); q.valid(); q.advance(), ++it) {
+        const int sl = q.slice(), t = q.tile();
         const int type = MODE == MODE_MSG ? __ldg(p.tile_type + t) : 0;
         const int key = type * p.S + sl;
         const int n0 = sl * p.NW;
@@ -241,8 +272,8 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
     const uint32_t box_addr = sO + team * CHUNK;
     uint8_t* box = smem_al + (box_addr - base);
     int it = 0, cur_key = -1;
-    for (int64_t i = i_begin; i < i_end; ++i, ++it) {
-      const int sl = (int)(i / n_tiles), t = (int)(i % n_tiles);
+    for (item_iter qi(nb, n_tiles, p.S, blockIdx.x, gridDim.x); qi.valid(); qi.advance(), ++it) {
+      const int sl = qi.slice(), t = qi.tile();
       const int type = MODE == MODE_MSG ? __ldg(p.tile_type + t) : 0;
       const int key = type * p.S + sl;
       const int n0 = sl * p.NW;
@@ -258,6 +289,12 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
       const int64_t grow = (int64_t)row0 + r;
       const bool row_ok = MODE == MODE_MSG ? true : grow < p.N;
       const int ngroups = nw >> 6;
+      // A slice of ONE 64-column group (K = 2 hw > 512, i.e. h = 400: the resident panel is only 64 columns wide) would
+      // leave team 1 without work and make the kernel epilogue-bound (measured: 355 TFLOP/s in GATES at h = 400): the
+      // teams then alternate ITEMS instead of groups -- item `it` uses accumulator it & 1 and belongs to team it & 1
+      const bool alt = ngroups == 1;
+      const bool mine = !alt || (it & 1) == team;
+      const int g_first = alt ? 0 : team, g_step = alt ? 1 : 2;
       // GATES / CAND: this row's h (and u) values of a 64-column group; the first group's are requested BEFORE the
       // accumulator wait so their latency is not part of the per-item epilogue chain
       uint4 hv[8], uv[8];
@@ -280,14 +317,14 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
           }
         }
       };
-      if (team < ngroups) fetch(team);
-      tc::mbar_wait(bar(BAR_ACC_FULL + buf), (it >> 1) & 1);
-      tc::fence_after_sync();
-      for (int g = team; g < ngroups; g += 2) {
+      if (mine && g_first < ngroups) fetch(g_first);
+      tc::mbar_wait(bar(BAR_ACC_FULL + buf), (it >> 1) & 1);      // (also the team that skips the item: its arrival
+      tc::fence_after_sync();                                     //  below must not run ahead of the accumulator)
+      for (int g = mine ? g_first : ngroups; g < ngroups; g += g_step) {
         const int colbase = n0 + g * 64;                   // column in [0, Ntot)
         const bool is_r = colbase < p.hw;                  // GATES: reset-gate half
         const int hcol = is_r ? colbase : colbase - p.hw;  // column in [0, hw)
-        if (g != team) fetch(g);
+        if (g != g_first) fetch(g);
         if (leader) tc::tma_store_wait_read();             // the team's box is free again
         tc::named_bar_sync(1 + team, 128);
 #pragma unroll
@@ -314,9 +351,9 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
 #pragma unroll
               for (int k4 = 0; k4 < 4; ++k4)
                 if (hcol + c16 * 16 + k4 * 4 < p.h)
-                  *reinterpret_cast<float4*>(dst + k4 * 4) =
-                      make_float4(__uint_as_float(acc[k4 * 4]), __uint_as_float(acc[k4 * 4 + 1]),
-                                  __uint_as_float(acc[k4 * 4 + 2]), __uint_as_float(acc[k4 * 4 + 3]));
+                  __stcs(reinterpret_cast<float4*>(dst + k4 * 4),          // streaming: the tape must not push the operands out of L2
+                         make_float4(__uint_as_float(acc[k4 * 4]), __uint_as_float(acc[k4 * 4 + 1]),
+                                     __uint_as_float(acc[k4 * 4 + 2]), __uint_as_float(acc[k4 * 4 + 3])));
             }
           } else {
             float hh[16], uu[16];
@@ -334,16 +371,16 @@ wgemm16_kernel(const params p, const __grid_constant__ CUtensorMap tmA1, const _
 #pragma unroll
               for (int k4 = 0; k4 < 4; ++k4)
                 if (hcol + c16 * 16 + k4 * 4 < p.h)
-                  *reinterpret_cast<float4*>(dst + k4 * 4) =
-                      make_float4(__uint_as_float(acc[k4 * 4]), __uint_as_float(acc[k4 * 4 + 1]),
-                                  __uint_as_float(acc[k4 * 4 + 2]), __uint_as_float(acc[k4 * 4 + 3]));
+                  __stcs(reinterpret_cast<float4*>(dst + k4 * 4),          // streaming: the tape must not push the operands out of L2
+                         make_float4(__uint_as_float(acc[k4 * 4]), __uint_as_float(acc[k4 * 4 + 1]),
+                                     __uint_as_float(acc[k4 * 4 + 2]), __uint_as_float(acc[k4 * 4 + 3])));
             }
             if (p.h_out && row_ok) {
               float* dst = p.h_out + grow * p.h + hcol + c16 * 16;
 #pragma unroll
               for (int k4 = 0; k4 < 4; ++k4)
                 if (hcol + c16 * 16 + k4 * 4 < p.h)
-                  *reinterpret_cast<float4*>(dst + k4 * 4) = make_float4(o[k4 * 4], o[k4 * 4 + 1], o[k4 * 4 + 2], o[k4 * 4 + 3]);
+                  __stcs(reinterpret_cast<float4*>(dst + k4 * 4), make_float4(o[k4 * 4], o[k4 * 4 + 1], o[k4 * 4 + 2], o[k4 * 4 + 3]));
             }
           }
           *reinterpret_cast<uint4*>(box + sw_off(r, 2 * c16)) = pack8(o);
@@ -501,6 +538,17 @@ int slice_width(int K, int Ntot) {
   if (nw > MAX_NW) nw = MAX_NW;
   if (nw > Ntot) nw = Ntot;
   return nw;
+}
+
+// row blocks of item_iter: blocks whose activations ([rows x K] FP16) stay below ~32 MB when they are swept more than once
+int row_blocks(int64_t n_row_tiles, int K, int S) {
+  static const int64_t block_bytes = getenv("GGNN_W16_BLOCK_MB") ? (int64_t)atoi(getenv("GGNN_W16_BLOCK_MB")) << 20 : (int64_t)32 << 20;
+  if (S <= 1 || block_bytes <= 0) return 1;
+  const int64_t bytes = n_row_tiles * BM * (int64_t)K * 2;
+  int64_t nb = (bytes + block_bytes - 1) / block_bytes;
+  if (nb < 1) nb = 1;
+  if (nb > n_row_tiles) nb = n_row_tiles;
+  return (int)nb;
 }
 
 template <int MODE>
@@ -1249,6 +1297,7 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     p.state16 = reinterpret_cast<const __half*>(state16);
     if (tape) { p.tape_g = tape->r; p.tape_u = tape->u; }
     prof_scope ps(ctx, GGNN_STAGE_GRU_GATES, st);
+    p.NB = row_blocks(n_row_tiles, 2 * hw, p.S);
     GGNN_TRY(launch<MODE_GATES>(ctx, p, tmActs, tmState, ctx->tm_Wg16, tmRh, tmU, (int64_t)n_row_tiles * p.S, st));
   }
   {
@@ -1262,6 +1311,7 @@ int ggnn_step_w16(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, void* msg16, v
     p.h_out = last_step ? h_out : nullptr;
     if (tape) p.tape_g = tape->c;
     prof_scope ps(ctx, GGNN_STAGE_GRU_CAND, st);
+    p.NB = row_blocks(n_row_tiles, 2 * hw, p.S);
     GGNN_TRY(launch<MODE_CAND>(ctx, p, tmActs, tmRh, ctx->tm_Wc16, tmState, tmState, (int64_t)n_row_tiles * p.S, st));
   }
   return GGNN_OK;
