@@ -158,6 +158,7 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
     free_dev(c, c->edge[s].B);
     free_dev(c, c->edge[s].Wt_tf32);
     free_dev(c, c->edge[s].Wt_tf32_lo);
+    free_dev(c, c->edge[s].Wt_tf32_hl);
     if (c->edge[s].Wt_f16) { cudaFree(c->edge[s].Wt_f16); c->edge[s].Wt_f16 = nullptr; }
     free_dev(c, c->edge[s].B_pad16);
     if (c->edge[s].fold_f16) { cudaFree(c->edge[s].fold_f16); c->edge[s].fold_f16 = nullptr; }
@@ -166,7 +167,7 @@ extern "C" void ggnn_destroy(ggnn_ctx* c) {
   free_dev(c, c->Wg); free_dev(c, c->bg); free_dev(c, c->Wc); free_dev(c, c->bc);
   if (c->Wgt_f16) cudaFree(c->Wgt_f16);
   if (c->Wct_f16) cudaFree(c->Wct_f16);
-  free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->Wgt_tf32_lo); free_dev(c, c->Wct_tf32_lo); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
+  free_dev(c, c->Wgt_tf32); free_dev(c, c->Wct_tf32); free_dev(c, c->Wgt_tf32_lo); free_dev(c, c->Wct_tf32_lo); free_dev(c, c->Wgt_tf32_hl); free_dev(c, c->Wct_tf32_hl); free_dev(c, c->bg_pad); free_dev(c, c->bc_pad);
   if (c->btab16) cudaFree(c->btab16);
   free_dev(c, c->bg_w16); free_dev(c, c->bc_w16);
   if (c->ws) {

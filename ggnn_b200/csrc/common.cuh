@@ -19,6 +19,8 @@ struct ggnn_edge_weights {
   float* Wt_tf32 = nullptr;// [two_e, hp, hp] TF32-rounded, transposed ([n][k]), zero padded to hp
   float* Wt_tf32_lo = nullptr; // same layout, tf32(W - tf32(W)): the residual pack of the strict (3xTF32) mode
   CUtensorMap tm_Wt_lo;
+  float* Wt_tf32_hl = nullptr; // hp == 128: [two_e][hi | lo][hp][hp], one 32 KB TMA box brings both packs of a K chunk
+  CUtensorMap tm_Wt_hl;
   void*  Wt_f16 = nullptr; // [two_e, P, P] FP16, transposed ([n][k]), zero padded; P = 128 (hp == 128) or hw16 (h > 128)
   CUtensorMap tm_Wt16;     // TMA view of Wt_f16 as [two_e*128 rows, 128 cols], box 64 x 128
   CUtensorMap tm_Wt16q;    // same, box 64 x 64 rows (gru_pair.cu: half of a matrix's output columns per CTA)
@@ -54,6 +56,9 @@ struct ggnn_ctx {
   float* Wct_tf32 = nullptr; // [hp, 2hp]
   float* Wgt_tf32_lo = nullptr, *Wct_tf32_lo = nullptr;   // residual packs (strict mode)
   CUtensorMap tm_Wg_lo, tm_Wc_lo, tm_Wg_half;   // (tm_Wg_lo / tm_Wg_half: boxes of hp rows)
+  float* Wgt_tf32_hl = nullptr, *Wct_tf32_hl = nullptr;   // hp == 128: [half][hi | lo][hp][2hp] and [hi | lo][hp][2hp]
+  CUtensorMap tm_Wg_hl, tm_Wc_hl;
+  bool hl_ok = false;
   void* Wgt_f16 = nullptr;   // [256, 256] FP16 packed like Wgt_tf32 (hp == 128 only)
   void* Wct_f16 = nullptr;   // [128, 256]
   CUtensorMap tm_Wg16, tm_Wc16;

@@ -64,6 +64,8 @@ struct params {
   const float* hstate;      // GATES: h
   const float* ubuf;        // CAND: u
   int b_bytes;              // bytes one TMA box of the weight maps delivers per K chunk
+  int combined;             // tmHi maps the [hi | lo] side-by-side pack (hp == 128): ONE 32 KB box per K chunk instead of two
+                            // 16 KB ones -- a bulk copy costs ~0.2 us whatever its size (scripts/micro/mc_stream.cu)
   int dbg;                  // timing experiments (GGNN_STC_DBG): 1 = epilogue touches no global memory, 2 = no split math,
                             // 4 = one MMA per K step instead of three
   unsigned long long* trace;// development aid (ggnn_debug_trace): %globaltimer of CTA 0's roles, MODE_GATES launches only
@@ -222,8 +224,12 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
         const int b_row = MODE == MODE_MSG ? __ldg(p.tile_type + itw) * p.Np : (MODE == MODE_GATES ? (itw & 1) * p.Np : 0);
         const uint32_t st0 = base + (uint32_t)s * st_bytes;
         tc::mbar_arrive_expect_tx(bar(BAR_FULL + s), 2u * (uint32_t)p.b_bytes);
-        tc::tma_load_2d(st0 + 2 * A_BYTES, &tmHi, kcw * BKF, b_row, bar(BAR_FULL + s));
-        tc::tma_load_2d(st0 + 2 * A_BYTES + b_alloc, &tmLo, kcw * BKF, b_row, bar(BAR_FULL + s));
+        if (p.combined) {       // rows [2 b_row, 2 b_row + Np) = hi -> B_hi, the next Np rows = lo -> B_lo (b_alloc == Np * 128 here)
+          tc::tma_load_2d(st0 + 2 * A_BYTES, &tmHi, kcw * BKF, 2 * b_row, bar(BAR_FULL + s));
+        } else {
+          tc::tma_load_2d(st0 + 2 * A_BYTES, &tmHi, kcw * BKF, b_row, bar(BAR_FULL + s));
+          tc::tma_load_2d(st0 + 2 * A_BYTES + b_alloc, &tmLo, kcw * BKF, b_row, bar(BAR_FULL + s));
+        }
         if (++kcw == KC) { kcw = 0; ++itw; }
       };
       if (total > 0) issue_w(0);
@@ -394,6 +400,8 @@ int ggnn_step_fp32_tc(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn
   const ggnn_edge_weights& ew = ctx->edge[slot];
   if (plan.N == 0) return GGNN_OK;
   if (!ew.Wt_tf32_lo) GGNN_FAIL(ctx, GGNN_E_STATE, "internal: strict tensor-core mode without residual weight packs");
+  static const bool split_boxes = getenv("GGNN_STC_SPLIT_BOXES") != nullptr;      // A-B switch: two 16 KB weight boxes per chunk
+  const bool hl = !split_boxes && hp == 128 && ctx->hl_ok && ew.Wt_tf32_hl != nullptr;
   if (plan.max_tiles > 0 && plan.nnz > 0) {
     prof_scope ps(ctx, GGNN_STAGE_MSG, st);
     params p{};
@@ -403,7 +411,8 @@ int ggnn_step_fp32_tc(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn
     p.tile_type = plan.tile_type; p.n_tiles = plan.n_tiles;
     p.out0 = bufs.msg;
     p.b_bytes = ew.tm_rows * BKF * 4;
-    GGNN_TRY(launch<MODE_MSG>(ctx, p, ew.tm_Wt, ew.tm_Wt_lo, plan.max_tiles, st));
+    p.combined = hl ? 1 : 0;
+    GGNN_TRY(launch<MODE_MSG>(ctx, p, hl ? ew.tm_Wt_hl : ew.tm_Wt, ew.tm_Wt_lo, plan.max_tiles, st));
   }
   GGNN_TRY(ggnn_aggregate(ctx, plan, bufs.msg, bufs.acts, h, /*round_tf32=*/false, st));
   const int64_t mt = ceil_div64(plan.N, BM);
@@ -414,7 +423,8 @@ int ggnn_step_fp32_tc(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn
     p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = hp; p.M = plan.N; p.n_tiles_host = (int)(2 * mt);
     p.out0 = bufs.rh; p.out1 = bufs.u; p.hstate = h_state;
     p.b_bytes = hp * BKF * 4;
-    GGNN_TRY(launch<MODE_GATES>(ctx, p, ctx->tm_Wg_half, ctx->tm_Wg_lo, 2 * mt, st));
+    p.combined = hl ? 1 : 0;
+    GGNN_TRY(launch<MODE_GATES>(ctx, p, hl ? ctx->tm_Wg_hl : ctx->tm_Wg_half, ctx->tm_Wg_lo, 2 * mt, st));
   }
   {
     prof_scope ps(ctx, GGNN_STAGE_GRU_CAND, st);
@@ -423,7 +433,8 @@ int ggnn_step_fp32_tc(ggnn_ctx* ctx, int slot, const ggnn_plan& plan, const ggnn
     p.h = h; p.hp = hp; p.Kp = 2 * hp; p.Np = hp; p.M = plan.N; p.n_tiles_host = (int)mt;
     p.out0 = h_state; p.ubuf = bufs.u;
     p.b_bytes = ctx->tm_rows_c * BKF * 4;
-    GGNN_TRY(launch<MODE_CAND>(ctx, p, ctx->tm_Wc, ctx->tm_Wc_lo, mt, st));
+    p.combined = hl ? 1 : 0;
+    GGNN_TRY(launch<MODE_CAND>(ctx, p, hl ? ctx->tm_Wc_hl : ctx->tm_Wc, ctx->tm_Wc_lo, mt, st));
   }
   return GGNN_OK;
 }

@@ -470,6 +470,13 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
     GGNN_LAUNCHED(ctx);
     int rows_lo;
     GGNN_TRY(make_weight_map(ctx, &ew.tm_Wt_lo, ew.Wt_tf32_lo, (int64_t)two_e * hp, hp, &rows_lo, hp));
+    if (hp == 128) {     // both packs of a type side by side: strict_tc.cu fetches them as ONE 32 KB box per K chunk
+      GGNN_TRY(realloc_f(ctx, ew.Wt_tf32_hl, (size_t)two_e * 2 * hp * hp));
+      const size_t blk = (size_t)hp * hp * 4;
+      GGNN_CUDA(ctx, cudaMemcpy2DAsync(ew.Wt_tf32_hl, 2 * blk, ew.Wt_tf32, blk, blk, two_e, cudaMemcpyDeviceToDevice, st));
+      GGNN_CUDA(ctx, cudaMemcpy2DAsync(ew.Wt_tf32_hl + (size_t)hp * hp, 2 * blk, ew.Wt_tf32_lo, blk, blk, two_e, cudaMemcpyDeviceToDevice, st));
+      GGNN_TRY(ggnn_make_tmap_2d(ctx, &ew.tm_Wt_hl, ew.Wt_tf32_hl, (int64_t)two_e * 2 * hp, hp, 2 * hp));
+    }
   }
   if (with_gru) {
     GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32, (size_t)4 * hp * hp));
@@ -492,6 +499,19 @@ int ggnn_tf32_pack_weights(ggnn_ctx* ctx, int slot, bool with_gru, cudaStream_t 
       GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg_lo, ctx->Wgt_tf32_lo, 2 * hp, 2 * hp, hp));
       GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg_half, ctx->Wgt_tf32, 2 * hp, 2 * hp, hp));
       GGNN_TRY(make_weight_map(ctx, &ctx->tm_Wc_lo, ctx->Wct_tf32_lo, hp, 2 * hp, &r_, hp));
+      ctx->hl_ok = false;
+      if (hp == 128) {
+        GGNN_TRY(realloc_f(ctx, ctx->Wgt_tf32_hl, (size_t)8 * hp * hp));
+        GGNN_TRY(realloc_f(ctx, ctx->Wct_tf32_hl, (size_t)4 * hp * hp));
+        const size_t half = (size_t)hp * 2 * hp * 4;         // one N = hp half of the gate weights, or all of Wc
+        GGNN_CUDA(ctx, cudaMemcpy2DAsync(ctx->Wgt_tf32_hl, 2 * half, ctx->Wgt_tf32, half, half, 2, cudaMemcpyDeviceToDevice, st));
+        GGNN_CUDA(ctx, cudaMemcpy2DAsync(ctx->Wgt_tf32_hl + (size_t)hp * 2 * hp, 2 * half, ctx->Wgt_tf32_lo, half, half, 2, cudaMemcpyDeviceToDevice, st));
+        GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->Wct_tf32_hl, ctx->Wct_tf32, half, cudaMemcpyDeviceToDevice, st));
+        GGNN_CUDA(ctx, cudaMemcpyAsync(ctx->Wct_tf32_hl + (size_t)hp * 2 * hp, ctx->Wct_tf32_lo, half, cudaMemcpyDeviceToDevice, st));
+        GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wg_hl, ctx->Wgt_tf32_hl, 4 * hp, 2 * hp, 2 * hp));
+        GGNN_TRY(ggnn_make_tmap_2d(ctx, &ctx->tm_Wc_hl, ctx->Wct_tf32_hl, 2 * hp, 2 * hp, 2 * hp));
+        ctx->hl_ok = true;
+      }
     }
     pack_bias_kernel<<<(2 * hp + 255) / 256, 256, 0, st>>>(ctx->bg, ctx->bg_pad, 2, h, hp);
     GGNN_LAUNCHED(ctx);
