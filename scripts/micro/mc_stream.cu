@@ -100,6 +100,42 @@ stream_kernel(const uint8_t* __restrict__ src_base_, int n_chunks_set, long long
   if (tid == 0) out_clk[blockIdx.x] = clock64() - t0;
 }
 
+// mode 2: unicast like mode 0, but TWO threads of the CTA (different warps) each drive half of the ring: is the ~0.2 us per
+// copy a cost of the issuing thread or of the SM's copy engine?
+__global__ void __launch_bounds__(128, 1)
+stream2_kernel(const uint8_t* __restrict__ src_base_, int n_chunks_set, long long total, size_t private_bytes) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ __align__(8) uint64_t full[STAGES];
+  const int tid = threadIdx.x;
+  const uint8_t* src_base = src_base_ + (size_t)blockIdx.x * private_bytes;
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&full[s])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0 || tid == 32) {
+    const int half = tid >> 5, HS = STAGES / 2;
+    long long issued = 0, done = 0;
+    const long long my_total = total / 2;
+    unsigned rng = 12345u + blockIdx.x * 7919u + half * 104729u;
+    while (done < my_total) {
+      while (issued < my_total && issued - done < HS) {
+        const int s = half * HS + (int)(issued % HS);
+        rng = rng * 1664525u + 1013904223u;
+        const uint8_t* src = src_base + (size_t)((rng >> 8) % (unsigned)n_chunks_set) * CHUNK;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&full[s])), "r"(CHUNK) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(smem + s * CHUNK)), "l"(src), "r"(CHUNK), "r"(smem_u32(&full[s])) : "memory");
+        ++issued;
+      }
+      const int s = half * HS + (int)(done % HS);
+      wait_parity(smem_u32(&full[s]), (unsigned)((done / HS) & 1));
+      ++done;
+    }
+  }
+  __syncthreads();
+}
+
 int main() {
   int dev = 0, sms = 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -116,6 +152,20 @@ int main() {
   const long long total = (64ll << 20) / CHUNK;  // chunks received per CTA: 64 MB
   printf("SMs %d; %d-slot ring of %d KB bulk copies out of an L2-resident 3 MB set; %lld chunks received per CTA\n", sms, STAGES,
          CHUNK / 1024, total);
+  cudaFuncSetAttribute(stream2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a);
+    stream2_kernel<<<sms, 128, smem_bytes>>>(w, (int)(private_bytes / CHUNK), total, private_bytes);
+    cudaEventRecord(b);
+    if (cudaDeviceSynchronize() != cudaSuccess) { printf("CUDA error\n"); return 1; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    if (rep == 2)
+      printf("private regions, mode 2 (two issuing threads, half a ring each): %.3f ms -> each SM RECEIVES %.1f GB/s\n", ms,
+             (double)total * CHUNK / ms / 1e6);
+  }
   for (int priv = 0; priv < 2; ++priv)
   for (int mode = 0; mode < 2; ++mode) {
     const size_t pb = priv ? private_bytes : 0;
