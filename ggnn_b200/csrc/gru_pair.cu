@@ -109,10 +109,19 @@ struct bias_tab {
   float bn[HP];             // bias of channel 2E-1
 };
 
-// development aid: event `ev` of iteration `it`, CTA `blockIdx.x` (0 or 1), nanoseconds
+// development aid: event `ev` of iteration `it`, CTA `blockIdx.x` (0 or 1), nanoseconds.
+// Built with -DGGNN_PAIR_WIDE_TRACE (GGNN_NVCC_EXTRA, scripts/gpu_pair_wide.py) the traced cluster can be chosen
+// (GGNN_PAIR_TRACE_CLUSTER) and GP_WIDE records every CTA's entry / set-up / weights-in / pair starts / exit; in the shipped
+// build those hooks are compiled out -- even never taken they cost the kernel 5 % when it runs alone (3.00 -> 3.15 ms per
+// 4 096 graphs x 8 steps, measured)
+#ifdef GGNN_PAIR_WIDE_TRACE
+#define GP_TRACED_CLUSTER ((int)(blockIdx.x >> 1) == p.dbg_cluster)
+#else
+#define GP_TRACED_CLUSTER (blockIdx.x < 2)
+#endif
 #define GP_TRACE(ev)                                                                            \
   do {                                                                                          \
-    if (p.dbg && (blockIdx.x >> 1) == p.dbg_cluster && it < 12) {                               \
+    if (p.dbg && GP_TRACED_CLUSTER && it < 12) {                                                \
       unsigned long long t_;                                                                    \
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                    \
       p.dbg[(((blockIdx.x & 1) * 12 + it) * 32 + (ev))] = t_;                                   \
@@ -120,6 +129,9 @@ struct bias_tab {
   } while (0)
 
 // whole-grid trace behind the cluster-0 one: per CTA 48 slots (0 entry, 1 set-up done, 2 weights in, 3 exit, 8 + it: MMAs of pair it start)
+#ifndef GGNN_PAIR_WIDE_TRACE
+#define GP_WIDE(slot) do { } while (0)
+#else
 #define GP_WIDE(slot)                                                                           \
   do {                                                                                          \
     if (p.dbg && p.dbg_wide) {                                                                  \
@@ -128,6 +140,7 @@ struct bias_tab {
       p.dbg[2 * 12 * 32 + blockIdx.x * 48 + (slot)] = t_;                                       \
     }                                                                                           \
   } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t sw_off(int r, int slot) {     // 16-byte slot `slot` of row r in a swizzled chunk
   return (r >> 3) * 1024 + (r & 7) * 128 + ((slot ^ (r & 7)) << 4);
@@ -231,11 +244,13 @@ gru_pair_kernel(const params p, const __grid_constant__ CUtensorMap tmH, const _
   // A pair exists while its EVEN tile does (the odd one may lie past the end: loaded as zeros, stored clipped).
   const int tile0 = (int)blockIdx.x;                     // = 2 * (blockIdx.x >> 1) + rank
   if (tid == 0) GP_WIDE(0);
+#ifdef GGNN_PAIR_WIDE_TRACE
   if (tid == 0 && p.dbg && p.dbg_wide) {
     unsigned smid_;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));
     p.dbg[2 * 12 * 32 + blockIdx.x * 48 + 4] = smid_;
   }
+#endif
   auto live = [&](int tile) { return tile - (int)rank < p.n_tiles; };
   auto is_reg = [&](int tile) { return p.regular && tile < p.n_tiles && __ldg(p.regular + tile) != 0; };
 

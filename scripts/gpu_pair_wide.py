@@ -1,4 +1,5 @@
-"""Whole-grid timing of gru_pair_kernel (GP_WIDE): per CTA entry / set-up / weights-in / pair starts / exit -- development aid."""
+"""Needs a library built with GGNN_NVCC_EXTRA=-DGGNN_PAIR_WIDE_TRACE python ggnn_b200/build.py --force (the hooks are compiled out otherwise).
+Whole-grid timing of gru_pair_kernel (GP_WIDE): per CTA entry / set-up / weights-in / pair starts / exit -- development aid."""
 import sys, os, ctypes
 os.environ["GGNN_PAIR_TRACE_WIDE"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
