@@ -1,4 +1,5 @@
-"""Phase trace of gru_pair_kernel (cluster 0, first iterations) -- development aid."""
+"""Phase trace of gru_pair_kernel (cluster 0, first iterations) -- development aid.
+Needs a library built with GGNN_NVCC_EXTRA=-DGGNN_PAIR_TRACE python ggnn_b200/build.py --force (hooks compiled out otherwise)."""
 import sys, os, ctypes
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
