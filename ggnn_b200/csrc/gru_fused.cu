@@ -58,12 +58,18 @@ struct gparams {
   unsigned long long* dbg;  // optional [64 events x 16 iterations] globaltimer trace of CTA 0
 };
 
+// (compiled out unless built with GGNN_NVCC_EXTRA=-DGGNN_GRU_FUSED_TRACE: hooks that are never taken still cost the
+//  CTA-pair kernel of gru_pair.cu 4-9 % -- measured there)
 __device__ __forceinline__ void trace(const gparams& p, int it, int ev) {
+#ifdef GGNN_GRU_FUSED_TRACE
   if (p.dbg && blockIdx.x == 0 && it < 16) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     p.dbg[it * 64 + ev] = t;
   }
+#else
+  (void)p; (void)it; (void)ev;
+#endif
 }
 
 // barrier slots (8 bytes each) after the operand buffers

@@ -70,6 +70,7 @@ struct params {
                             // 4 = one MMA per K step instead of three
   unsigned long long* trace;// development aid (ggnn_debug_trace): %globaltimer of CTA 0's roles, MODE_GATES launches only
 };
+#ifdef GGNN_STC_TRACE                 // development build (GGNN_NVCC_EXTRA=-DGGNN_STC_TRACE, scripts/gpu_stc_trace.py)
 #define STC_TRACE(slot, idx)                                                                     \
   do {                                                                                           \
     if (MODE == MODE_GATES && p.trace && blockIdx.x == 0 && (idx) < 64) {                        \
@@ -78,6 +79,9 @@ struct params {
       p.trace[(slot) * 64 + (idx)] = t_;                                                         \
     }                                                                                            \
   } while (0)
+#else
+#define STC_TRACE(slot, idx) do { } while (0)
+#endif
 
 // gate math: ex2.approx / rcp.approx forms (~2e-7 relative).  Measured: accurate expf / tanhf change the end-to-end
 // error by < 2 % (it is set by the tensor core's accumulation, see the header) and cost 3 ms per 4 096-graph chunk.
