@@ -1,4 +1,5 @@
-"""Phase trace of the fused GRU kernel (CTA 0, first iterations) -- development aid."""
+"""Needs a library built with GGNN_NVCC_EXTRA=-DGGNN_GRU_FUSED_TRACE python ggnn_b200/build.py --force.
+Phase trace of the fused GRU kernel (CTA 0, first iterations) -- development aid."""
 import sys, os, ctypes
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
