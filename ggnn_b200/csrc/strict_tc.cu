@@ -70,6 +70,12 @@ struct params {
                             // 4 = one MMA per K step instead of three
   unsigned long long* trace;// development aid (ggnn_debug_trace): %globaltimer of CTA 0's roles, MODE_GATES launches only
 };
+// the timing experiments of GGNN_STC_DBG exist only in builds with -DGGNN_STC_TRACE as well (a constant 0 otherwise)
+#ifdef GGNN_STC_TRACE
+#define STC_DBG(p) ((p).dbg)
+#else
+#define STC_DBG(p) 0
+#endif
 #ifdef GGNN_STC_TRACE                 // development build (GGNN_NVCC_EXTRA=-DGGNN_STC_TRACE, scripts/gpu_stc_trace.py)
 #define STC_TRACE(slot, idx)                                                                     \
   do {                                                                                           \
@@ -200,7 +206,7 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
 #pragma unroll
       for (int j = 0; j < RPT; ++j) {
         float4 hi, lo;
-        if (p.dbg & 2) { hi = x[j]; lo = x[j]; } else {
+        if (STC_DBG(p) & 2) { hi = x[j]; lo = x[j]; } else {
         // round-half-up in two integer ops (tc::to_tf32_fast) instead of cvt.rna (a conversion-unit instruction, 16 per
         // clock per SM): x - hi is exact either way and lo only has to be SOME TF32 number within 2^-11 of it
         hi.x = tc::to_tf32_fast(x[j].x); hi.y = tc::to_tf32_fast(x[j].y); hi.z = tc::to_tf32_fast(x[j].z); hi.w = tc::to_tf32_fast(x[j].w);
@@ -251,7 +257,7 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
           const uint32_t a0 = base + (uint32_t)s * st_bytes, b0 = a0 + 2 * A_BYTES;
 #pragma unroll
           for (int k = 0; k < BKF / 8; ++k) {         // UMMA K = 8 for TF32 (32 bytes)
-            if (!(p.dbg & 4)) {
+            if (!(STC_DBG(p) & 4)) {
             tc::umma_tf32(dx, tc::umma_desc_sw128(a0 + k * 32), tc::umma_desc_sw128(b0 + b_alloc + k * 32), idesc, (kc | k) != 0);
             tc::umma_tf32(dx, tc::umma_desc_sw128(a0 + A_BYTES + k * 32), tc::umma_desc_sw128(b0 + k * 32), idesc, 1u); }
             tc::umma_tf32(d, tc::umma_desc_sw128(a0 + k * 32), tc::umma_desc_sw128(b0 + k * 32), idesc, (kc | k) != 0);
@@ -284,7 +290,7 @@ split_gemm_kernel(const params p, const __grid_constant__ CUtensorMap tmHi, cons
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const int64_t row = (int64_t)tile * BM + prow + 16 * k;
-        ok[k] = row < p.M && !(p.dbg & 1);
+        ok[k] = row < p.M && !(STC_DBG(p) & 1);
         if (MODE == MODE_MSG && ok[k]) ok[k] = __ldg(p.gather + row) >= 0;
       }
       const float* bias = p.bias;
